@@ -1,0 +1,161 @@
+/*
+ * gsr_b200.h -- C ABI of the B200-native Gaussian-splatting rasterizer.
+ *
+ * This is the drop-in boundary for the one hot path of s-esposito/MonoGS:
+ * the differentiable rasterizer with SE(3) pose gradients and simple-knn's
+ * distCUDA2.  Every entry point below replaces one interface of the
+ * reference (paths relative to /root/reference/submodules):
+ *
+ *   gsr_forward_plan + gsr_forward_render
+ *        <- CudaRasterizer::Rasterizer::forward
+ *           (diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:33-60,
+ *            rasterizer_impl.cu:198-344), bound to Python by
+ *            RasterizeGaussiansCUDA (rasterize_points.cu:35-122, ext.cpp:16)
+ *   gsr_backward
+ *        <- CudaRasterizer::Rasterizer::backward (rasterizer.h:62-92,
+ *           rasterizer_impl.cu:348-455), bound by
+ *           RasterizeGaussiansBackwardCUDA (rasterize_points.cu:124-211)
+ *   gsr_mark_visible
+ *        <- CudaRasterizer::Rasterizer::markVisible (rasterizer.h:26-31,
+ *           rasterizer_impl.cu:141-153), bound by markVisible
+ *           (rasterize_points.cu:213-232)
+ *   gsr_knn_dist2
+ *        <- SimpleKNN::knn (simple-knn/simple_knn.cu:185-221), bound by
+ *           distCUDA2 (simple-knn/spatial.cu:15-26)
+ *   gsr_sort_pairs_u64 / gsr_debug_*  -- test hooks for the bit-exact
+ *           parity of keys, lists and ranges (rasterizer_impl.cu:70-138,306-311)
+ *
+ * The reference's std::function<char*(size_t)> resize callbacks
+ * (rasterizer.h:34-36) become caller-allocated workspaces whose sizes are
+ * returned by the gsr_*_bytes functions; the forward is split in two calls
+ * around the one unavoidable host read of num_rendered
+ * (rasterizer_impl.cu:284).
+ *
+ * Conventions: all data pointers are DEVICE pointers (fp32 / int32 row-major,
+ * exactly the tensors the reference binding receives); a NULL pointer means
+ * "absent" like the reference's empty tensors (forward.cu:207,243);
+ * `stream` is a cudaStream_t passed as void*; every function returns 0 on
+ * success, a negative GSR_E* code for bad arguments, or a positive
+ * cudaError_t value.  No torch types appear here.
+ */
+#ifndef GSR_B200_H_
+#define GSR_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_OK 0
+#define GSR_EINVAL (-1)     /* bad argument combination / size            */
+#define GSR_ENOCOLOR (-2)   /* neither shs nor colors_precomp              */
+#define GSR_ENOCOV (-3)     /* neither scales+rotations nor cov3D_precomp  */
+#define GSR_EPREFILTER (-4) /* prefiltered=1 but a point was culled        */
+#define GSR_EOVERFLOW (-5)  /* num_rendered does not fit the index type    */
+
+/* Library / build identification ("sm_100a", version). */
+const char* gsr_version(void);
+
+/* ---- workspace sizes (bytes). All workspaces need 256-byte alignment. -- */
+/* Per-Gaussian state written by forward and re-read by backward. */
+size_t gsr_geom_bytes(int P, int width, int height);
+/* Per-pixel state (final T, n_contrib) + per-tile ranges; saved for backward. */
+size_t gsr_image_bytes(int width, int height);
+/* Sorted instance list (Gaussian ids in tile|depth order); saved for backward. */
+size_t gsr_point_list_bytes(int64_t num_rendered);
+/* Temporary key/value ping-pong buffers + radix-sort scratch; forward only. */
+size_t gsr_binning_bytes(int64_t num_rendered);
+/* Scratch for gsr_backward (packed per-Gaussian partial gradients, tau partials). */
+size_t gsr_backward_scratch_bytes(int P);
+/* Scratch for gsr_knn_dist2. */
+size_t gsr_knn_bytes(int P);
+
+/* ---- forward, phase 1: preprocess + tile-count scan ---------------------
+ * Projects every Gaussian, fills radii[P] (int32) and the geometry state,
+ * the per-tile ranges (in image_ws) and the radix digit offsets, and returns
+ * num_rendered = sum of tiles touched through *num_rendered (host int64).  This call synchronises `stream` once (the reference does a
+ * blocking cudaMemcpy at the same place). */
+int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs /*M*/,
+                     int width, int height,
+                     const float* means3D, const float* shs,
+                     const float* colors_precomp, const float* opacities,
+                     const float* scales, float scale_modifier,
+                     const float* rotations, const float* cov3D_precomp,
+                     const float* viewmatrix, const float* projmatrix,
+                     const float* campos, float tan_fovx, float tan_fovy,
+                     int prefiltered, int* radii, void* geom_ws, void* image_ws,
+                     int64_t* num_rendered, int debug);
+
+/* ---- forward, phase 2: key emit + sort + ranges + render ----------------
+ * out_color[3,H,W], out_depth[1,H,W], out_opacity[1,H,W] are fully written;
+ * n_touched[P] (int32) must be zero on entry and is atomically incremented. */
+int gsr_forward_render(void* stream, int P, int width, int height,
+                       const float* background, const int* radii,
+                       const void* geom_ws, void* image_ws, void* binning_ws,
+                       uint32_t* point_list, int64_t num_rendered,
+                       float* out_color, float* out_depth, float* out_opacity,
+                       int* n_touched, int debug);
+
+/* ---- backward -----------------------------------------------------------
+ * Outputs (all optional except where noted; NULL = not wanted):
+ *   dL_dmeans2D[P,3], dL_dcolors[P,3], dL_dopacity[P,1], dL_dmeans3D[P,3],
+ *   dL_dcov3D[P,6], dL_dsh[P,M,3], dL_dscales[P,3], dL_drotations[P,4],
+ *   dL_dtau_per_gaussian[P,6] (the reference's raw output), and
+ *   dL_dtau[6] = sum over Gaussians (rho = [0:3], theta = [3:6]), reduced
+ *   in-kernel (replaces torch.sum in diff_gaussian_rasterization/__init__.py:152).
+ * Every output given is fully written (no pre-zeroing needed).
+ * dL_dout_color[3,H,W] / dL_dout_depth[1,H,W] may be NULL (treated as zero). */
+int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs,
+                 int width, int height, const float* background,
+                 const float* means3D, const float* shs,
+                 const float* colors_precomp, const float* scales,
+                 float scale_modifier, const float* rotations,
+                 const float* cov3D_precomp, const float* viewmatrix,
+                 const float* projmatrix, const float* projmatrix_raw,
+                 const float* campos, float tan_fovx, float tan_fovy,
+                 const int* radii, const void* geom_ws, const void* image_ws,
+                 const uint32_t* point_list, int64_t num_rendered,
+                 const float* dL_dout_color, const float* dL_dout_depth,
+                 void* scratch,
+                 float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                 float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                 float* dL_dscales, float* dL_drotations,
+                 float* dL_dtau_per_gaussian, float* dL_dtau, int debug);
+
+/* present[P] (uint8 0/1) = p_view.z > 0.2  (auxiliary.h:139-164). */
+int gsr_mark_visible(void* stream, int P, const float* means3D,
+                     const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present);
+
+/* mean_dist2[P] = mean squared distance to the 3 nearest other points. */
+int gsr_knn_dist2(void* stream, int P, const float* points, float* mean_dist2,
+                  void* knn_ws);
+
+/* ---- test / parity hooks --------------------------------------------------*/
+/* Stable LSD radix sort of (u64 key, u32 value) pairs on key bits
+ * [0, end_bit) -- the operation cub::DeviceRadixSort::SortPairs performs at
+ * rasterizer_impl.cu:306-311. `ws` needs gsr_binning_bytes(n) bytes. */
+int gsr_sort_pairs_u64(void* stream, int64_t n, const uint64_t* keys_in,
+                       const uint32_t* values_in, uint64_t* keys_out,
+                       uint32_t* values_out, int end_bit, void* ws);
+
+/* Pointers into the workspaces, for bit-exact checks against the reference's
+ * GeometryState / BinningState / ImageState (rasterizer_impl.h:33-62).
+ * geom record layout: see DESIGN.md "Data layout in HBM". */
+int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, const float** rec_a /*float4[P]: x,y,depth,ext_x*/,
+                         const float** rec_b /*float4[P]: conic xyz, opacity*/,
+                         const float** rec_c /*float4[P]: rgb, ext_y*/,
+                         const uint32_t** tiles_touched);
+int gsr_debug_image_views(const void* image_ws, int width, int height,
+                          const float** final_T, const uint32_t** n_contrib,
+                          const uint32_t** ranges /*uint2[tiles]*/);
+/* Sorted keys of the LAST gsr_forward_render call live in binning_ws. */
+int gsr_debug_sorted_keys(const void* binning_ws, int64_t num_rendered, int width, int height,
+                          const uint64_t** keys_sorted);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSR_B200_H_ */

@@ -1,0 +1,245 @@
+// api.cu -- the C ABI declared in include/gsr_b200.h.
+// Host-side orchestration only: argument checks, workspace carving, kernel
+// launches on the caller's stream.  See the header for which reference
+// interface each entry point replaces.
+#include <mutex>
+#include "common.cuh"
+#include "kernels.cuh"
+
+using namespace gsr;
+
+namespace {
+
+// Number of bits needed to represent n (getHigherMsb, rasterizer_impl.cu:35-50).
+int higher_msb(uint32_t n) {
+  int b = 0;
+  while (n >> b) ++b;
+  return b;
+}
+int sort_passes_for(int W, int H) {
+  const int bits = 32 + higher_msb((uint32_t)num_tiles(W, H));
+  return (bits + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+}
+
+struct HostSlot {
+  unsigned long long total;
+  int error_flag;
+};
+std::mutex g_mu;
+HostSlot* g_pinned = nullptr;
+
+int check(cudaError_t e) { return e == cudaSuccess ? GSR_OK : (int)e; }
+int debug_sync(cudaStream_t st, int debug) {
+  if (!debug) return GSR_OK;
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  return check(e);
+}
+#define GSR_TRY(expr)                 \
+  do {                                \
+    int _rc = (expr);                 \
+    if (_rc != GSR_OK) return _rc;    \
+  } while (0)
+
+}  // namespace
+
+extern "C" {
+
+const char* gsr_version(void) { return "gsr_b200 0.1 (sm_100a)"; }
+
+size_t gsr_geom_bytes(int P, int width, int height) { return carve_geom(nullptr, P, width, height, nullptr); }
+size_t gsr_image_bytes(int width, int height) { return carve_image(nullptr, width, height, nullptr); }
+size_t gsr_point_list_bytes(int64_t R) { return align_up(4 * (size_t)(R > 0 ? R : 1)); }
+size_t gsr_binning_bytes(int64_t R) { return carve_binning(nullptr, R, nullptr); }
+size_t gsr_backward_scratch_bytes(int P) { return carve_backward(nullptr, P, nullptr); }
+size_t gsr_knn_bytes(int P) { return knn_workspace_bytes(P); }
+
+int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
+                     const float* means3D, const float* shs, const float* colors_precomp,
+                     const float* opacities, const float* scales, float scale_modifier,
+                     const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                     const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy,
+                     int prefiltered, int* radii, void* geom_ws, void* image_ws, int64_t* num_rendered,
+                     int debug) {
+  if (!num_rendered) return GSR_EINVAL;
+  *num_rendered = 0;
+  if (P < 0 || width <= 0 || height <= 0) return GSR_EINVAL;
+  if (P == 0) return GSR_OK;
+  if (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !geom_ws || !image_ws) return GSR_EINVAL;
+  if (!shs && !colors_precomp) return GSR_ENOCOLOR;       // rasterizer_impl.cu:245-248
+  if (shs && !colors_precomp && (!campos || sh_coeffs < (sh_degree + 1) * (sh_degree + 1) || sh_degree > 3))
+    return GSR_EINVAL;
+  if (!cov3D_precomp && (!scales || !rotations)) return GSR_ENOCOV;
+  if (num_tiles(width, height) > 65536) return GSR_EINVAL;  // two 8-bit tile digits
+  cudaStream_t st = (cudaStream_t)stream;
+
+  GeomViews g;
+  carve_geom((char*)geom_ws, P, width, height, &g);
+  ImageViews im;
+  carve_image((char*)image_ws, width, height, &im);
+  GSR_TRY(check(cudaMemsetAsync((char*)geom_ws + g.zero_begin, 0, g.zero_end - g.zero_begin, st)));
+  GSR_TRY(check(launch_preprocess_fwd(st, P, sh_degree, sh_coeffs, means3D, colors_precomp ? nullptr : shs,
+                                      colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
+                                      viewmatrix, projmatrix, campos, width, height, tan_fovx, tan_fovy,
+                                      prefiltered, radii, g, g.hist, g.tile_diff)));
+  GSR_TRY(debug_sync(st, debug));
+  GSR_TRY(check(launch_finish_scan(st, num_pre_blocks(P), g.block_sums, g.total, (int)num_tiles(width, height),
+                                   g.tile_diff, im.ranges, g.hist, sort_passes_for(width, height))));
+  // the one host read of the forward (rasterizer_impl.cu:284)
+  HostSlot slot;
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_pinned) GSR_TRY(check(cudaHostAlloc((void**)&g_pinned, sizeof(HostSlot), cudaHostAllocDefault)));
+    GSR_TRY(check(cudaMemcpyAsync(&g_pinned->total, g.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st)));
+    GSR_TRY(check(cudaMemcpyAsync(&g_pinned->error_flag, g.error_flag, sizeof(int), cudaMemcpyDeviceToHost, st)));
+    GSR_TRY(check(cudaStreamSynchronize(st)));
+    slot = *g_pinned;
+  }
+  if (slot.error_flag) return GSR_EPREFILTER;
+  if (slot.total >= (1ull << 30)) return GSR_EOVERFLOW;
+  *num_rendered = (int64_t)slot.total;
+  return GSR_OK;
+}
+
+int gsr_forward_render(void* stream, int P, int width, int height, const float* background, const int* radii,
+                       const void* geom_ws, void* image_ws, void* binning_ws, uint32_t* point_list,
+                       int64_t num_rendered, float* out_color, float* out_depth, float* out_opacity,
+                       int* n_touched, int debug) {
+  if (P < 0 || width <= 0 || height <= 0 || num_rendered < 0) return GSR_EINVAL;
+  if (P == 0) return GSR_OK;  // reference returns its zero-filled outputs (rasterize_points.cu:85)
+  if (!background || !radii || !geom_ws || !image_ws || !out_color || !out_depth || !out_opacity || !n_touched)
+    return GSR_EINVAL;
+  if (num_rendered > 0 && (!binning_ws || !point_list)) return GSR_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  GeomViews g;
+  carve_geom((char*)geom_ws, P, width, height, &g);
+  ImageViews im;
+  carve_image((char*)image_ws, width, height, &im);
+  const int tiles_x = (width + TILE_X - 1) / TILE_X, tiles_y = (height + TILE_Y - 1) / TILE_Y;
+
+  if (num_rendered > 0) {
+    BinningViews bv;
+    carve_binning((char*)binning_ws, num_rendered, &bv);
+    GSR_TRY(check(cudaMemsetAsync((char*)binning_ws + bv.zero_begin, 0, bv.zero_end - bv.zero_begin, st)));
+    GSR_TRY(check(launch_emit_keys(st, P, g, radii, tiles_x, tiles_y, bv.keys_a, bv.vals_a)));
+    GSR_TRY(debug_sync(st, debug));
+    GSR_TRY(check(sort_pairs_u64_prehist(st, num_rendered, bv.keys_a, bv.keys_b, bv.vals_a, bv.vals_b,
+                                         sort_passes_for(width, height), g.hist, bv.tickets, bv.lookback,
+                                         point_list)));
+    GSR_TRY(debug_sync(st, debug));
+  }
+  GSR_TRY(check(launch_render_fwd(st, width, height, im, point_list, g, background, out_color, out_depth,
+                                  out_opacity, n_touched)));
+  return debug_sync(st, debug);
+}
+
+int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
+                 const float* background, const float* means3D, const float* shs, const float* colors_precomp,
+                 const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                 const float* viewmatrix, const float* projmatrix, const float* projmatrix_raw,
+                 const float* campos, float tan_fovx, float tan_fovy, const int* radii, const void* geom_ws,
+                 const void* image_ws, const uint32_t* point_list, int64_t num_rendered,
+                 const float* dL_dout_color, const float* dL_dout_depth, void* scratch, float* dL_dmeans2D,
+                 float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                 float* dL_dscales, float* dL_drotations, float* dL_dtau_per_gaussian, float* dL_dtau,
+                 int debug) {
+  if (P < 0 || width <= 0 || height <= 0 || num_rendered < 0) return GSR_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (P == 0) {
+    if (dL_dtau) GSR_TRY(check(cudaMemsetAsync(dL_dtau, 0, 6 * sizeof(float), st)));
+    return GSR_OK;
+  }
+  if (!background || !means3D || !viewmatrix || !projmatrix || !projmatrix_raw || !radii || !geom_ws ||
+      !image_ws || !scratch)
+    return GSR_EINVAL;
+  if (!cov3D_precomp && (!scales || !rotations)) return GSR_ENOCOV;
+  if (num_rendered > 0 && !point_list) return GSR_EINVAL;
+  GeomViews g;
+  carve_geom((char*)geom_ws, P, width, height, &g);
+  ImageViews im;
+  carve_image((char*)image_ws, width, height, &im);
+  BackwardViews bw;
+  carve_backward((char*)scratch, P, &bw);
+  GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, sizeof(float) * GRAD_STRIDE * (size_t)P, st)));
+  if (num_rendered > 0) {
+    GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
+                                    dL_dout_depth, bw.packed)));
+    GSR_TRY(debug_sync(st, debug));
+  }
+  const float* shs_used = colors_precomp ? nullptr : shs;
+  GSR_TRY(check(launch_preprocess_bwd(st, P, sh_degree, sh_coeffs, means3D, radii, shs_used, g.clamped, scales,
+                                      rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                                      projmatrix_raw, campos, width, height, tan_fovx, tan_fovy, bw, dL_dmeans2D,
+                                      dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+                                      dL_drotations, dL_dtau_per_gaussian, dL_dtau)));
+  return debug_sync(st, debug);
+}
+
+int gsr_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present) {
+  (void)projmatrix;  // the reference computes p_proj but only tests p_view.z (auxiliary.h:149-154)
+  if (P < 0) return GSR_EINVAL;
+  if (P == 0) return GSR_OK;
+  if (!means3D || !viewmatrix || !present) return GSR_EINVAL;
+  return check(launch_mark_visible((cudaStream_t)stream, P, means3D, viewmatrix, present));
+}
+
+int gsr_knn_dist2(void* stream, int P, const float* points, float* mean_dist2, void* knn_ws) {
+  if (P < 0) return GSR_EINVAL;
+  if (P == 0) return GSR_OK;
+  if (!points || !mean_dist2 || !knn_ws) return GSR_EINVAL;
+  return check(launch_knn((cudaStream_t)stream, P, points, mean_dist2, knn_ws));
+}
+
+int gsr_sort_pairs_u64(void* stream, int64_t n, const uint64_t* keys_in, const uint32_t* values_in,
+                       uint64_t* keys_out, uint32_t* values_out, int end_bit, void* ws) {
+  if (n < 0 || end_bit <= 0 || end_bit > 64 || n >= (1ll << 30)) return GSR_EINVAL;
+  if (n == 0) return GSR_OK;
+  if (!keys_in || !values_in || !keys_out || !values_out || !ws) return GSR_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  BinningViews bv;
+  carve_binning((char*)ws, n, &bv);
+  const int n_passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+  GSR_TRY(check(cudaMemsetAsync((char*)ws + bv.zero_begin, 0, bv.zero_end - bv.zero_begin, st)));
+  GSR_TRY(check(cudaMemcpyAsync(bv.keys_a, keys_in, 8 * (size_t)n, cudaMemcpyDeviceToDevice, st)));
+  GSR_TRY(check(cudaMemcpyAsync(bv.vals_a, values_in, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st)));
+  GSR_TRY(check(launch_digit_hist_u64(st, bv.keys_a, n, n_passes, bv.hist)));
+  GSR_TRY(check(sort_pairs_u64_prehist(st, n, bv.keys_a, bv.keys_b, bv.vals_a, bv.vals_b, n_passes, bv.hist,
+                                       bv.tickets, bv.lookback, values_out)));
+  const uint64_t* sorted = (n_passes & 1) ? bv.keys_b : bv.keys_a;
+  return check(cudaMemcpyAsync(keys_out, sorted, 8 * (size_t)n, cudaMemcpyDeviceToDevice, st));
+}
+
+int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, const float** rec_a,
+                         const float** rec_b, const float** rec_c, const uint32_t** tiles_touched) {
+  if (!geom_ws) return GSR_EINVAL;
+  GeomViews g;
+  carve_geom((char*)geom_ws, P, width, height, &g);
+  if (rec_a) *rec_a = (const float*)g.rec_a;
+  if (rec_b) *rec_b = (const float*)g.rec_b;
+  if (rec_c) *rec_c = (const float*)g.rec_c;
+  if (tiles_touched) *tiles_touched = g.tiles_touched;
+  return GSR_OK;
+}
+
+int gsr_debug_image_views(const void* image_ws, int width, int height, const float** final_T,
+                          const uint32_t** n_contrib, const uint32_t** ranges) {
+  if (!image_ws) return GSR_EINVAL;
+  ImageViews im;
+  carve_image((char*)image_ws, width, height, &im);
+  if (final_T) *final_T = im.final_T;
+  if (n_contrib) *n_contrib = im.n_contrib;
+  if (ranges) *ranges = (const uint32_t*)im.ranges;
+  return GSR_OK;
+}
+
+int gsr_debug_sorted_keys(const void* binning_ws, int64_t num_rendered, int width, int height,
+                          const uint64_t** keys_sorted) {
+  if (!binning_ws || !keys_sorted) return GSR_EINVAL;
+  BinningViews bv;
+  carve_binning((char*)binning_ws, num_rendered, &bv);
+  *keys_sorted = (sort_passes_for(width, height) & 1) ? bv.keys_b : bv.keys_a;
+  return GSR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,181 @@
+// common.cuh -- shared definitions for the sm_100a rasterizer kernels.
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <cuda_runtime.h>
+#include "../../include/gsr_b200.h"
+
+namespace gsr {
+
+constexpr int TILE_X = 16;   // binning tile: must equal the reference's BLOCK_X/BLOCK_Y
+constexpr int TILE_Y = 16;   // (config.h:15-17) or radii->tiles->keys->ranges would differ
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+
+// ---------------------------------------------------------------------------
+// Workspace carving. Every sub-array is 256-byte aligned.
+// ---------------------------------------------------------------------------
+__host__ __device__ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// Per-Gaussian geometry state ("GeometryState" of rasterizer_impl.h:33-48,
+// re-laid out as three float4 records so the renderers gather 3 x 16 B).
+//   rec_a = {mean2D.x, mean2D.y, depth(view z), cull extent x}
+//   rec_b = {conic.x, conic.y, conic.z, opacity}
+//   rec_c = {r, g, b, cull extent y}
+struct GeomViews {
+  float4* rec_a;
+  float4* rec_b;
+  float4* rec_c;
+  uint32_t* tiles_touched;   // [P]
+  uint32_t* block_sums;      // [ceil(P/256)+1] per-block tile counts -> exclusive offsets
+  uint8_t* clamped;          // [3P] SH clamp flags (forward.cu:69-71)
+  // --- small region zeroed at the start of every forward ---
+  uint32_t* hist;            // [SORT_MAX_PASSES*256] radix digit histograms -> exclusive offsets
+  int* tile_diff;            // [tiles+1] +1/-1 difference array over tile ids
+  unsigned long long* total; // [1] num_rendered
+  int* error_flag;           // [1]
+  size_t zero_begin, zero_end;
+};
+
+__host__ __device__ inline int num_pre_blocks(int P) { return (P + 255) / 256; }
+__host__ __device__ inline size_t num_tiles(int W, int H) {
+  return (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+}
+
+__host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, GeomViews* v) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
+  char* a = take(sizeof(float4) * (size_t)P);
+  char* b = take(sizeof(float4) * (size_t)P);
+  char* c = take(sizeof(float4) * (size_t)P);
+  char* t = take(sizeof(uint32_t) * (size_t)P);
+  char* s = take(sizeof(uint32_t) * (size_t)(num_pre_blocks(P) + 1));
+  char* cl = take((size_t)3 * P);
+  size_t zb = off;
+  char* h = take(sizeof(uint32_t) * 8 * 256);
+  char* td = take(sizeof(int) * (num_tiles(W, H) + 1));
+  char* tot = take(256);
+  size_t ze = off;
+  if (v) {
+    v->rec_a = (float4*)a; v->rec_b = (float4*)b; v->rec_c = (float4*)c;
+    v->tiles_touched = (uint32_t*)t; v->block_sums = (uint32_t*)s; v->clamped = (uint8_t*)cl;
+    v->hist = (uint32_t*)h; v->tile_diff = (int*)td;
+    v->total = (unsigned long long*)tot; v->error_flag = (int*)(tot ? tot + 64 : nullptr);
+    v->zero_begin = zb; v->zero_end = ze;
+  }
+  return off;
+}
+
+// Per-pixel + per-tile state ("ImageState", rasterizer_impl.h:50-57).
+struct ImageViews {
+  float* final_T;        // [H*W]
+  uint32_t* n_contrib;   // [H*W]
+  uint2* ranges;         // [tiles]
+};
+__host__ __device__ inline size_t carve_image(char* base, int W, int H, ImageViews* v) {
+  size_t off = 0;
+  size_t N = (size_t)W * H;
+  size_t tiles = num_tiles(W, H);
+  auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
+  char* a = take(4 * N); char* b = take(4 * N); char* c = take(8 * tiles);
+  if (v) { v->final_T = (float*)a; v->n_contrib = (uint32_t*)b; v->ranges = (uint2*)c; }
+  return off;
+}
+
+// Radix-sort workspace ("BinningState", rasterizer_impl.h:59-69, minus the
+// final point_list which the caller owns).
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_MAX_PASSES = 8;
+constexpr int SORT_TILE = 256 * 16;  // keys per thread block per pass
+
+struct BinningViews {
+  uint64_t* keys_a;      // [R]
+  uint64_t* keys_b;      // [R]
+  uint32_t* vals_a;      // [R]
+  uint32_t* vals_b;      // [R]
+  uint32_t* hist;        // [SORT_MAX_PASSES * SORT_RADIX] global digit histograms
+  uint32_t* tickets;     // [SORT_MAX_PASSES] dynamic block ids
+  uint32_t* lookback;    // [SORT_MAX_PASSES * nblocks * SORT_RADIX] decoupled look-back status
+  size_t zero_begin;     // byte range [zero_begin, zero_end) must be zeroed before a sort
+  size_t zero_end;
+};
+__host__ __device__ inline size_t sort_blocks(int64_t R) { return (size_t)((R + SORT_TILE - 1) / SORT_TILE); }
+__host__ __device__ inline size_t carve_binning(char* base, int64_t R, BinningViews* v) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
+  size_t n = (size_t)(R > 0 ? R : 1);
+  char* ka = take(8 * n); char* kb = take(8 * n); char* va = take(4 * n); char* vb = take(4 * n);
+  size_t zb = off;
+  char* h = take(4 * (size_t)SORT_MAX_PASSES * SORT_RADIX);
+  char* t = take(4 * (size_t)SORT_MAX_PASSES);
+  char* lb = take(4 * (size_t)SORT_MAX_PASSES * sort_blocks(n) * SORT_RADIX);
+  size_t ze = off;
+  if (v) {
+    v->keys_a = (uint64_t*)ka; v->keys_b = (uint64_t*)kb; v->vals_a = (uint32_t*)va; v->vals_b = (uint32_t*)vb;
+    v->hist = (uint32_t*)h; v->tickets = (uint32_t*)t; v->lookback = (uint32_t*)lb;
+    v->zero_begin = zb; v->zero_end = ze;
+  }
+  return off;
+}
+
+// Packed per-Gaussian partial gradients accumulated by the backward renderer
+// (one 48-byte record so the 10 atomics of a warp hit 1-2 sectors):
+//   [0]=dL/dmean2D.x [1]=dL/dmean2D.y [2]=dL/dconic.x [3]=dL/dconic.y
+//   [4]=dL/dconic.w  [5]=dL/dopacity  [6..8]=dL/dcolor rgb [9]=dL/ddepth
+constexpr int GRAD_STRIDE = 12;
+struct BackwardViews {
+  float* packed;        // [P * GRAD_STRIDE]
+  double* tau_partial;  // [nblocks * 6]
+};
+__host__ __device__ inline size_t carve_backward(char* base, int P, BackwardViews* v) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
+  char* a = take(sizeof(float) * GRAD_STRIDE * (size_t)P);
+  char* b = take(sizeof(double) * 6 * (size_t)num_pre_blocks(P));
+  if (v) { v->packed = (float*)a; v->tau_partial = (double*)b; }
+  return off;
+}
+
+// ---------------------------------------------------------------------------
+// Explicitly rounded fp32 arithmetic.  nvcc never re-contracts these
+// intrinsics, so the quantities that feed integer outputs (radii, tile rects,
+// depth key bits, the n_touched threshold) follow exactly the operation
+// sequence the reference kernels execute (its FMA contraction was read from
+// the PTX nvcc 12.9 generates for forward.cu; see DESIGN.md "Bit-exactness").
+// ---------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float ffma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float frcp(float a) { return __frcp_rn(a); }
+__device__ __forceinline__ float fsqrt(float a) { return __fsqrt_rn(a); }
+
+// a0*b0 + a1*b1 + a2*b2 the way nvcc contracts a left-associated sum of
+// products: fma(a2,b2, fma(a0,b0, a1*b1)).
+__device__ __forceinline__ float dot3c(float a0, float b0, float a1, float b1, float a2, float b2) {
+  return ffma(a2, b2, ffma(a0, b0, fmul(a1, b1)));
+}
+// matrix[r] * x + matrix[r+4] * y + matrix[r+8] * z + matrix[r+12]  (auxiliary.h:58-77)
+__device__ __forceinline__ float affine_row(const float* m, int r, float x, float y, float z) {
+  return fadd(m[r + 12], dot3c(x, m[r], y, m[r + 4], z, m[r + 8]));
+}
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
+
+#define GSR_DEVINL __device__ __forceinline__
+#endif
+
+// Camera constants passed by value (kernel parameter -> constant bank).
+struct CameraParams {
+  float view[16];      // W2C^T, flat index 4*col+row  
+  float proj[16];      // (P*W2C)^T
+  float campos[3];
+  float tan_fovx, tan_fovy;
+  float focal_x, focal_y;
+  int W, H;
+  int tiles_x, tiles_y;
+};
+
+}  // namespace gsr

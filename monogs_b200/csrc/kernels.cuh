@@ -1,0 +1,59 @@
+// kernels.cuh -- host-side launchers of the sm_100a kernels (one per .cu file).
+#pragma once
+#include "common.cuh"
+
+namespace gsr {
+
+// preprocess.cu
+cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const float* means3D, const float* shs,
+                                  const float* colors_precomp, const float* opacities, const float* scales,
+                                  float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                                  const float* viewmatrix, const float* projmatrix, const float* campos, int W,
+                                  int H, float tan_fovx, float tan_fovy, int prefiltered, int* radii,
+                                  const GeomViews& g, uint32_t* depth_hist, int* tile_diff);
+cudaError_t launch_finish_scan(cudaStream_t st, int n_blocks, uint32_t* block_sums, unsigned long long* total,
+                               int n_tiles, const int* tile_diff, uint2* ranges, uint32_t* hist, int n_passes);
+cudaError_t launch_mark_visible(cudaStream_t st, int P, const float* means3D, const float* viewmatrix,
+                                uint8_t* present);
+
+// binning.cu
+cudaError_t launch_emit_keys(cudaStream_t st, int P, const GeomViews& g, const int* radii, int tiles_x,
+                             int tiles_y, uint64_t* keys, uint32_t* vals);
+
+// radix_sort.cu
+cudaError_t sort_pairs_u64_prehist(cudaStream_t st, long long n, uint64_t* keys_a, uint64_t* keys_b,
+                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes,
+                                   const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
+                                   uint32_t* final_vals);
+cudaError_t sort_pairs_u32_prehist(cudaStream_t st, long long n, uint32_t* keys_a, uint32_t* keys_b,
+                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes,
+                                   const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
+                                   uint32_t* final_vals);
+cudaError_t launch_digit_hist_u64(cudaStream_t st, const uint64_t* keys, long long n, int n_passes, uint32_t* hist);
+cudaError_t launch_digit_hist_u32(cudaStream_t st, const uint32_t* keys, long long n, int n_passes, uint32_t* hist);
+
+// render_fwd.cu
+cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
+                              const GeomViews& g, const float* bg, float* out_color, float* out_depth,
+                              float* out_opacity, int* n_touched);
+
+// render_bwd.cu
+cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
+                              const GeomViews& g, const float* bg, const float* dL_dpix,
+                              const float* dL_dpix_depth, float* packed);
+
+// preprocess_bwd.cu
+cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const float* means3D, const int* radii,
+                                  const float* shs, const uint8_t* clamped, const float* scales,
+                                  const float* rotations, float scale_modifier, const float* cov3D_precomp,
+                                  const float* viewmatrix, const float* projmatrix, const float* projmatrix_raw,
+                                  const float* campos, int W, int H, float tan_fovx, float tan_fovy,
+                                  const BackwardViews& bw, float* dL_dmeans2D, float* dL_dcolors,
+                                  float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                                  float* dL_dscales, float* dL_drots, float* dL_dtau_pg, float* dL_dtau);
+
+// knn.cu
+size_t knn_workspace_bytes(int P);
+cudaError_t launch_knn(cudaStream_t st, int P, const float* points, float* mean_dist2, void* ws);
+
+}  // namespace gsr

@@ -1,0 +1,455 @@
+// preprocess.cu -- forward per-Gaussian stage (K1, K2, K3 of SURVEY 2.2).
+//
+// Replaces preprocessCUDA (forward.cu:157-258), checkFrustum
+// (rasterizer_impl.cu:54-66) and the cub::DeviceScan::InclusiveSum call
+// (rasterizer_impl.cu:280).  One thread per Gaussian; inputs are staged
+// through shared memory so every global load is a fully coalesced 128-bit
+// access, outputs are three float4 records (SoA of float4).
+//
+// Besides the reference's outputs this kernel derives, at per-GAUSSIAN cost,
+// everything the instance-level stages need:
+//   * depth-digit histograms for the first four radix passes (weighted by the
+//     number of tiles the Gaussian touches),
+//   * a difference array over tile ids (+1 at the start of each covered tile
+//     row, -1 after its end) whose prefix sum is the per-tile instance count:
+//     that gives the tile ranges (identifyTileRanges, rasterizer_impl.cu:116-138)
+//     and the tile-digit histograms without ever reading the instance keys.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace gsr {
+
+// SH basis constants (auxiliary.h:22-39).
+__device__ const float kC0 = 0.28209479177387814f;
+__device__ const float kC1 = 0.4886025119029199f;
+__device__ const float kC2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                 -1.0925484305920792f, 0.5462742152960396f};
+__device__ const float kC3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                 0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
+                                 -0.5900435899266435f};
+
+// SH -> RGB (forward.cu:22-73). Returns unclamped+0.5 colour; caller clamps.
+GSR_DEVINL float3 sh_to_rgb(int deg, int M, const float* __restrict__ sh /* [M][3] of this Gaussian */,
+                            float3 pos, float3 campos) {
+  float3 dir = make_float3(pos.x - campos.x, pos.y - campos.y, pos.z - campos.z);
+  // glm: dir / length(dir) is a true division; keep it one.
+  float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+  float x = dir.x / len, y = dir.y / len, z = dir.z / len;
+  float3 r;
+  auto S = [&](int k, int c) { return sh[3 * k + c]; };
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float v = kC0 * S(0, c);
+    if (deg > 0) {
+      v = v - kC1 * y * S(1, c) + kC1 * z * S(2, c) - kC1 * x * S(3, c);
+      if (deg > 1) {
+        float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        v = v + kC2[0] * xy * S(4, c) + kC2[1] * yz * S(5, c) + kC2[2] * (2.0f * zz - xx - yy) * S(6, c) +
+            kC2[3] * xz * S(7, c) + kC2[4] * (xx - yy) * S(8, c);
+        if (deg > 2) {
+          v = v + kC3[0] * y * (3.0f * xx - yy) * S(9, c) + kC3[1] * xy * z * S(10, c) +
+              kC3[2] * y * (4.0f * zz - xx - yy) * S(11, c) +
+              kC3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * S(12, c) +
+              kC3[4] * x * (4.0f * zz - xx - yy) * S(13, c) + kC3[5] * z * (xx - yy) * S(14, c) +
+              kC3[6] * x * (xx - 3.0f * yy) * S(15, c);
+        }
+      }
+    }
+    v += 0.5f;
+    (&r.x)[c] = v;
+  }
+  return r;
+}
+
+// 3D covariance from scale + quaternion, operation-for-operation what nvcc
+// emits for computeCov3D (forward.cu:120-154).  q = (r,x,y,z), NOT re-normalised.
+GSR_DEVINL void cov3d_from_scale_rot(float3 s_in, float mod, float4 q, float* cov) {
+  const float sx = fmul(mod, s_in.x), sy = fmul(mod, s_in.y), sz = fmul(mod, s_in.z);
+  const float r = q.x, x = q.y, y = q.z, z = q.w;
+  const float yy = fmul(y, y), zz = fmul(z, z);
+  const float xy = fmul(x, y), rz = fmul(r, z), xz = fmul(x, z), ry = fmul(r, y);
+  const float yz = fmul(y, z), rx = fmul(r, x);
+  const float yy_zz = fadd(yy, zz);
+  const float xx_zz = ffma(x, x, zz);
+  const float xx_yy = ffma(x, x, yy);
+  auto twice = [](float v) { return fadd(v, v); };
+  const float R00 = fsub(1.0f, twice(yy_zz));
+  const float a01 = twice(fsub(xy, rz));
+  const float a02 = twice(fadd(ry, xz));
+  const float a10 = twice(fadd(xy, rz));
+  const float R11 = fsub(1.0f, twice(xx_zz));
+  const float a12 = twice(fsub(yz, rx));
+  const float a20 = twice(fsub(xz, ry));
+  const float a21 = twice(fadd(rx, yz));
+  const float R22 = fsub(1.0f, twice(xx_yy));
+  // M = S * R (glm column-major); the products with the zero entries of S
+  // vanish for finite inputs.
+  const float m0 = fmul(sx, R00), m1 = fmul(sy, a01), m2 = fmul(sz, a02);
+  const float m3 = fmul(sx, a10), m4 = fmul(sy, R11), m5 = fmul(sz, a12);
+  const float m6 = fmul(sx, a20), m7 = fmul(sy, a21), m8 = fmul(sz, R22);
+  cov[0] = ffma(m2, m2, ffma(m0, m0, fmul(m1, m1)));
+  cov[1] = ffma(m5, m2, ffma(m3, m0, fmul(m4, m1)));
+  cov[2] = ffma(m8, m2, ffma(m6, m0, fmul(m7, m1)));
+  cov[3] = ffma(m5, m5, ffma(m3, m3, fmul(m4, m4)));
+  cov[4] = ffma(m8, m5, ffma(m6, m3, fmul(m7, m4)));
+  cov[5] = ffma(m8, m8, ffma(m6, m6, fmul(m7, m7)));
+}
+
+// EWA projection of the 3D covariance (computeCov2D, forward.cu:76-115),
+// same operation order as the reference's generated code. v = viewmatrix.
+GSR_DEVINL float3 cov2d_project(float tx, float ty, float tz, float focal_x, float focal_y, float tan_fovx,
+                                float tan_fovy, const float* cov, const float* v) {
+  const float limx = fmul(tan_fovx, 1.3f), limy = fmul(tan_fovy, 1.3f);
+  const float txtz = fdiv(tx, tz), tytz = fdiv(ty, tz);
+  const float cx = fminf(limx, fmaxf(-limx, txtz));
+  const float cy = fminf(limy, fmaxf(-limy, tytz));
+  const float ntz = -tz;
+  const float tz2 = fmul(tz, tz);
+  const float J00 = fdiv(focal_x, tz);
+  const float J02 = fdiv(fmul(focal_x, fmul(cx, ntz)), tz2);
+  const float J11 = fdiv(focal_y, tz);
+  const float J12 = fdiv(fmul(focal_y, fmul(cy, ntz)), tz2);
+  const float T00 = ffma(v[2], J02, fmul(v[0], J00));
+  const float T01 = ffma(v[6], J02, fmul(v[4], J00));
+  const float T02 = ffma(J02, v[10], fmul(v[8], J00));
+  const float T10 = ffma(v[2], J12, fmul(J11, v[1]));
+  const float T11 = ffma(v[6], J12, fmul(J11, v[5]));
+  const float T12 = ffma(J12, v[10], fmul(J11, v[9]));
+  const float A0 = ffma(T02, cov[2], ffma(T00, cov[0], fmul(T01, cov[1])));
+  const float B0 = ffma(T12, cov[2], ffma(T10, cov[0], fmul(T11, cov[1])));
+  const float A1 = ffma(T02, cov[4], ffma(T00, cov[1], fmul(T01, cov[3])));
+  const float B1 = ffma(T12, cov[4], ffma(T10, cov[1], fmul(T11, cov[3])));
+  const float A2 = ffma(T02, cov[5], ffma(T00, cov[2], fmul(T01, cov[4])));
+  const float B2 = ffma(T12, cov[5], ffma(T10, cov[2], fmul(T11, cov[4])));
+  const float c00 = ffma(T02, A2, ffma(T00, A0, fmul(T01, A1)));
+  const float c01 = ffma(T02, B2, ffma(T00, B0, fmul(T01, B1)));
+  const float c11 = ffma(T12, B2, ffma(T10, B0, fmul(T11, B1)));
+  return make_float3(fadd(c00, 0.3f), c01, fadd(c11, 0.3f));
+}
+
+// ndc2Pix (auxiliary.h:41-44): evaluated in double because of the 1.0 / 0.5
+// literals; nvcc contracts (v+1)*S-1 into one double fma.
+GSR_DEVINL float ndc_to_pix(float v, int S) {
+  double t = __fma_rn(__dadd_rn((double)v, 1.0), (double)S, -1.0);
+  return (float)__dmul_rn(t, 0.5);
+}
+
+// getRect (auxiliary.h:46-56).
+GSR_DEVINL void tile_rect(float px, float py, int radius, int tiles_x, int tiles_y, uint2& rmin, uint2& rmax) {
+  const float r = (float)radius;
+  const float inv = 0.0625f;  // division by BLOCK_X = 16 is exact as a multiply
+  int x0 = (int)fmul(fsub(px, r), inv);
+  int y0 = (int)fmul(fsub(py, r), inv);
+  int x1 = (int)fmul(fadd(fadd(fadd(px, r), 16.0f), -1.0f), inv);
+  int y1 = (int)fmul(fadd(fadd(fadd(py, r), 16.0f), -1.0f), inv);
+  rmin.x = min((unsigned)tiles_x, (unsigned)max(0, x0));
+  rmin.y = min((unsigned)tiles_y, (unsigned)max(0, y0));
+  rmax.x = min((unsigned)tiles_x, (unsigned)max(0, x1));
+  rmax.y = min((unsigned)tiles_y, (unsigned)max(0, y1));
+}
+
+constexpr int PRE_THREADS = 256;
+
+// Coalesced load of `n_floats` consecutive floats per thread-block row into smem.
+template <int PER>
+GSR_DEVINL void stage_block(const float* __restrict__ g, float* s, long long base_elem, long long total_elem) {
+  // block covers PRE_THREADS * PER floats starting at base_elem
+  for (int i = threadIdx.x; i < PRE_THREADS * PER; i += PRE_THREADS) {
+    long long e = base_elem + i;
+    s[i] = (e < total_elem) ? __ldg(g + e) : 0.0f;
+  }
+}
+
+__global__ void __launch_bounds__(PRE_THREADS)
+preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ shs,
+                      const float* __restrict__ colors_precomp, const float* __restrict__ opacities,
+                      const float* __restrict__ scales, float scale_modifier,
+                      const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
+                      const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
+                      const float* __restrict__ campos, int W, int H, float tan_fovx, float tan_fovy,
+                      float focal_x, float focal_y, int tiles_x, int tiles_y, int prefiltered,
+                      int* __restrict__ radii, GeomViews g, uint32_t* __restrict__ depth_hist /*[4][256]*/,
+                      int* __restrict__ tile_diff /*[tiles+1]*/) {
+  __shared__ float s_mean[PRE_THREADS * 3];
+  __shared__ float s_scale[PRE_THREADS * 3];
+  __shared__ float s_rot[PRE_THREADS * 4];
+  __shared__ float s_cam[36];
+  __shared__ uint32_t s_hist[4 * 256];
+  __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
+
+  const int tid = threadIdx.x;
+  const long long blk_base = (long long)blockIdx.x * PRE_THREADS;
+  const int idx = (int)(blk_base + tid);
+
+  if (tid < 16) s_cam[tid] = viewmatrix[tid];
+  else if (tid < 32) s_cam[tid] = projmatrix[tid - 16];
+  else if (tid < 35) s_cam[tid] = campos ? campos[tid - 32] : 0.0f;
+  for (int i = tid; i < 4 * 256; i += PRE_THREADS) s_hist[i] = 0;
+  stage_block<3>(means3D, s_mean, blk_base * 3, (long long)P * 3);
+  if (cov3D_precomp == nullptr) {
+    stage_block<3>(scales, s_scale, blk_base * 3, (long long)P * 3);
+    stage_block<4>(rotations, s_rot, blk_base * 4, (long long)P * 4);
+  }
+  __syncthreads();
+
+  uint32_t my_tiles = 0;
+  if (idx < P) {
+    const float* view = s_cam;
+    const float* proj = s_cam + 16;
+    const float px = s_mean[3 * tid], py = s_mean[3 * tid + 1], pz = s_mean[3 * tid + 2];
+    int my_radius_i = 0;
+    float4 ra = make_float4(0.f, 0.f, 0.f, -1e30f), rb = make_float4(0.f, 0.f, 0.f, 0.f),
+           rc = make_float4(0.f, 0.f, 0.f, -1e30f);
+
+    // near culling (in_frustum, auxiliary.h:139-164): p_view.z <= 0.2 -> invisible
+    const float depth = affine_row(view, 2, px, py, pz);
+    bool alive = !(depth <= 0.2f);  // NaN depth stays alive, like the reference test
+    if (!alive && prefiltered) atomicExch(g.error_flag, 1);
+
+    if (alive) {
+      const float hx = affine_row(proj, 0, px, py, pz);
+      const float hy = affine_row(proj, 1, px, py, pz);
+      const float hw = affine_row(proj, 3, px, py, pz);
+      const float p_w = frcp(fadd(hw, 0.0000001f));
+      const float projx = fmul(hx, p_w), projy = fmul(hy, p_w);
+
+      float cov[6];
+      if (cov3D_precomp != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) cov[k] = __ldg(cov3D_precomp + (size_t)idx * 6 + k);
+      } else {
+        cov3d_from_scale_rot(make_float3(s_scale[3 * tid], s_scale[3 * tid + 1], s_scale[3 * tid + 2]),
+                             scale_modifier,
+                             make_float4(s_rot[4 * tid], s_rot[4 * tid + 1], s_rot[4 * tid + 2], s_rot[4 * tid + 3]),
+                             cov);
+      }
+      const float tx = affine_row(view, 0, px, py, pz);
+      const float ty = affine_row(view, 1, px, py, pz);
+      const float3 c2 = cov2d_project(tx, ty, depth, focal_x, focal_y, tan_fovx, tan_fovy, cov, view);
+
+      const float det = fsub(fmul(c2.x, c2.z), fmul(c2.y, c2.y));
+      if (det == 0.0f) alive = false;
+      if (alive) {
+        const float det_inv = frcp(det);
+        const float conx = fmul(c2.z, det_inv), cony = fmul(det_inv, -c2.y), conz = fmul(c2.x, det_inv);
+        const float mid = fmul(fadd(c2.x, c2.z), 0.5f);
+        const float sq = fsqrt(fmaxf(fsub(fmul(mid, mid), det), 0.1f));
+        const float lam = fmaxf(fadd(mid, sq), fsub(mid, sq));
+        const float rad_f = ceilf(fmul(fsqrt(lam), 3.0f));
+        my_radius_i = (int)rad_f;
+        const float pix_x = ndc_to_pix(projx, W), pix_y = ndc_to_pix(projy, H);
+        uint2 rmin, rmax;
+        tile_rect(pix_x, pix_y, my_radius_i, tiles_x, tiles_y, rmin, rmax);
+        my_tiles = (rmax.y - rmin.y) * (rmax.x - rmin.x);
+        if (my_tiles == 0) {
+          alive = false;
+          my_radius_i = 0;
+        } else {
+          const float opac = __ldg(opacities + idx);
+          // Conservative per-axis reach of alpha >= 1/255 (see DESIGN.md "culling"):
+          // q(d) <= 2*ln(255*o); inflated so fp32 rounding in `power` can never
+          // make a pixel outside the box pass the reference's alpha test.
+          const float tau2 = 2.0f * logf(255.0f * opac) + 1.0f;
+          float ex = -1e30f, ey = -1e30f;
+          if (tau2 > 0.0f) {
+            ex = sqrtf(tau2 * c2.x) * 1.001f + 0.01f;
+            ey = sqrtf(tau2 * c2.z) * 1.001f + 0.01f;
+          } else if (!(tau2 <= 0.0f)) {  // NaN opacity: never cull
+            ex = ey = 1e30f;
+          }
+          float3 rgb;
+          if (colors_precomp != nullptr) {
+            rgb = make_float3(__ldg(colors_precomp + (size_t)idx * 3), __ldg(colors_precomp + (size_t)idx * 3 + 1),
+                              __ldg(colors_precomp + (size_t)idx * 3 + 2));
+          } else {
+            rgb = sh_to_rgb(D, M, shs + (size_t)idx * M * 3, make_float3(px, py, pz),
+                            make_float3(s_cam[32], s_cam[33], s_cam[34]));
+            g.clamped[3 * (size_t)idx + 0] = rgb.x < 0.f;
+            g.clamped[3 * (size_t)idx + 1] = rgb.y < 0.f;
+            g.clamped[3 * (size_t)idx + 2] = rgb.z < 0.f;
+            rgb.x = fmaxf(rgb.x, 0.f); rgb.y = fmaxf(rgb.y, 0.f); rgb.z = fmaxf(rgb.z, 0.f);
+          }
+          ra = make_float4(pix_x, pix_y, depth, ex);
+          rb = make_float4(conx, cony, conz, opac);
+          rc = make_float4(rgb.x, rgb.y, rgb.z, ey);
+
+          // depth-digit histograms, weighted by instance count
+          const uint32_t db = __float_as_uint(depth);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) atomicAdd(&s_hist[k * 256 + ((db >> (8 * k)) & 255u)], my_tiles);
+          // tile-id difference array: each covered tile row is one id interval
+          for (unsigned y = rmin.y; y < rmax.y; ++y) {
+            atomicAdd(&tile_diff[y * tiles_x + rmin.x], 1);
+            atomicAdd(&tile_diff[y * tiles_x + rmax.x], -1);
+          }
+        }
+      }
+    }
+    radii[idx] = my_radius_i;
+    g.tiles_touched[idx] = my_tiles;
+    g.rec_a[idx] = ra;
+    g.rec_b[idx] = rb;
+    g.rec_c[idx] = rc;
+  }
+
+  // block sum of tile counts (first level of the offset scan)
+  uint32_t v = my_tiles;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((tid & 31) == 0) s_warp_sum[tid >> 5] = v;
+  __syncthreads();
+  if (tid == 0) {
+    uint32_t s = 0;
+#pragma unroll
+    for (int w = 0; w < PRE_THREADS / 32; ++w) s += s_warp_sum[w];
+    g.block_sums[blockIdx.x] = s;
+  }
+  for (int i = tid; i < 4 * 256; i += PRE_THREADS) {
+    uint32_t c = s_hist[i];
+    if (c) atomicAdd(&depth_hist[i], c);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Single-block finishing scan: (1) block_sums -> exclusive offsets + total,
+// (2) tile_diff -> per-tile counts -> tile ranges + tile-digit histograms,
+// (3) every pass' digit histogram -> exclusive digit offsets.
+// ---------------------------------------------------------------------------
+constexpr int SCAN_THREADS = 1024;
+
+GSR_DEVINL uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp, uint32_t& block_total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  __syncthreads();
+  if (lane == 31) s_warp[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t x = s_warp[lane];
+    uint32_t xi = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, xi, o);
+      if (lane >= o) xi += t;
+    }
+    s_warp[lane] = xi - x;
+    if (lane == 31) s_warp[32] = xi;
+  }
+  __syncthreads();
+  block_total = s_warp[32];
+  return s_warp[w] + inc - v;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+finish_scan_kernel(int n_blocks, uint32_t* __restrict__ block_sums, unsigned long long* __restrict__ total,
+                   int n_tiles, const int* __restrict__ tile_diff, uint2* __restrict__ ranges,
+                   uint32_t* __restrict__ hist /*[passes][256]*/, int n_passes) {
+  __shared__ uint32_t s_warp[33];
+  __shared__ uint32_t s_thist[2 * 256];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 512; i += SCAN_THREADS) s_thist[i] = 0;
+
+  // (1) offsets of the preprocess blocks
+  unsigned long long carry = 0;
+  for (int base = 0; base < n_blocks; base += SCAN_THREADS) {
+    int i = base + tid;
+    uint32_t v = i < n_blocks ? block_sums[i] : 0;
+    uint32_t tot;
+    uint32_t ex = block_exclusive_scan_1024(v, s_warp, tot);
+    if (i < n_blocks) block_sums[i] = (uint32_t)(carry + ex);
+    carry += tot;
+    __syncthreads();
+  }
+  if (tid == 0) { *total = carry; block_sums[n_blocks] = (uint32_t)carry; }
+
+  // (2) tile counts -> ranges, tile-digit histograms (passes 4 and 5)
+  unsigned long long tcarry = 0;
+  uint32_t dcarry = 0;  // modular arithmetic: partial sums of the +1/-1 array may dip below 0
+  for (int base = 0; base < n_tiles; base += SCAN_THREADS) {
+    int i = base + tid;
+    int d = i < n_tiles ? tile_diff[i] : 0;
+    // inclusive scan of the difference array = instances in tile i
+    uint32_t tot;
+    uint32_t exd = block_exclusive_scan_1024((uint32_t)d, s_warp, tot);
+    uint32_t cnt = dcarry + exd + (uint32_t)d;
+    __syncthreads();
+    uint32_t tot2;
+    uint32_t exc = block_exclusive_scan_1024(i < n_tiles ? cnt : 0u, s_warp, tot2);
+    if (i < n_tiles) {
+      uint32_t start = (uint32_t)(tcarry + exc);
+      ranges[i] = cnt ? make_uint2(start, start + cnt) : make_uint2(0u, 0u);
+      if (cnt) {
+        atomicAdd(&s_thist[i & 255], cnt);
+        atomicAdd(&s_thist[256 + ((i >> 8) & 255)], cnt);
+      }
+    }
+    dcarry += tot;
+    tcarry += tot2;
+    __syncthreads();
+  }
+  __syncthreads();
+  if (n_passes > 4) for (int i = tid; i < 256; i += SCAN_THREADS) hist[4 * 256 + i] = s_thist[i];
+  if (n_passes > 5) for (int i = tid; i < 256; i += SCAN_THREADS) hist[5 * 256 + i] = s_thist[256 + i];
+  __syncthreads();
+
+  // (3) exclusive digit offsets, one warp per pass
+  const int w = tid >> 5, lane = tid & 31;
+  if (w < n_passes) {
+    uint32_t run = 0;
+    for (int c = 0; c < 8; ++c) {
+      uint32_t v = hist[w * 256 + c * 32 + lane];
+      uint32_t inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+      }
+      hist[w * 256 + c * 32 + lane] = run + inc - v;
+      run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+  }
+}
+
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ viewmatrix,
+                                    uint8_t* __restrict__ present) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  float x = means3D[3 * (size_t)idx], y = means3D[3 * (size_t)idx + 1], z = means3D[3 * (size_t)idx + 2];
+  present[idx] = !(affine_row(viewmatrix, 2, x, y, z) <= 0.2f);
+}
+
+// ---------------------------------------------------------------------------
+cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const float* means3D, const float* shs,
+                                  const float* colors_precomp, const float* opacities, const float* scales,
+                                  float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                                  const float* viewmatrix, const float* projmatrix, const float* campos, int W,
+                                  int H, float tan_fovx, float tan_fovy, int prefiltered, int* radii,
+                                  const GeomViews& g, uint32_t* depth_hist, int* tile_diff) {
+  const float focal_y = H / (2.0f * tan_fovy);
+  const float focal_x = W / (2.0f * tan_fovx);
+  const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
+  preprocess_fwd_kernel<<<num_pre_blocks(P), PRE_THREADS, 0, st>>>(
+      P, D, M, means3D, shs, colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
+      viewmatrix, projmatrix, campos, W, H, tan_fovx, tan_fovy, focal_x, focal_y, tiles_x, tiles_y, prefiltered,
+      radii, g, depth_hist, tile_diff);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_finish_scan(cudaStream_t st, int n_blocks, uint32_t* block_sums, unsigned long long* total,
+                               int n_tiles, const int* tile_diff, uint2* ranges, uint32_t* hist, int n_passes) {
+  finish_scan_kernel<<<1, SCAN_THREADS, 0, st>>>(n_blocks, block_sums, total, n_tiles, tile_diff, ranges, hist,
+                                                 n_passes);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_mark_visible(cudaStream_t st, int P, const float* means3D, const float* viewmatrix,
+                                uint8_t* present) {
+  mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means3D, viewmatrix, present);
+  return cudaGetLastError();
+}
+
+}  // namespace gsr

@@ -1,0 +1,268 @@
+// radix_sort.cu -- stable LSD radix sort of (key, u32 value) pairs, 8-bit digits,
+// one kernel per pass with decoupled look-back ("onesweep"), hand-written for
+// sm_100a.  Replaces cub::DeviceRadixSort::SortPairs at
+// rasterizer_impl.cu:306-311 (u64 tile|depth keys) and simple_knn.cu:210-213
+// (u32 Morton keys).
+//
+// Per pass, per 4096-key tile (256 threads x 16 keys, warp-striped so that a
+// warp owns 512 consecutive keys and stability follows from lane/item order):
+//   1. rank keys inside the warp with match.any on the digit + per-warp digit
+//      counters in shared memory;
+//   2. thread d combines the 8 warp counters of digit d, publishes the tile's
+//      count for d, and walks back over preceding tiles' published counts
+//      (flagged 32-bit words: bits 31..30 = state, 29..0 = count);
+//   3. keys and values are scattered into shared memory in tile-sorted order
+//      and written out with one coalesced run per digit.
+// The digit histograms needed up front are NOT computed from the keys for the
+// rasterizer path: preprocess derives them per Gaussian (see preprocess.cu).
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace gsr {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr uint32_t FLAG_LOCAL = 1u << 30;
+constexpr uint32_t FLAG_INCL = 2u << 30;
+constexpr uint32_t FLAG_MASK = 3u << 30;
+constexpr uint32_t VALUE_MASK = ~FLAG_MASK;
+
+template <typename KeyT>
+struct RsSmem {
+  KeyT keys[SORT_TILE];
+  uint32_t vals[SORT_TILE];
+  uint32_t warp_hist[RS_WARPS][SORT_RADIX];
+  uint32_t bin_start[SORT_RADIX];   // exclusive digit prefix inside the tile
+  uint32_t global_base[SORT_RADIX]; // global index of tile-position 0 of each digit (mod 2^32)
+  uint32_t warp_tot[RS_WARPS];
+  uint32_t block_id;
+};
+
+GSR_DEVINL uint32_t ld_volatile_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+GSR_DEVINL void st_volatile_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS)
+onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
+                     const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, long long n,
+                     int shift, const uint32_t* __restrict__ digit_offsets /*[256] exclusive*/,
+                     uint32_t* __restrict__ ticket, uint32_t* __restrict__ lookback /*[nblocks][256]*/) {
+  extern __shared__ __align__(16) unsigned char rs_smem_raw[];
+  RsSmem<KeyT>& sm = *reinterpret_cast<RsSmem<KeyT>*>(rs_smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+
+  if (tid == 0) sm.block_id = atomicAdd(ticket, 1u);
+#pragma unroll
+  for (int i = tid; i < RS_WARPS * SORT_RADIX; i += RS_THREADS) (&sm.warp_hist[0][0])[i] = 0;
+  __syncthreads();
+  const uint32_t bid = sm.block_id;
+  const long long tile_base = (long long)bid * SORT_TILE;
+  const int tile_n = (int)min((long long)SORT_TILE, n - tile_base);
+
+  // ---- load (warp-striped) ----
+  KeyT key[RS_ITEMS];
+  uint32_t val[RS_ITEMS];
+  uint32_t rank[RS_ITEMS];
+  const int wbase = w * 32 * RS_ITEMS;
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    const int t = wbase + i * 32 + lane;
+    if (t < tile_n) {
+      key[i] = keys_in[tile_base + t];
+      val[i] = vals_in[tile_base + t];
+    } else {
+      key[i] = ~KeyT(0);
+      val[i] = 0;
+    }
+  }
+
+  // ---- rank inside the warp ----
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    const int t = wbase + i * 32 + lane;
+    const uint32_t d = (t < tile_n) ? (uint32_t)((key[i] >> shift) & (SORT_RADIX - 1)) : (uint32_t)(SORT_RADIX - 1);
+    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    const uint32_t below = __popc(peers & ((1u << lane) - 1u));
+    uint32_t prev = 0;
+    if (below == 0) {
+      prev = sm.warp_hist[w][d];
+      sm.warp_hist[w][d] = prev + __popc(peers);
+    }
+    prev = __shfl_sync(0xffffffffu, prev, __ffs(peers) - 1);
+    rank[i] = prev + below;
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // ---- per-digit combine + look-back (thread d owns digit d) ----
+  {
+    const int d = tid;
+    uint32_t run = 0;
+#pragma unroll
+    for (int ww = 0; ww < RS_WARPS; ++ww) {
+      uint32_t c = sm.warp_hist[ww][d];
+      sm.warp_hist[ww][d] = run;
+      run += c;
+    }
+    uint32_t count = run;
+    if (d == SORT_RADIX - 1) count -= (uint32_t)(SORT_TILE - tile_n);  // padding keys were ranked as digit 255
+    uint32_t* my_status = lookback + (size_t)bid * SORT_RADIX + d;
+    st_volatile_u32(my_status, (bid == 0 ? FLAG_INCL : FLAG_LOCAL) | count);
+
+    // exclusive scan of `run` over digits (tile-local bin starts; padding included, it sorts last)
+    uint32_t inc = run;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) sm.warp_tot[w] = inc;
+    __syncthreads();
+    uint32_t woff = 0;
+#pragma unroll
+    for (int ww = 0; ww < RS_WARPS; ++ww) woff += (ww < w) ? sm.warp_tot[ww] : 0u;
+    const uint32_t bstart = woff + inc - run;
+    sm.bin_start[d] = bstart;
+
+    uint32_t excl = 0;
+    if (bid > 0) {
+      long long p = (long long)bid - 1;
+      while (true) {
+        uint32_t s = ld_volatile_u32(lookback + (size_t)p * SORT_RADIX + d);
+        const uint32_t f = s & FLAG_MASK;
+        if (f == 0) continue;  // predecessor tile has not published yet
+        excl += s & VALUE_MASK;
+        if (f == FLAG_INCL) break;
+        --p;
+      }
+      st_volatile_u32(my_status, FLAG_INCL | ((excl + count) & VALUE_MASK));
+    }
+    sm.global_base[d] = digit_offsets[d] + excl - bstart;
+  }
+  __syncthreads();
+
+  // ---- scatter into tile-sorted order in shared memory ----
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    const int t = wbase + i * 32 + lane;
+    const uint32_t d = (t < tile_n) ? (uint32_t)((key[i] >> shift) & (SORT_RADIX - 1)) : (uint32_t)(SORT_RADIX - 1);
+    const uint32_t pos = sm.bin_start[d] + sm.warp_hist[w][d] + rank[i];
+    sm.keys[pos] = key[i];
+    sm.vals[pos] = val[i];
+  }
+  __syncthreads();
+
+  // ---- coalesced write-out (padding occupies positions >= tile_n) ----
+#pragma unroll 4
+  for (int p = tid; p < tile_n; p += RS_THREADS) {
+    const KeyT k = sm.keys[p];
+    const uint32_t d = (uint32_t)((k >> shift) & (SORT_RADIX - 1));
+    const uint32_t g = sm.global_base[d] + (uint32_t)p;
+    keys_out[g] = k;
+    vals_out[g] = sm.vals[p];
+  }
+}
+
+// Generic digit histogram over the keys (test hook / kNN path).
+template <typename KeyT>
+__global__ void __launch_bounds__(256)
+digit_hist_kernel(const KeyT* __restrict__ keys, long long n, int n_passes, uint32_t* __restrict__ hist) {
+  __shared__ uint32_t s[SORT_MAX_PASSES * SORT_RADIX];
+  for (int i = threadIdx.x; i < n_passes * SORT_RADIX; i += 256) s[i] = 0;
+  __syncthreads();
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+    KeyT k = keys[i];
+    for (int p = 0; p < n_passes; ++p) atomicAdd(&s[p * SORT_RADIX + (uint32_t)((k >> (8 * p)) & 255)], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n_passes * SORT_RADIX; i += 256)
+    if (s[i]) atomicAdd(&hist[i], s[i]);
+}
+
+__global__ void digit_offsets_kernel(uint32_t* hist, int n_passes) {
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (w >= n_passes) return;
+  uint32_t run = 0;
+  for (int c = 0; c < 8; ++c) {
+    uint32_t v = hist[w * 256 + c * 32 + lane];
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    hist[w * 256 + c * 32 + lane] = run + inc - v;
+    run += __shfl_sync(0xffffffffu, inc, 31);
+  }
+}
+
+template <typename KeyT>
+static cudaError_t sort_passes_impl(cudaStream_t st, long long n, KeyT* keys_a, KeyT* keys_b, uint32_t* vals_a,
+                                    uint32_t* vals_b, int n_passes, const uint32_t* digit_offsets,
+                                    uint32_t* tickets, uint32_t* lookback, uint32_t* final_vals) {
+  static bool attr_set = false;
+  const size_t smem = sizeof(RsSmem<KeyT>);
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(onesweep_pass_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const unsigned nblocks = (unsigned)sort_blocks(n);
+  KeyT* kin = keys_a; KeyT* kout = keys_b;
+  uint32_t* vin = vals_a; uint32_t* vout = vals_b;
+  for (int p = 0; p < n_passes; ++p) {
+    uint32_t* vdst = (p == n_passes - 1 && final_vals) ? final_vals : vout;
+    onesweep_pass_kernel<KeyT><<<nblocks, RS_THREADS, smem, st>>>(
+        kin, kout, vin, vdst, n, 8 * p, digit_offsets + p * SORT_RADIX, tickets + p,
+        lookback + (size_t)p * nblocks * SORT_RADIX);
+    KeyT* tk = kin; kin = kout; kout = tk;
+    uint32_t* tv = vin; vin = vout; vout = tv;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t sort_pairs_u64_prehist(cudaStream_t st, long long n, uint64_t* keys_a, uint64_t* keys_b,
+                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes,
+                                   const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
+                                   uint32_t* final_vals) {
+  if (n <= 0) return cudaSuccess;
+  return sort_passes_impl<uint64_t>(st, n, keys_a, keys_b, vals_a, vals_b, n_passes, digit_offsets, tickets,
+                                    lookback, final_vals);
+}
+
+cudaError_t sort_pairs_u32_prehist(cudaStream_t st, long long n, uint32_t* keys_a, uint32_t* keys_b,
+                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes,
+                                   const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
+                                   uint32_t* final_vals) {
+  if (n <= 0) return cudaSuccess;
+  return sort_passes_impl<uint32_t>(st, n, keys_a, keys_b, vals_a, vals_b, n_passes, digit_offsets, tickets,
+                                    lookback, final_vals);
+}
+
+cudaError_t launch_digit_hist_u64(cudaStream_t st, const uint64_t* keys, long long n, int n_passes,
+                                  uint32_t* hist) {
+  if (n <= 0) return cudaSuccess;
+  int blocks = (int)min((long long)148 * 8, (n + 255) / 256);
+  digit_hist_kernel<uint64_t><<<blocks, 256, 0, st>>>(keys, n, n_passes, hist);
+  digit_offsets_kernel<<<1, 256, 0, st>>>(hist, n_passes);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_digit_hist_u32(cudaStream_t st, const uint32_t* keys, long long n, int n_passes,
+                                  uint32_t* hist) {
+  if (n <= 0) return cudaSuccess;
+  int blocks = (int)min((long long)148 * 8, (n + 255) / 256);
+  digit_hist_kernel<uint32_t><<<blocks, 256, 0, st>>>(keys, n, n_passes, hist);
+  digit_offsets_kernel<<<1, 256, 0, st>>>(hist, n_passes);
+  return cudaGetLastError();
+}
+
+}  // namespace gsr

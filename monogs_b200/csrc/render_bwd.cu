@@ -1,0 +1,256 @@
+// render_bwd.cu -- backward tile renderer (K8 of SURVEY 2.2).
+//
+// Replaces renderCUDA<3> of backward.cu:563-787 and its block-wide
+// shared-memory tree reduction (render_cuda_reduce_sum, backward.cu:548-559).
+// Same tile/warp decomposition and cp.async staging as the forward kernel,
+// traversed back to front.  Differences from the reference's schedule (the
+// math per (pixel, Gaussian) pair is the same):
+//   * the traversal starts at the tile's largest n_contrib instead of the end
+//     of the list (entries behind every pixel's last contributor are no-ops);
+//   * no block barrier inside the per-Gaussian loop: each warp culls, replays
+//     and reduces on its own;
+//   * the ten partial gradients of a (warp, Gaussian) pair are reduced with a
+//     12-shuffle "transpose" butterfly that leaves each total in a distinct
+//     lane, and those ten lanes issue ONE warp-wide red.global.add.f32 into a
+//     packed 48-byte per-Gaussian record (1-2 sectors per instruction);
+//   * warps in which no pixel is touched by the Gaussian do nothing.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace gsr {
+
+constexpr int RB_THREADS = 256;
+constexpr int RB_BATCH = 256;
+
+struct RbStage {
+  float4 a[RB_BATCH];
+  float4 b[RB_BATCH];
+  float4 c[RB_BATCH];
+  uint32_t id[RB_BATCH];
+};
+
+GSR_DEVINL void rb_cp_async16(void* smem_dst, const void* gmem_src) {
+  uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");
+}
+GSR_DEVINL void rb_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+GSR_DEVINL void rb_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Reduce 10 per-lane values over the warp with 12 shuffles. On return the
+// total of value k sits in v0 of the lanes whose bits 4..1 select k:
+//   k = 5*b4 + (b3 ? 3 + b2 : (b2 ? 2 : b1))   (see owner_slot()).
+GSR_DEVINL float reduce10(float v[10], int lane) {
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+  float w[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const float keep = b4 ? v[i + 5] : v[i];
+    const float send = b4 ? v[i] : v[i + 5];
+    w[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  }
+  float u[3];
+  {  // 5 -> (0,1,2) | (3,4,-)
+    const float s0 = b3 ? w[0] : w[3], k0 = b3 ? w[3] : w[0];
+    const float s1 = b3 ? w[1] : w[4], k1 = b3 ? w[4] : w[1];
+    const float s2 = b3 ? w[2] : 0.0f, k2 = b3 ? 0.0f : w[2];
+    u[0] = k0 + __shfl_xor_sync(0xffffffffu, s0, 8);
+    u[1] = k1 + __shfl_xor_sync(0xffffffffu, s1, 8);
+    u[2] = k2 + __shfl_xor_sync(0xffffffffu, s2, 8);
+  }
+  float t[2];
+  {  // 3 -> (0,1) | (2,-)
+    const float s0 = b2 ? u[0] : u[2], k0 = b2 ? u[2] : u[0];
+    const float s1 = b2 ? u[1] : 0.0f, k1 = b2 ? 0.0f : u[1];
+    t[0] = k0 + __shfl_xor_sync(0xffffffffu, s0, 4);
+    t[1] = k1 + __shfl_xor_sync(0xffffffffu, s1, 4);
+  }
+  float r;
+  {  // 2 -> 0 | 1
+    const float s0 = b1 ? t[0] : t[1], k0 = b1 ? t[1] : t[0];
+    r = k0 + __shfl_xor_sync(0xffffffffu, s0, 2);
+  }
+  r += __shfl_xor_sync(0xffffffffu, r, 1);
+  return r;
+}
+
+// Which of the 10 values a lane ends up owning (-1: none / duplicate).
+GSR_DEVINL int owner_slot(int lane) {
+  if (lane & 1) return -1;
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+  int k5;
+  if (!b3) {             // group (0,1,2)
+    if (!b2) k5 = b1 ? 1 : 0;   // (0,1)
+    else { if (b1) return -1; k5 = 2; }
+  } else {               // group (3,4,-)
+    if (!b2) k5 = b1 ? 4 : 3;
+    else return -1;
+  }
+  return (b4 ? 5 : 0) + k5;
+}
+
+__global__ void __launch_bounds__(RB_THREADS)
+render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+                  int tiles_x, const float* __restrict__ bg, const float4* __restrict__ rec_a,
+                  const float4* __restrict__ rec_b, const float4* __restrict__ rec_c,
+                  const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
+                  const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth,
+                  float* __restrict__ packed /*[P][GRAD_STRIDE]*/) {
+  __shared__ __align__(16) RbStage stage[2];
+  __shared__ uint32_t s_max[RB_THREADS / 32];
+
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int tile = blockIdx.y * tiles_x + blockIdx.x;
+  const int wx0 = blockIdx.x * TILE_X + (w & 1) * 8;
+  const int wy0 = blockIdx.y * TILE_Y + (w >> 1) * 4;
+  const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
+  const bool inside = pxi < W && pyi < H;
+  const float pixx = (float)pxi, pixy = (float)pyi;
+  const float rx0 = (float)wx0, rx1 = (float)(wx0 + 7), ry0 = (float)wy0, ry1 = (float)(wy0 + 3);
+  const size_t pix = (size_t)pyi * W + pxi;
+  const size_t HW = (size_t)H * W;
+
+  const uint2 range = ranges[tile];
+  const float T_final = inside ? final_T[pix] : 0.0f;
+  const uint32_t last_contributor = inside ? n_contrib[pix] : 0u;
+  float dpr = 0.f, dpg = 0.f, dpb = 0.f, dpd = 0.f;
+  if (inside) {
+    if (dL_dpix) { dpr = dL_dpix[pix]; dpg = dL_dpix[HW + pix]; dpb = dL_dpix[2 * HW + pix]; }
+    if (dL_dpix_depth) dpd = dL_dpix_depth[pix];
+  }
+  const float bg_dot_dpixel = bg[0] * dpr + bg[1] * dpg + bg[2] * dpb;
+
+  // tile-wide start of the back-to-front walk
+  uint32_t wm = last_contributor;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wm = max(wm, __shfl_xor_sync(0xffffffffu, wm, o));
+  if (lane == 0) s_max[w] = wm;
+  __syncthreads();
+  uint32_t tile_last = 0;
+#pragma unroll
+  for (int i = 0; i < RB_THREADS / 32; ++i) tile_last = max(tile_last, s_max[i]);
+  const int total = (int)tile_last;  // list positions [0, total) are replayed, from the back
+  const int n_batches = (total + RB_BATCH - 1) / RB_BATCH;
+
+  float T = T_final;
+  float acc_r = 0.f, acc_g = 0.f, acc_b = 0.f, acc_d = 0.f;
+  float last_alpha = 0.f, last_r = 0.f, last_g = 0.f, last_b = 0.f, last_d = 0.f;
+  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+  const int slot = owner_slot(lane);
+
+  // batch k covers list positions pos = total-1 - (k*RB_BATCH + t), t = 0..255 (descending)
+  uint32_t id_next = 0;
+  if (n_batches > 0) {
+    if (tid < total) {
+      const uint32_t id = point_list[range.x + (total - 1 - tid)];
+      stage[0].id[tid] = id;
+      rb_cp_async16(&stage[0].a[tid], rec_a + id);
+      rb_cp_async16(&stage[0].b[tid], rec_b + id);
+      rb_cp_async16(&stage[0].c[tid], rec_c + id);
+    }
+    rb_commit();
+    if (RB_BATCH + tid < total) id_next = point_list[range.x + (total - 1 - RB_BATCH - tid)];
+  }
+
+  for (int b = 0; b < n_batches; ++b) {
+    const int cur = b & 1;
+    if (b + 1 < n_batches) {
+      const int e = (b + 1) * RB_BATCH + tid;
+      if (e < total) {
+        RbStage& nx = stage[cur ^ 1];
+        nx.id[tid] = id_next;
+        rb_cp_async16(&nx.a[tid], rec_a + id_next);
+        rb_cp_async16(&nx.b[tid], rec_b + id_next);
+        rb_cp_async16(&nx.c[tid], rec_c + id_next);
+      }
+      rb_commit();
+      const int e2 = (b + 2) * RB_BATCH + tid;
+      if (e2 < total) id_next = point_list[range.x + (total - 1 - e2)];
+      rb_wait<1>();
+    } else {
+      rb_wait<0>();
+    }
+    __syncthreads();
+
+    const RbStage& sg = stage[cur];
+    const int count = min(RB_BATCH, total - b * RB_BATCH);
+    for (int g0 = 0; g0 < count; g0 += 32) {
+      const int jj = g0 + lane;
+      bool hit = false;
+      if (jj < count) {
+        const float4 a = sg.a[jj];
+        const float ey = sg.c[jj].w;
+        hit = (a.x + a.w >= rx0) && (a.x - a.w <= rx1) && (a.y + ey >= ry0) && (a.y - ey <= ry1);
+      }
+      uint32_t mask = __ballot_sync(0xffffffffu, hit);
+      while (mask) {
+        const int j = g0 + __ffs(mask) - 1;
+        mask &= mask - 1;
+        const uint32_t pos = (uint32_t)(total - 1 - (b * RB_BATCH + j));  // 0-based list position
+        const float4 a = sg.a[j];
+        const float4 co = sg.b[j];
+        const float dx = fsub(a.x, pixx), dy = fsub(a.y, pixy);
+        const float q = ffma(dx, fmul(dx, co.x), fmul(dy, fmul(dy, co.z)));
+        const float power = fsub(fmul(q, -0.5f), fmul(dy, fmul(dx, co.y)));
+        const float G = expf(power);
+        const float alpha = fminf(fmul(co.w, G), 0.99f);
+        // skip rules of backward.cu:676-689
+        const bool skip = !inside || pos >= last_contributor || power > 0.0f || alpha < 1.0f / 255.0f;
+        if (__ballot_sync(0xffffffffu, !skip) == 0) continue;
+
+        float v[10];
+#pragma unroll
+        for (int i = 0; i < 10; ++i) v[i] = 0.0f;
+        if (!skip) {
+          const float4 c = sg.c[j];
+          const float one_m_alpha = 1.0f - alpha;
+          T = T / one_m_alpha;
+          const float dchannel_dcolor = alpha * T;
+          float dL_dalpha = 0.0f;
+          acc_r = last_alpha * last_r + (1.f - last_alpha) * acc_r; last_r = c.x;
+          dL_dalpha += (c.x - acc_r) * dpr;
+          acc_g = last_alpha * last_g + (1.f - last_alpha) * acc_g; last_g = c.y;
+          dL_dalpha += (c.y - acc_g) * dpg;
+          acc_b = last_alpha * last_b + (1.f - last_alpha) * acc_b; last_b = c.z;
+          dL_dalpha += (c.z - acc_b) * dpb;
+          acc_d = last_alpha * last_d + (1.f - last_alpha) * acc_d; last_d = a.z;
+          dL_dalpha += (a.z - acc_d) * dpd;
+          dL_dalpha *= T;
+          last_alpha = alpha;
+          dL_dalpha += (-T_final / one_m_alpha) * bg_dot_dpixel;
+
+          const float dL_dG = co.w * dL_dalpha;
+          const float gdx = G * dx, gdy = G * dy;
+          const float dG_ddelx = -gdx * co.x - gdy * co.y;
+          const float dG_ddely = -gdy * co.z - gdx * co.y;
+          v[0] = dL_dG * dG_ddelx * ddelx_dx;
+          v[1] = dL_dG * dG_ddely * ddely_dy;
+          v[2] = -0.5f * gdx * dx * dL_dG;
+          v[3] = -0.5f * gdx * dy * dL_dG;
+          v[4] = -0.5f * gdy * dy * dL_dG;
+          v[5] = G * dL_dalpha;
+          v[6] = dchannel_dcolor * dpr;
+          v[7] = dchannel_dcolor * dpg;
+          v[8] = dchannel_dcolor * dpb;
+          v[9] = dchannel_dcolor * dpd;
+        }
+        const float r = reduce10(v, lane);
+        if (slot >= 0) atomicAdd(packed + (size_t)sg.id[j] * GRAD_STRIDE + slot, r);
+      }
+    }
+    __syncthreads();
+  }
+  rb_wait<0>();
+}
+
+cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
+                              const GeomViews& g, const float* bg, const float* dL_dpix,
+                              const float* dL_dpix_depth, float* packed) {
+  const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
+  dim3 grid(tiles_x, tiles_y);
+  render_bwd_kernel<<<grid, RB_THREADS, 0, st>>>(im.ranges, point_list, W, H, tiles_x, bg, g.rec_a, g.rec_b,
+                                                 g.rec_c, im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, packed);
+  return cudaGetLastError();
+}
+
+}  // namespace gsr

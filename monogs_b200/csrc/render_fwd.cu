@@ -1,0 +1,175 @@
+// render_fwd.cu -- forward tile renderer (K7 of SURVEY 2.2).
+//
+// Replaces renderCUDA<3> (forward.cu:263-392).  One 256-thread block per
+// 16x16 tile, but each WARP owns an 8x4 pixel sub-rectangle:
+//   * the tile's instance list is staged in batches of 256 through shared
+//     memory with cp.async (LDGSTS) gathers of three 16-byte records per
+//     Gaussian, double buffered so the gather of batch b+1 overlaps the
+//     blending of batch b;
+//   * before blending, every lane tests ONE staged Gaussian against the warp's
+//     pixel rectangle (conservative reach of alpha >= 1/255, precomputed per
+//     Gaussian) and a ballot turns that into a 32-bit survivor mask -- the
+//     per-pixel loop then only visits Gaussians that can contribute to this
+//     warp, which skips exactly the iterations the reference `continue`s;
+//   * a warp whose 32 pixels are all saturated stops blending, the block
+//     stops fetching when all 8 warps are done.
+// The blended quantities follow the reference's fp32 operation order exactly
+// (explicit fmul/ffma), so final_T, n_contrib and the integer n_touched are
+// bit-identical and colour/depth/opacity agree to the last bit.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace gsr {
+
+constexpr int RF_THREADS = 256;
+constexpr int RF_BATCH = 256;
+
+struct RfStage {
+  float4 a[RF_BATCH];
+  float4 b[RF_BATCH];
+  float4 c[RF_BATCH];
+  uint32_t id[RF_BATCH];
+};
+
+GSR_DEVINL void cp_async16(void* smem_dst, const void* gmem_src) {
+  uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");
+}
+GSR_DEVINL void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+GSR_DEVINL void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__global__ void __launch_bounds__(RF_THREADS)
+render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+                  int tiles_x, const float4* __restrict__ rec_a, const float4* __restrict__ rec_b,
+                  const float4* __restrict__ rec_c, const float* __restrict__ bg, float* __restrict__ final_T,
+                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_depth,
+                  float* __restrict__ out_opacity, int* __restrict__ n_touched) {
+  __shared__ __align__(16) RfStage stage[2];
+
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int tile = blockIdx.y * tiles_x + blockIdx.x;
+  // warp sub-rectangle: 2 columns x 4 rows of 8x4-pixel rectangles
+  const int wx0 = blockIdx.x * TILE_X + (w & 1) * 8;
+  const int wy0 = blockIdx.y * TILE_Y + (w >> 1) * 4;
+  const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
+  const bool inside = pxi < W && pyi < H;
+  const float pixx = (float)pxi, pixy = (float)pyi;
+  const float rx0 = (float)wx0, rx1 = (float)(wx0 + 7), ry0 = (float)wy0, ry1 = (float)(wy0 + 3);
+
+  const uint2 range = ranges[tile];
+  const int total = (int)(range.y - range.x);
+  const int n_batches = (total + RF_BATCH - 1) / RF_BATCH;
+
+  float T = 1.0f, Cr = 0.f, Cg = 0.f, Cb = 0.f, D = 0.f;
+  uint32_t last_contributor = 0;
+  bool done = !inside;
+
+  // prologue: gather batch 0, prefetch the ids of batch 1
+  uint32_t id_next = 0;
+  if (n_batches > 0) {
+    if (tid < total) {
+      const uint32_t id = point_list[range.x + tid];
+      stage[0].id[tid] = id;
+      cp_async16(&stage[0].a[tid], rec_a + id);
+      cp_async16(&stage[0].b[tid], rec_b + id);
+      cp_async16(&stage[0].c[tid], rec_c + id);
+    }
+    cp_async_commit();
+    if (RF_BATCH + tid < total) id_next = point_list[range.x + RF_BATCH + tid];
+  }
+
+  for (int b = 0; b < n_batches; ++b) {
+    const int cur = b & 1;
+    // issue the gather of batch b+1 into the other buffer (free since the barrier ending batch b-1)
+    if (b + 1 < n_batches) {
+      const int e = (b + 1) * RF_BATCH + tid;
+      if (e < total) {
+        RfStage& nx = stage[cur ^ 1];
+        nx.id[tid] = id_next;
+        cp_async16(&nx.a[tid], rec_a + id_next);
+        cp_async16(&nx.b[tid], rec_b + id_next);
+        cp_async16(&nx.c[tid], rec_c + id_next);
+      }
+      cp_async_commit();
+      const int e2 = (b + 2) * RF_BATCH + tid;
+      if (e2 < total) id_next = point_list[range.x + e2];
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+
+    const RfStage& sg = stage[cur];
+    const int count = min(RF_BATCH, total - b * RF_BATCH);
+    const bool warp_live = !__all_sync(0xffffffffu, done);
+    if (warp_live) {
+      for (int g0 = 0; g0 < count; g0 += 32) {
+        // lane-parallel conservative cull of 32 staged Gaussians against this warp's rectangle
+        const int jj = g0 + lane;
+        bool hit = false;
+        if (jj < count) {
+          const float4 a = sg.a[jj];
+          const float ey = sg.c[jj].w;
+          hit = (a.x + a.w >= rx0) && (a.x - a.w <= rx1) && (a.y + ey >= ry0) && (a.y - ey <= ry1);
+        }
+        uint32_t mask = __ballot_sync(0xffffffffu, hit);
+        while (mask) {
+          const int j = g0 + __ffs(mask) - 1;
+          mask &= mask - 1;
+          const float4 a = sg.a[j];
+          const float4 co = sg.b[j];
+          const float dx = fsub(a.x, pixx), dy = fsub(a.y, pixy);
+          // power = -0.5f*(con.x*dx*dx + con.z*dy*dy) - con.y*dx*dy  (forward.cu:345)
+          const float q = ffma(dx, fmul(dx, co.x), fmul(dy, fmul(dy, co.z)));
+          const float power = fsub(fmul(q, -0.5f), fmul(dy, fmul(dx, co.y)));
+          const float alpha = fminf(fmul(co.w, expf(power)), 0.99f);
+          const float test_T = fmul(T, fsub(1.0f, alpha));
+          bool act = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+          if (act && test_T < 0.0001f) { done = true; act = false; }
+          if (act) {
+            const float4 c = sg.c[j];
+            Cr = ffma(T, fmul(alpha, c.x), Cr);
+            Cg = ffma(T, fmul(alpha, c.y), Cg);
+            Cb = ffma(T, fmul(alpha, c.z), Cb);
+            D = ffma(T, fmul(alpha, a.z), D);
+            T = test_T;
+            last_contributor = (uint32_t)(b * RF_BATCH + j + 1);
+          }
+          // n_touched: pixels where this Gaussian is seen with T(1-alpha) > 0.5 (forward.cu:369-371)
+          const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
+          if (tv != 0 && lane == 0) atomicAdd(&n_touched[sg.id[j]], __popc(tv));
+          if (__all_sync(0xffffffffu, done)) { mask = 0; g0 = count; }
+        }
+      }
+    }
+    // everyone must be done reading `cur` before batch b+2 is gathered into it
+    if (__syncthreads_and(done)) break;
+  }
+  cp_async_wait<0>();
+
+  if (inside) {
+    const size_t pix = (size_t)pyi * W + pxi;
+    const size_t HW = (size_t)H * W;
+    final_T[pix] = T;
+    n_contrib[pix] = last_contributor;
+    out_color[pix] = ffma(T, bg[0], Cr);
+    out_color[HW + pix] = ffma(T, bg[1], Cg);
+    out_color[2 * HW + pix] = ffma(T, bg[2], Cb);
+    out_depth[pix] = D;
+    out_opacity[pix] = fsub(1.0f, T);
+  }
+}
+
+cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
+                              const GeomViews& g, const float* bg, float* out_color, float* out_depth,
+                              float* out_opacity, int* n_touched) {
+  const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
+  dim3 grid(tiles_x, tiles_y);
+  render_fwd_kernel<<<grid, RF_THREADS, 0, st>>>(im.ranges, point_list, W, H, tiles_x, g.rec_a, g.rec_b, g.rec_c,
+                                                 bg, im.final_T, im.n_contrib, out_color, out_depth, out_opacity,
+                                                 n_touched);
+  return cudaGetLastError();
+}
+
+}  // namespace gsr

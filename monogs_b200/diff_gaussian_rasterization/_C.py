@@ -1,0 +1,177 @@
+"""Host-side mirror of the reference's pybind module `diff_gaussian_rasterization._C`
+(submodules/diff-gaussian-rasterization/ext.cpp:15-19), implemented on top of the
+C ABI in include/gsr_b200.h via ctypes.  Same function names, argument order and
+return tuples as RasterizeGaussiansCUDA / RasterizeGaussiansBackwardCUDA /
+markVisible (rasterize_points.cu:35-232).  There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .. import _abi
+
+NUM_CHANNELS = 3
+
+
+def _ptr(t):
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32(t, name):
+    """contiguous fp32 CUDA tensor or None for an absent (empty) one."""
+    if t is None or t.numel() == 0:
+        return None
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name}: expected scalar type Float but found {t.dtype}")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name}: expected a CUDA tensor")
+    return t.contiguous()
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, projmatrix_raw, tan_fovx, tan_fovy, image_height, image_width,
+                        sh, degree, campos, prefiltered, debug):
+    """-> (num_rendered, color[3,H,W], radii[P] i32, geomBuffer u8, binningBuffer u8, imgBuffer u8,
+           depth[1,H,W], opacity[1,H,W], n_touched[P] i32)   (rasterize_points.cu:35-122)"""
+    lib = _abi.load()
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:58-60
+    P, H, W = int(means3D.size(0)), int(image_height), int(image_width)
+    dev = means3D.device
+    fopt = dict(dtype=torch.float32, device=dev)
+    if P == 0:
+        z = lambda *s: torch.zeros(*s, **fopt)
+        e = torch.empty(0, dtype=torch.uint8, device=dev)
+        zi = torch.zeros(0, dtype=torch.int32, device=dev)
+        return 0, z(NUM_CHANNELS, H, W), zi, e, e.clone(), e.clone(), z(1, H, W), z(1, H, W), zi.clone()
+
+    with torch.cuda.device(dev):
+        means3D_c = _f32(means3D, "means3D")
+        colors_c, opacity_c = _f32(colors, "colors"), _f32(opacity, "opacity")
+        scales_c, rot_c, cov_c = _f32(scales, "scales"), _f32(rotations, "rotations"), _f32(cov3D_precomp, "cov3D_precomp")
+        sh_c, campos_c = _f32(sh, "sh"), _f32(campos, "campos")
+        view_c, proj_c, bg_c = _f32(viewmatrix, "viewmatrix"), _f32(projmatrix, "projmatrix"), _f32(background, "bg")
+        M = int(sh.size(1)) if (sh is not None and sh.numel() != 0) else 0
+
+        out_color = torch.empty(NUM_CHANNELS, H, W, **fopt)
+        out_depth = torch.empty(1, H, W, **fopt)
+        out_opacity = torch.empty(1, H, W, **fopt)
+        radii = torch.empty(P, dtype=torch.int32, device=dev)
+        n_touched = torch.zeros(P, dtype=torch.int32, device=dev)
+        geom = torch.empty(lib.gsr_geom_bytes(P, W, H), dtype=torch.uint8, device=dev)
+        img = torch.empty(lib.gsr_image_bytes(W, H), dtype=torch.uint8, device=dev)
+
+        R = C.c_int64(0)
+        st = _stream()
+        rc = lib.gsr_forward_plan(st, P, int(degree), M, W, H, _ptr(means3D_c), _ptr(sh_c), _ptr(colors_c),
+                                  _ptr(opacity_c), _ptr(scales_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c),
+                                  _ptr(view_c), _ptr(proj_c), _ptr(campos_c), float(tan_fovx), float(tan_fovy),
+                                  int(bool(prefiltered)), radii.data_ptr(), geom.data_ptr(), img.data_ptr(),
+                                  C.byref(R), int(bool(debug)))
+        _abi.check(rc, "gsr_forward_plan")
+        R = int(R.value)
+        point_list = torch.empty(lib.gsr_point_list_bytes(R), dtype=torch.uint8, device=dev)
+        binning = torch.empty(lib.gsr_binning_bytes(R) if R > 0 else 0, dtype=torch.uint8, device=dev)
+        rc = lib.gsr_forward_render(st, P, W, H, _ptr(bg_c), radii.data_ptr(), geom.data_ptr(), img.data_ptr(),
+                                    _ptr(binning), point_list.data_ptr(), R, out_color.data_ptr(),
+                                    out_depth.data_ptr(), out_opacity.data_ptr(), n_touched.data_ptr(),
+                                    int(bool(debug)))
+        _abi.check(rc, "gsr_forward_render")
+        if debug:
+            rasterize_gaussians.last_binning = binning  # test hook: sorted keys live in here
+    return R, out_color, radii, geom, point_list, img, out_depth, out_opacity, n_touched
+
+
+def _backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                   projmatrix, projmatrix_raw, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth, sh, degree, campos,
+                   geomBuffer, R, binningBuffer, imageBuffer, debug, want, per_gaussian_tau):
+    lib = _abi.load()
+    P = int(means3D.size(0))
+    dev = means3D.device
+    fopt = dict(dtype=torch.float32, device=dev)
+    M = int(sh.size(1)) if (sh is not None and sh.numel() != 0) else 0
+    H, W = None, None
+    for g in (dL_dout_color, dL_dout_depth):
+        if g is not None:
+            H, W = int(g.size(1)), int(g.size(2))
+    if H is None:
+        raise RuntimeError("backward needs at least one of dL_dout_color / dL_dout_depth")
+    names = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
+    shapes = dict(means2D=(P, 3), colors=(P, NUM_CHANNELS), opacity=(P, 1), means3D=(P, 3), cov3D=(P, 6),
+                  sh=(P, M, 3), scales=(P, 3), rotations=(P, 4))
+    out = {}
+    for n in names:
+        if not want.get(n, True):
+            out[n] = None
+        elif P == 0 or (n == "sh" and M == 0):
+            out[n] = torch.zeros(*shapes[n], **fopt)
+        elif n in ("scales", "rotations") and (scales is None or scales.numel() == 0):
+            out[n] = torch.zeros(*shapes[n], **fopt)  # cov3D_precomp path: reference leaves them zero
+        else:
+            out[n] = torch.empty(*shapes[n], **fopt)
+    tau_pg = (torch.zeros(P, 6, **fopt) if P == 0 else torch.empty(P, 6, **fopt)) if per_gaussian_tau else None
+    tau = torch.zeros(6, **fopt)
+    if P == 0:
+        return out, tau_pg, tau
+    with torch.cuda.device(dev):
+        scratch = torch.empty(lib.gsr_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
+        gc, gd = _f32(dL_dout_color, "dL_dout_color"), _f32(dL_dout_depth, "dL_dout_depth")
+        args = [_f32(background, "bg"), _f32(means3D, "means3D"), _f32(sh, "sh"), _f32(colors, "colors"),
+                _f32(scales, "scales")]
+        rot_c, cov_c = _f32(rotations, "rotations"), _f32(cov3D_precomp, "cov3D_precomp")
+        cam = [_f32(viewmatrix, "viewmatrix"), _f32(projmatrix, "projmatrix"), _f32(projmatrix_raw, "projmatrix_raw"),
+               _f32(campos, "campos")]
+        radii_c = radii.contiguous()
+        rc = lib.gsr_backward(
+            _stream(), P, int(degree), M, W, H, _ptr(args[0]), _ptr(args[1]), _ptr(args[2]), _ptr(args[3]),
+            _ptr(args[4]), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(cam[0]), _ptr(cam[1]), _ptr(cam[2]),
+            _ptr(cam[3]), float(tan_fovx), float(tan_fovy), radii_c.data_ptr(), geomBuffer.data_ptr(),
+            imageBuffer.data_ptr(), _ptr(binningBuffer), int(R), _ptr(gc), _ptr(gd), scratch.data_ptr(),
+            _ptr(out["means2D"]), _ptr(out["colors"]), _ptr(out["opacity"]), _ptr(out["means3D"]),
+            _ptr(out["cov3D"]), _ptr(out["sh"]), _ptr(out["scales"]), _ptr(out["rotations"]), _ptr(tau_pg),
+            tau.data_ptr(), int(bool(debug)))
+        _abi.check(rc, "gsr_backward")
+    return out, tau_pg, tau
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                 cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw, tan_fovx, tan_fovy,
+                                 dL_dout_color, dL_dout_depth, sh, degree, campos, geomBuffer, R, binningBuffer,
+                                 imageBuffer, debug):
+    """Reference-compatible raw backward (rasterize_points.cu:124-211):
+    -> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, dL_dtau[P,6])"""
+    out, tau_pg, _ = _backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                    cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw, tan_fovx, tan_fovy,
+                                    dL_dout_color, dL_dout_depth, sh, degree, campos, geomBuffer, R, binningBuffer,
+                                    imageBuffer, debug, {}, True)
+    return (out["means2D"], out["colors"], out["opacity"], out["means3D"], out["cov3D"], out["sh"], out["scales"],
+            out["rotations"], tau_pg)
+
+
+def rasterize_gaussians_backward_fused(*args, want=None):
+    """Same inputs as rasterize_gaussians_backward; returns (dict of wanted grads, dL_dtau[6]) with the
+    pose gradient already summed over Gaussians in-kernel (replaces torch.sum at __init__.py:152)."""
+    out, _, tau = _backward_impl(*args, want or {}, False)
+    return out, tau
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """bool[P] = p_view.z > 0.2  (rasterize_points.cu:213-232)"""
+    lib = _abi.load()
+    P = int(means3D.size(0))
+    present = torch.zeros(P, dtype=torch.bool, device=means3D.device)
+    if P != 0:
+        with torch.cuda.device(means3D.device):
+            rc = lib.gsr_mark_visible(_stream(), P, _f32(means3D, "means3D").data_ptr(),
+                                      _f32(viewmatrix, "viewmatrix").data_ptr(),
+                                      _f32(projmatrix, "projmatrix").data_ptr(), present.data_ptr())
+            _abi.check(rc, "gsr_mark_visible")
+    return present
