@@ -162,6 +162,13 @@ __device__ __forceinline__ float affine_row(const float* m, int r, float x, floa
   return fadd(m[r + 12], dot3c(x, m[r], y, m[r + 4], z, m[r + 8]));
 }
 
+// power = -0.5f*(con.x*dx*dx + con.z*dy*dy) - con.y*dx*dy  (forward.cu:345), in the operation order of the
+// reference's SASS: q = fma(dx, dx*cx, dy*(dy*cz)); power = fma(q, -0.5, -(dy*(dx*cy))).
+__device__ __forceinline__ float gauss_power(float dx, float dy, float cx, float cy, float cz) {
+  const float q = ffma(dx, fmul(dx, cx), fmul(dy, fmul(dy, cz)));
+  return ffma(q, -0.5f, -fmul(dy, fmul(dx, cy)));
+}
+
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
 #define GSR_DEVINL __device__ __forceinline__

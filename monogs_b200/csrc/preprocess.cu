@@ -67,20 +67,21 @@ GSR_DEVINL void cov3d_from_scale_rot(float3 s_in, float mod, float4 q, float* co
   const float sx = fmul(mod, s_in.x), sy = fmul(mod, s_in.y), sz = fmul(mod, s_in.z);
   const float r = q.x, x = q.y, y = q.z, z = q.w;
   const float yy = fmul(y, y), zz = fmul(z, z);
-  const float xy = fmul(x, y), rz = fmul(r, z), xz = fmul(x, z), ry = fmul(r, y);
-  const float yz = fmul(y, z), rx = fmul(r, x);
+  const float rz = fmul(r, z), xz = fmul(x, z), rx = fmul(r, x);
   const float yy_zz = fadd(yy, zz);
   const float xx_zz = ffma(x, x, zz);
   const float xx_yy = ffma(x, x, yy);
   auto twice = [](float v) { return fadd(v, v); };
   const float R00 = fsub(1.0f, twice(yy_zz));
-  const float a01 = twice(fsub(xy, rz));
-  const float a02 = twice(fadd(ry, xz));
-  const float a10 = twice(fadd(xy, rz));
+  // ptxas fuses one product of each off-diagonal sum into an FFMA (read from the SASS of the
+  // reference build, not its PTX: plain mul.f32/add.f32 may still be contracted by ptxas).
+  const float a01 = twice(ffma(x, y, -rz));
+  const float a02 = twice(ffma(r, y, xz));
+  const float a10 = twice(ffma(x, y, rz));
   const float R11 = fsub(1.0f, twice(xx_zz));
-  const float a12 = twice(fsub(yz, rx));
-  const float a20 = twice(fsub(xz, ry));
-  const float a21 = twice(fadd(rx, yz));
+  const float a12 = twice(ffma(y, z, -rx));
+  const float a20 = twice(ffma(-r, y, xz));
+  const float a21 = twice(ffma(y, z, rx));
   const float R22 = fsub(1.0f, twice(xx_yy));
   // M = S * R (glm column-major); the products with the zero entries of S
   // vanish for finite inputs.
@@ -227,13 +228,13 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       const float ty = affine_row(view, 1, px, py, pz);
       const float3 c2 = cov2d_project(tx, ty, depth, focal_x, focal_y, tan_fovx, tan_fovy, cov, view);
 
-      const float det = fsub(fmul(c2.x, c2.z), fmul(c2.y, c2.y));
+      const float det = ffma(c2.x, c2.z, -fmul(c2.y, c2.y));  // FFMA(a, c, -(b*b)) in the reference SASS
       if (det == 0.0f) alive = false;
       if (alive) {
         const float det_inv = frcp(det);
         const float conx = fmul(c2.z, det_inv), cony = fmul(det_inv, -c2.y), conz = fmul(c2.x, det_inv);
         const float mid = fmul(fadd(c2.x, c2.z), 0.5f);
-        const float sq = fsqrt(fmaxf(fsub(fmul(mid, mid), det), 0.1f));
+        const float sq = fsqrt(fmaxf(ffma(mid, mid, -det), 0.1f));
         const float lam = fmaxf(fadd(mid, sq), fsub(mid, sq));
         const float rad_f = ceilf(fmul(fsqrt(lam), 3.0f));
         my_radius_i = (int)rad_f;

@@ -190,8 +190,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const float4 a = sg.a[j];
         const float4 co = sg.b[j];
         const float dx = fsub(a.x, pixx), dy = fsub(a.y, pixy);
-        const float q = ffma(dx, fmul(dx, co.x), fmul(dy, fmul(dy, co.z)));
-        const float power = fsub(fmul(q, -0.5f), fmul(dy, fmul(dx, co.y)));
+        const float power = gauss_power(dx, dy, co.x, co.y, co.z);
         const float G = expf(power);
         const float alpha = fminf(fmul(co.w, G), 0.99f);
         // skip rules of backward.cu:676-689

@@ -120,9 +120,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           const float4 a = sg.a[j];
           const float4 co = sg.b[j];
           const float dx = fsub(a.x, pixx), dy = fsub(a.y, pixy);
-          // power = -0.5f*(con.x*dx*dx + con.z*dy*dy) - con.y*dx*dy  (forward.cu:345)
-          const float q = ffma(dx, fmul(dx, co.x), fmul(dy, fmul(dy, co.z)));
-          const float power = fsub(fmul(q, -0.5f), fmul(dy, fmul(dx, co.y)));
+          const float power = gauss_power(dx, dy, co.x, co.y, co.z);
           const float alpha = fminf(fmul(co.w, expf(power)), 0.99f);
           const float test_T = fmul(T, fsub(1.0f, alpha));
           bool act = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
