@@ -74,8 +74,8 @@ size_t gsr_knn_bytes(int P);
 
 /* ---- forward, phase 1: preprocess + tile-count scan ---------------------
  * Projects every Gaussian, fills radii[P] (int32) and the geometry state,
- * the per-tile ranges (in image_ws) and the radix digit offsets, and returns
- * num_rendered = sum of tiles touched through *num_rendered (host int64).  This call synchronises `stream` once (the reference does a
+ * sorts the Gaussians by (view depth, id) and returns num_rendered = sum of
+ * tiles touched through *num_rendered (host int64).  This call synchronises `stream` once (the reference does a
  * blocking cudaMemcpy at the same place). */
 int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs /*M*/,
                      int width, int height,
@@ -85,7 +85,7 @@ int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs /*M*/,
                      const float* rotations, const float* cov3D_precomp,
                      const float* viewmatrix, const float* projmatrix,
                      const float* campos, float tan_fovx, float tan_fovy,
-                     int prefiltered, int* radii, void* geom_ws, void* image_ws,
+                     int prefiltered, int* radii, void* geom_ws,
                      int64_t* num_rendered, int debug);
 
 /* ---- forward, phase 2: key emit + sort + ranges + render ----------------
@@ -151,9 +151,11 @@ int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, cons
 int gsr_debug_image_views(const void* image_ws, int width, int height,
                           const float** final_T, const uint32_t** n_contrib,
                           const uint32_t** ranges /*uint2[tiles]*/);
-/* Sorted keys of the LAST gsr_forward_render call live in binning_ws. */
-int gsr_debug_sorted_keys(const void* binning_ws, int64_t num_rendered, int width, int height,
-                          const uint64_t** keys_sorted);
+/* Rebuilds the reference's sorted 64-bit keys (tile << 32 | depth bits, rasterizer_impl.cu:102-104) of the
+ * LAST gsr_forward_render call that used these workspaces into keys_sorted[num_rendered] (device). */
+int gsr_debug_sorted_keys(void* stream, const void* geom_ws, const void* binning_ws,
+                          const uint32_t* point_list, int P, int64_t num_rendered, int width, int height,
+                          uint64_t* keys_sorted);
 
 #ifdef __cplusplus
 }

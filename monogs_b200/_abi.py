@@ -22,7 +22,7 @@ SIGNATURES = {
     "gsr_backward_scratch_bytes": (sz, [i32]),
     "gsr_knn_bytes": (sz, [i32]),
     "gsr_forward_plan": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, f32, f32,
-                               i32, vp, vp, vp, C.POINTER(i64), i32]),
+                               i32, vp, vp, C.POINTER(i64), i32]),
     "gsr_forward_render": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, i32]),
     "gsr_backward": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, f32, f32,
                            vp, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
@@ -31,7 +31,7 @@ SIGNATURES = {
     "gsr_sort_pairs_u64": (i32, [vp, i64, vp, vp, vp, vp, i32, vp]),
     "gsr_debug_geom_views": (i32, [vp, i32, i32, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "gsr_debug_image_views": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
-    "gsr_debug_sorted_keys": (i32, [vp, i64, i32, i32, C.POINTER(vp)]),
+    "gsr_debug_sorted_keys": (i32, [vp, vp, vp, vp, i32, i64, i32, i32, vp]),
 }
 
 ERRORS = {

@@ -16,8 +16,9 @@ int higher_msb(uint32_t n) {
   while (n >> b) ++b;
   return b;
 }
-int sort_passes_for(int W, int H) {
-  const int bits = 32 + higher_msb((uint32_t)num_tiles(W, H));
+// radix passes over the tile id alone (the 32 depth bits are handled by the per-Gaussian depth sort)
+int tile_passes_for(int W, int H) {
+  const int bits = higher_msb((uint32_t)num_tiles(W, H));
   return (bits + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
 }
 
@@ -59,13 +60,12 @@ int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs, int widt
                      const float* opacities, const float* scales, float scale_modifier,
                      const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
                      const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy,
-                     int prefiltered, int* radii, void* geom_ws, void* image_ws, int64_t* num_rendered,
-                     int debug) {
+                     int prefiltered, int* radii, void* geom_ws, int64_t* num_rendered, int debug) {
   if (!num_rendered) return GSR_EINVAL;
   *num_rendered = 0;
   if (P < 0 || width <= 0 || height <= 0) return GSR_EINVAL;
   if (P == 0) return GSR_OK;
-  if (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !geom_ws || !image_ws) return GSR_EINVAL;
+  if (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !geom_ws) return GSR_EINVAL;
   if (!shs && !colors_precomp) return GSR_ENOCOLOR;       // rasterizer_impl.cu:245-248
   if (shs && !colors_precomp && (!campos || sh_coeffs < (sh_degree + 1) * (sh_degree + 1) || sh_degree > 3))
     return GSR_EINVAL;
@@ -75,16 +75,17 @@ int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs, int widt
 
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
-  ImageViews im;
-  carve_image((char*)image_ws, width, height, &im);
   GSR_TRY(check(cudaMemsetAsync((char*)geom_ws + g.zero_begin, 0, g.zero_end - g.zero_begin, st)));
   GSR_TRY(check(launch_preprocess_fwd(st, P, sh_degree, sh_coeffs, means3D, colors_precomp ? nullptr : shs,
                                       colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
                                       viewmatrix, projmatrix, campos, width, height, tan_fovx, tan_fovy,
-                                      prefiltered, radii, g, g.hist, g.tile_diff)));
+                                      prefiltered, radii, g)));
   GSR_TRY(debug_sync(st, debug));
-  GSR_TRY(check(launch_finish_scan(st, num_pre_blocks(P), g.block_sums, g.total, (int)num_tiles(width, height),
-                                   g.tile_diff, im.ranges, g.hist, sort_passes_for(width, height))));
+  // Gaussians into (depth bits, id) order: 4 stable passes, result back in dkeys_a / order_a
+  GSR_TRY(check(sort_pairs_u32_prehist(st, P, g.dkeys_a, g.dkeys_b, g.order_a, g.order_b, 4, g.hist, g.tickets,
+                                       g.lookback, nullptr)));
+  GSR_TRY(debug_sync(st, debug));
+  GSR_TRY(check(launch_chunk_scan(st, P, g.order_a, g)));
   // the one host read of the forward (rasterizer_impl.cu:284)
   HostSlot slot;
   {
@@ -120,13 +121,18 @@ int gsr_forward_render(void* stream, int P, int width, int height, const float* 
   if (num_rendered > 0) {
     BinningViews bv;
     carve_binning((char*)binning_ws, num_rendered, &bv);
+    const int n_tp = tile_passes_for(width, height);
     GSR_TRY(check(cudaMemsetAsync((char*)binning_ws + bv.zero_begin, 0, bv.zero_end - bv.zero_begin, st)));
-    GSR_TRY(check(launch_emit_keys(st, P, g, radii, tiles_x, tiles_y, bv.keys_a, bv.vals_a)));
+    GSR_TRY(check(launch_emit_instances(st, P, g.order_a, g, radii, tiles_x, tiles_y, bv.tkeys_a, bv.vals_a)));
     GSR_TRY(debug_sync(st, debug));
-    GSR_TRY(check(sort_pairs_u64_prehist(st, num_rendered, bv.keys_a, bv.keys_b, bv.vals_a, bv.vals_b,
-                                         sort_passes_for(width, height), g.hist, bv.tickets, bv.lookback,
-                                         point_list)));
+    GSR_TRY(check(launch_tile_digit_hist(st, bv.tkeys_a, num_rendered, n_tp, bv.hist)));
+    GSR_TRY(check(sort_pairs_u32_prehist(st, num_rendered, bv.tkeys_a, bv.tkeys_b, bv.vals_a, bv.vals_b, n_tp,
+                                         bv.hist, bv.tickets, bv.lookback, point_list)));
     GSR_TRY(debug_sync(st, debug));
+    GSR_TRY(check(launch_tile_ranges(st, num_rendered, (n_tp & 1) ? bv.tkeys_b : bv.tkeys_a, im.ranges,
+                                     num_tiles(width, height))));
+  } else {
+    GSR_TRY(check(launch_tile_ranges(st, 0, nullptr, im.ranges, num_tiles(width, height))));
   }
   GSR_TRY(check(launch_render_fwd(st, width, height, im, point_list, g, background, out_color, out_depth,
                                   out_opacity, n_touched)));
@@ -201,12 +207,12 @@ int gsr_sort_pairs_u64(void* stream, int64_t n, const uint64_t* keys_in, const u
   carve_binning((char*)ws, n, &bv);
   const int n_passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
   GSR_TRY(check(cudaMemsetAsync((char*)ws + bv.zero_begin, 0, bv.zero_end - bv.zero_begin, st)));
-  GSR_TRY(check(cudaMemcpyAsync(bv.keys_a, keys_in, 8 * (size_t)n, cudaMemcpyDeviceToDevice, st)));
+  GSR_TRY(check(cudaMemcpyAsync(bv.keys64_a, keys_in, 8 * (size_t)n, cudaMemcpyDeviceToDevice, st)));
   GSR_TRY(check(cudaMemcpyAsync(bv.vals_a, values_in, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st)));
-  GSR_TRY(check(launch_digit_hist_u64(st, bv.keys_a, n, n_passes, bv.hist)));
-  GSR_TRY(check(sort_pairs_u64_prehist(st, n, bv.keys_a, bv.keys_b, bv.vals_a, bv.vals_b, n_passes, bv.hist,
+  GSR_TRY(check(launch_digit_hist_u64(st, bv.keys64_a, n, n_passes, bv.hist)));
+  GSR_TRY(check(sort_pairs_u64_prehist(st, n, bv.keys64_a, bv.keys64_b, bv.vals_a, bv.vals_b, n_passes, bv.hist,
                                        bv.tickets, bv.lookback, values_out)));
-  const uint64_t* sorted = (n_passes & 1) ? bv.keys_b : bv.keys_a;
+  const uint64_t* sorted = (n_passes & 1) ? bv.keys64_b : bv.keys64_a;
   return check(cudaMemcpyAsync(keys_out, sorted, 8 * (size_t)n, cudaMemcpyDeviceToDevice, st));
 }
 
@@ -233,13 +239,15 @@ int gsr_debug_image_views(const void* image_ws, int width, int height, const flo
   return GSR_OK;
 }
 
-int gsr_debug_sorted_keys(const void* binning_ws, int64_t num_rendered, int width, int height,
-                          const uint64_t** keys_sorted) {
-  if (!binning_ws || !keys_sorted) return GSR_EINVAL;
+int gsr_debug_sorted_keys(void* stream, const void* geom_ws, const void* binning_ws, const uint32_t* point_list,
+                          int P, int64_t num_rendered, int width, int height, uint64_t* keys_sorted) {
+  if (!geom_ws || !binning_ws || !keys_sorted || !point_list) return GSR_EINVAL;
+  GeomViews g;
+  carve_geom((char*)geom_ws, P, width, height, &g);
   BinningViews bv;
   carve_binning((char*)binning_ws, num_rendered, &bv);
-  *keys_sorted = (sort_passes_for(width, height) & 1) ? bv.keys_b : bv.keys_a;
-  return GSR_OK;
+  const uint32_t* tk = (tile_passes_for(width, height) & 1) ? bv.tkeys_b : bv.tkeys_a;
+  return check(launch_rebuild_keys((cudaStream_t)stream, num_rendered, tk, point_list, g.rec_a, keys_sorted));
 }
 
 }  // extern "C"

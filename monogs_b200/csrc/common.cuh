@@ -26,11 +26,17 @@ struct GeomViews {
   float4* rec_b;
   float4* rec_c;
   uint32_t* tiles_touched;   // [P]
-  uint32_t* block_sums;      // [ceil(P/256)+1] per-block tile counts -> exclusive offsets
   uint8_t* clamped;          // [3P] SH clamp flags (forward.cu:69-71)
+  // depth-order machinery (forward only)
+  uint32_t* dkeys_a;         // [P] float bits of view depth (0xFFFFFFFF for culled Gaussians)
+  uint32_t* dkeys_b;         // [P]
+  uint32_t* order_a;         // [P] Gaussian ids; after the 4-pass sort: ids in (depth, id) order
+  uint32_t* order_b;         // [P]
+  uint32_t* chunk_offsets;   // [ceil(P/256)+1] exclusive instance offsets of 256-Gaussian chunks, depth order
   // --- small region zeroed at the start of every forward ---
-  uint32_t* hist;            // [SORT_MAX_PASSES*256] radix digit histograms -> exclusive offsets
-  int* tile_diff;            // [tiles+1] +1/-1 difference array over tile ids
+  uint32_t* hist;            // [4*256] depth digit histograms -> exclusive offsets
+  uint32_t* tickets;         // [4]
+  uint32_t* lookback;        // [4 * sort_blocks(P) * 256]
   unsigned long long* total; // [1] num_rendered
   int* error_flag;           // [1]
   size_t zero_begin, zero_end;
@@ -40,25 +46,35 @@ __host__ __device__ inline int num_pre_blocks(int P) { return (P + 255) / 256; }
 __host__ __device__ inline size_t num_tiles(int W, int H) {
   return (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
 }
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_TILE = 256 * 16;  // keys per thread block per pass
+__host__ __device__ inline size_t sort_blocks(int64_t n) { return (size_t)((n + SORT_TILE - 1) / SORT_TILE); }
 
 __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, GeomViews* v) {
+  (void)W; (void)H;
   size_t off = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
   char* a = take(sizeof(float4) * (size_t)P);
   char* b = take(sizeof(float4) * (size_t)P);
   char* c = take(sizeof(float4) * (size_t)P);
   char* t = take(sizeof(uint32_t) * (size_t)P);
-  char* s = take(sizeof(uint32_t) * (size_t)(num_pre_blocks(P) + 1));
   char* cl = take((size_t)3 * P);
+  char* ka = take(4 * (size_t)P); char* kb = take(4 * (size_t)P);
+  char* oa = take(4 * (size_t)P); char* ob = take(4 * (size_t)P);
+  char* co = take(sizeof(uint32_t) * (size_t)(num_pre_blocks(P) + 1));
   size_t zb = off;
-  char* h = take(sizeof(uint32_t) * 8 * 256);
-  char* td = take(sizeof(int) * (num_tiles(W, H) + 1));
+  char* h = take(sizeof(uint32_t) * 4 * 256);
+  char* tk = take(sizeof(uint32_t) * 4);
+  char* lb = take(sizeof(uint32_t) * 4 * sort_blocks(P > 0 ? P : 1) * SORT_RADIX);
   char* tot = take(256);
   size_t ze = off;
   if (v) {
     v->rec_a = (float4*)a; v->rec_b = (float4*)b; v->rec_c = (float4*)c;
-    v->tiles_touched = (uint32_t*)t; v->block_sums = (uint32_t*)s; v->clamped = (uint8_t*)cl;
-    v->hist = (uint32_t*)h; v->tile_diff = (int*)td;
+    v->tiles_touched = (uint32_t*)t; v->clamped = (uint8_t*)cl;
+    v->dkeys_a = (uint32_t*)ka; v->dkeys_b = (uint32_t*)kb; v->order_a = (uint32_t*)oa; v->order_b = (uint32_t*)ob;
+    v->chunk_offsets = (uint32_t*)co;
+    v->hist = (uint32_t*)h; v->tickets = (uint32_t*)tk; v->lookback = (uint32_t*)lb;
     v->total = (unsigned long long*)tot; v->error_flag = (int*)(tot ? tot + 64 : nullptr);
     v->zero_begin = zb; v->zero_end = ze;
   }
@@ -81,25 +97,22 @@ __host__ __device__ inline size_t carve_image(char* base, int W, int H, ImageVie
   return off;
 }
 
-// Radix-sort workspace ("BinningState", rasterizer_impl.h:59-69, minus the
-// final point_list which the caller owns).
-constexpr int SORT_RADIX_BITS = 8;
-constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
-constexpr int SORT_MAX_PASSES = 8;
-constexpr int SORT_TILE = 256 * 16;  // keys per thread block per pass
-
+// Instance binning workspace ("BinningState", rasterizer_impl.h:59-69, minus the final point_list which the
+// caller owns).  Instances are emitted in DEPTH order, so only the tile id (<= 16 bits) is left to sort on.
 struct BinningViews {
-  uint64_t* keys_a;      // [R]
-  uint64_t* keys_b;      // [R]
-  uint32_t* vals_a;      // [R]
+  uint32_t* tkeys_a;     // [R] tile ids, emission (= depth) order
+  uint32_t* tkeys_b;     // [R]
+  uint32_t* vals_a;      // [R] Gaussian ids
   uint32_t* vals_b;      // [R]
-  uint32_t* hist;        // [SORT_MAX_PASSES * SORT_RADIX] global digit histograms
-  uint32_t* tickets;     // [SORT_MAX_PASSES] dynamic block ids
-  uint32_t* lookback;    // [SORT_MAX_PASSES * nblocks * SORT_RADIX] decoupled look-back status
+  uint64_t* keys64_a;    // generic u64 sorter (gsr_sort_pairs_u64 test hook) aliases of the same memory
+  uint64_t* keys64_b;
+  uint32_t* hist;        // [8 * 256] digit histograms -> exclusive offsets
+  uint32_t* tickets;     // [8]
+  uint32_t* lookback;    // [8 * sort_blocks(R) * 256]
   size_t zero_begin;     // byte range [zero_begin, zero_end) must be zeroed before a sort
   size_t zero_end;
 };
-__host__ __device__ inline size_t sort_blocks(int64_t R) { return (size_t)((R + SORT_TILE - 1) / SORT_TILE); }
+constexpr int SORT_MAX_PASSES = 8;
 __host__ __device__ inline size_t carve_binning(char* base, int64_t R, BinningViews* v) {
   size_t off = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
@@ -111,7 +124,8 @@ __host__ __device__ inline size_t carve_binning(char* base, int64_t R, BinningVi
   char* lb = take(4 * (size_t)SORT_MAX_PASSES * sort_blocks(n) * SORT_RADIX);
   size_t ze = off;
   if (v) {
-    v->keys_a = (uint64_t*)ka; v->keys_b = (uint64_t*)kb; v->vals_a = (uint32_t*)va; v->vals_b = (uint32_t*)vb;
+    v->tkeys_a = (uint32_t*)ka; v->tkeys_b = (uint32_t*)kb; v->vals_a = (uint32_t*)va; v->vals_b = (uint32_t*)vb;
+    v->keys64_a = (uint64_t*)ka; v->keys64_b = (uint64_t*)kb;
     v->hist = (uint32_t*)h; v->tickets = (uint32_t*)t; v->lookback = (uint32_t*)lb;
     v->zero_begin = zb; v->zero_end = ze;
   }

@@ -10,15 +10,20 @@ cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const fl
                                   float scale_modifier, const float* rotations, const float* cov3D_precomp,
                                   const float* viewmatrix, const float* projmatrix, const float* campos, int W,
                                   int H, float tan_fovx, float tan_fovy, int prefiltered, int* radii,
-                                  const GeomViews& g, uint32_t* depth_hist, int* tile_diff);
-cudaError_t launch_finish_scan(cudaStream_t st, int n_blocks, uint32_t* block_sums, unsigned long long* total,
-                               int n_tiles, const int* tile_diff, uint2* ranges, uint32_t* hist, int n_passes);
+                                  const GeomViews& g);
+cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g);
 cudaError_t launch_mark_visible(cudaStream_t st, int P, const float* means3D, const float* viewmatrix,
                                 uint8_t* present);
 
 // binning.cu
-cudaError_t launch_emit_keys(cudaStream_t st, int P, const GeomViews& g, const int* radii, int tiles_x,
-                             int tiles_y, uint64_t* keys, uint32_t* vals);
+cudaError_t launch_emit_instances(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g,
+                                  const int* radii, int tiles_x, int tiles_y, uint32_t* tkeys, uint32_t* vals);
+cudaError_t launch_tile_digit_hist(cudaStream_t st, const uint32_t* tkeys, long long n, int n_passes,
+                                   uint32_t* hist);
+cudaError_t launch_tile_ranges(cudaStream_t st, long long L, const uint32_t* tkeys_sorted, uint2* ranges,
+                               size_t n_tiles);
+cudaError_t launch_rebuild_keys(cudaStream_t st, long long L, const uint32_t* tkeys_sorted,
+                                const uint32_t* point_list, const float4* rec_a, uint64_t* keys);
 
 // radix_sort.cu
 cudaError_t sort_pairs_u64_prehist(cudaStream_t st, long long n, uint64_t* keys_a, uint64_t* keys_b,

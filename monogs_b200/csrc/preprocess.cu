@@ -169,14 +169,12 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
                       const float* __restrict__ campos, int W, int H, float tan_fovx, float tan_fovy,
                       float focal_x, float focal_y, int tiles_x, int tiles_y, int prefiltered,
-                      int* __restrict__ radii, GeomViews g, uint32_t* __restrict__ depth_hist /*[4][256]*/,
-                      int* __restrict__ tile_diff /*[tiles+1]*/) {
+                      int* __restrict__ radii, GeomViews g) {
   __shared__ float s_mean[PRE_THREADS * 3];
   __shared__ float s_scale[PRE_THREADS * 3];
   __shared__ float s_rot[PRE_THREADS * 4];
   __shared__ float s_cam[36];
   __shared__ uint32_t s_hist[4 * 256];
-  __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
 
   const int tid = threadIdx.x;
   const long long blk_base = (long long)blockIdx.x * PRE_THREADS;
@@ -274,15 +272,6 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
           rb = make_float4(conx, cony, conz, opac);
           rc = make_float4(rgb.x, rgb.y, rgb.z, ey);
 
-          // depth-digit histograms, weighted by instance count
-          const uint32_t db = __float_as_uint(depth);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) atomicAdd(&s_hist[k * 256 + ((db >> (8 * k)) & 255u)], my_tiles);
-          // tile-id difference array: each covered tile row is one id interval
-          for (unsigned y = rmin.y; y < rmax.y; ++y) {
-            atomicAdd(&tile_diff[y * tiles_x + rmin.x], 1);
-            atomicAdd(&tile_diff[y * tiles_x + rmax.x], -1);
-          }
         }
       }
     }
@@ -291,31 +280,57 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     g.rec_a[idx] = ra;
     g.rec_b[idx] = rb;
     g.rec_c[idx] = rc;
-  }
-
-  // block sum of tile counts (first level of the offset scan)
-  uint32_t v = my_tiles;
+    // depth sort key: positive floats order like their bit patterns; culled Gaussians go last
+    const uint32_t dkey = my_tiles ? __float_as_uint(ra.z) : 0xFFFFFFFFu;
+    g.dkeys_a[idx] = dkey;
+    g.order_a[idx] = (uint32_t)idx;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  if ((tid & 31) == 0) s_warp_sum[tid >> 5] = v;
+    for (int k = 0; k < 4; ++k) atomicAdd(&s_hist[k * 256 + ((dkey >> (8 * k)) & 255u)], 1u);
+  }
   __syncthreads();
-  if (tid == 0) {
-    uint32_t s = 0;
-#pragma unroll
-    for (int w = 0; w < PRE_THREADS / 32; ++w) s += s_warp_sum[w];
-    g.block_sums[blockIdx.x] = s;
-  }
   for (int i = tid; i < 4 * 256; i += PRE_THREADS) {
     uint32_t c = s_hist[i];
-    if (c) atomicAdd(&depth_hist[i], c);
+    if (c) atomicAdd(&g.hist[i], c);
   }
 }
 
-// ---------------------------------------------------------------------------
-// Single-block finishing scan: (1) block_sums -> exclusive offsets + total,
-// (2) tile_diff -> per-tile counts -> tile ranges + tile-digit histograms,
-// (3) every pass' digit histogram -> exclusive digit offsets.
-// ---------------------------------------------------------------------------
+// Exclusive prefix over the 256 bins of each pass' digit histogram (one warp per pass).
+__global__ void digit_offsets4_kernel(uint32_t* hist, int n_passes) {
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (w >= n_passes) return;
+  uint32_t run = 0;
+  for (int c = 0; c < 8; ++c) {
+    uint32_t v = hist[w * 256 + c * 32 + lane];
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    hist[w * 256 + c * 32 + lane] = run + inc - v;
+    run += __shfl_sync(0xffffffffu, inc, 31);
+  }
+}
+
+// Instance count of every 256-Gaussian chunk of the DEPTH-ordered list.
+__global__ void __launch_bounds__(256)
+chunk_sums_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles_touched,
+                  uint32_t* __restrict__ chunk_sums) {
+  __shared__ uint32_t s_w[8];
+  const int s = blockIdx.x * 256 + threadIdx.x;
+  uint32_t v = s < P ? tiles_touched[order[s]] : 0u;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += s_w[w];
+    chunk_sums[blockIdx.x] = t;
+  }
+}
+
 constexpr int SCAN_THREADS = 1024;
 
 GSR_DEVINL uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp, uint32_t& block_total) {
@@ -345,74 +360,21 @@ GSR_DEVINL uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp, uint
   return s_warp[w] + inc - v;
 }
 
+// chunk sums -> exclusive chunk offsets (in place) + total = num_rendered (cub InclusiveSum, rasterizer_impl.cu:280).
 __global__ void __launch_bounds__(SCAN_THREADS)
-finish_scan_kernel(int n_blocks, uint32_t* __restrict__ block_sums, unsigned long long* __restrict__ total,
-                   int n_tiles, const int* __restrict__ tile_diff, uint2* __restrict__ ranges,
-                   uint32_t* __restrict__ hist /*[passes][256]*/, int n_passes) {
+chunk_scan_kernel(int n_chunks, uint32_t* __restrict__ chunk_sums, unsigned long long* __restrict__ total) {
   __shared__ uint32_t s_warp[33];
-  __shared__ uint32_t s_thist[2 * 256];
-  const int tid = threadIdx.x;
-  for (int i = tid; i < 512; i += SCAN_THREADS) s_thist[i] = 0;
-
-  // (1) offsets of the preprocess blocks
   unsigned long long carry = 0;
-  for (int base = 0; base < n_blocks; base += SCAN_THREADS) {
-    int i = base + tid;
-    uint32_t v = i < n_blocks ? block_sums[i] : 0;
+  for (int base = 0; base < n_chunks; base += SCAN_THREADS) {
+    const int i = base + threadIdx.x;
+    const uint32_t v = i < n_chunks ? chunk_sums[i] : 0u;
     uint32_t tot;
-    uint32_t ex = block_exclusive_scan_1024(v, s_warp, tot);
-    if (i < n_blocks) block_sums[i] = (uint32_t)(carry + ex);
+    const uint32_t ex = block_exclusive_scan_1024(v, s_warp, tot);
+    if (i < n_chunks) chunk_sums[i] = (uint32_t)(carry + ex);
     carry += tot;
     __syncthreads();
   }
-  if (tid == 0) { *total = carry; block_sums[n_blocks] = (uint32_t)carry; }
-
-  // (2) tile counts -> ranges, tile-digit histograms (passes 4 and 5)
-  unsigned long long tcarry = 0;
-  uint32_t dcarry = 0;  // modular arithmetic: partial sums of the +1/-1 array may dip below 0
-  for (int base = 0; base < n_tiles; base += SCAN_THREADS) {
-    int i = base + tid;
-    int d = i < n_tiles ? tile_diff[i] : 0;
-    // inclusive scan of the difference array = instances in tile i
-    uint32_t tot;
-    uint32_t exd = block_exclusive_scan_1024((uint32_t)d, s_warp, tot);
-    uint32_t cnt = dcarry + exd + (uint32_t)d;
-    __syncthreads();
-    uint32_t tot2;
-    uint32_t exc = block_exclusive_scan_1024(i < n_tiles ? cnt : 0u, s_warp, tot2);
-    if (i < n_tiles) {
-      uint32_t start = (uint32_t)(tcarry + exc);
-      ranges[i] = cnt ? make_uint2(start, start + cnt) : make_uint2(0u, 0u);
-      if (cnt) {
-        atomicAdd(&s_thist[i & 255], cnt);
-        atomicAdd(&s_thist[256 + ((i >> 8) & 255)], cnt);
-      }
-    }
-    dcarry += tot;
-    tcarry += tot2;
-    __syncthreads();
-  }
-  __syncthreads();
-  if (n_passes > 4) for (int i = tid; i < 256; i += SCAN_THREADS) hist[4 * 256 + i] = s_thist[i];
-  if (n_passes > 5) for (int i = tid; i < 256; i += SCAN_THREADS) hist[5 * 256 + i] = s_thist[256 + i];
-  __syncthreads();
-
-  // (3) exclusive digit offsets, one warp per pass
-  const int w = tid >> 5, lane = tid & 31;
-  if (w < n_passes) {
-    uint32_t run = 0;
-    for (int c = 0; c < 8; ++c) {
-      uint32_t v = hist[w * 256 + c * 32 + lane];
-      uint32_t inc = v;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += t;
-      }
-      hist[w * 256 + c * 32 + lane] = run + inc - v;
-      run += __shfl_sync(0xffffffffu, inc, 31);
-    }
-  }
+  if (threadIdx.x == 0) { *total = carry; chunk_sums[n_chunks] = (uint32_t)carry; }
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ viewmatrix,
@@ -429,21 +391,23 @@ cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const fl
                                   float scale_modifier, const float* rotations, const float* cov3D_precomp,
                                   const float* viewmatrix, const float* projmatrix, const float* campos, int W,
                                   int H, float tan_fovx, float tan_fovy, int prefiltered, int* radii,
-                                  const GeomViews& g, uint32_t* depth_hist, int* tile_diff) {
+                                  const GeomViews& g) {
   const float focal_y = H / (2.0f * tan_fovy);
   const float focal_x = W / (2.0f * tan_fovx);
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   preprocess_fwd_kernel<<<num_pre_blocks(P), PRE_THREADS, 0, st>>>(
       P, D, M, means3D, shs, colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
       viewmatrix, projmatrix, campos, W, H, tan_fovx, tan_fovy, focal_x, focal_y, tiles_x, tiles_y, prefiltered,
-      radii, g, depth_hist, tile_diff);
+      radii, g);
+  digit_offsets4_kernel<<<1, 128, 0, st>>>(g.hist, 4);
   return cudaGetLastError();
 }
 
-cudaError_t launch_finish_scan(cudaStream_t st, int n_blocks, uint32_t* block_sums, unsigned long long* total,
-                               int n_tiles, const int* tile_diff, uint2* ranges, uint32_t* hist, int n_passes) {
-  finish_scan_kernel<<<1, SCAN_THREADS, 0, st>>>(n_blocks, block_sums, total, n_tiles, tile_diff, ranges, hist,
-                                                 n_passes);
+// offsets of the depth-ordered chunks + total; `order` = Gaussian ids in depth order
+cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g) {
+  const int nc = num_pre_blocks(P);
+  chunk_sums_kernel<<<nc, 256, 0, st>>>(P, order, g.tiles_touched, g.chunk_offsets);
+  chunk_scan_kernel<<<1, SCAN_THREADS, 0, st>>>(nc, g.chunk_offsets, g.total);
   return cudaGetLastError();
 }
 

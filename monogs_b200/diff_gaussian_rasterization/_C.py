@@ -74,8 +74,8 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         rc = lib.gsr_forward_plan(st, P, int(degree), M, W, H, _ptr(means3D_c), _ptr(sh_c), _ptr(colors_c),
                                   _ptr(opacity_c), _ptr(scales_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c),
                                   _ptr(view_c), _ptr(proj_c), _ptr(campos_c), float(tan_fovx), float(tan_fovy),
-                                  int(bool(prefiltered)), radii.data_ptr(), geom.data_ptr(), img.data_ptr(),
-                                  C.byref(R), int(bool(debug)))
+                                  int(bool(prefiltered)), radii.data_ptr(), geom.data_ptr(), C.byref(R),
+                                  int(bool(debug)))
         _abi.check(rc, "gsr_forward_plan")
         R = int(R.value)
         point_list = torch.empty(lib.gsr_point_list_bytes(R), dtype=torch.uint8, device=dev)
@@ -161,6 +161,18 @@ def rasterize_gaussians_backward_fused(*args, want=None):
     pose gradient already summed over Gaussians in-kernel (replaces torch.sum at __init__.py:152)."""
     out, _, tau = _backward_impl(*args, want or {}, False)
     return out, tau
+
+
+def debug_sorted_keys(geom, binning, point_list, P, R, W, H):
+    """Test hook: the reference's sorted 64-bit keys (tile << 32 | depth bits) as an int64 tensor [R]."""
+    lib = _abi.load()
+    keys = torch.empty(max(int(R), 0), dtype=torch.int64, device=geom.device)
+    if R > 0:
+        with torch.cuda.device(geom.device):
+            rc = lib.gsr_debug_sorted_keys(_stream(), geom.data_ptr(), binning.data_ptr(), point_list.data_ptr(), int(P),
+                                           int(R), int(W), int(H), keys.data_ptr())
+            _abi.check(rc, "gsr_debug_sorted_keys")
+    return keys
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

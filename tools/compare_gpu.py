@@ -59,15 +59,10 @@ def run_pair(P, kind, seed, anisotropic, layered, timing_iters, log):
     if Ro == Rr:
         pl_o = plist.view(torch.int32)[:Ro]
         res["point_list_mismatch"] = int((pl_o != st["point_list"]).sum())
-        # sorted keys of ours live in the debug-retained binning buffer
         import ctypes as C
         from monogs_b200 import _abi
         lib = _abi.load()
-        kp = C.c_void_p()
-        lib.gsr_debug_sorted_keys(ours.rasterize_gaussians.last_binning.data_ptr(), Ro, cam.W, cam.H, C.byref(kp))
-        base = ours.rasterize_gaussians.last_binning.data_ptr()
-        off = kp.value - base
-        keys_o = ours.rasterize_gaussians.last_binning[off:off + 8 * Ro].view(torch.int64)
+        keys_o = ours.debug_sorted_keys(geom, ours.rasterize_gaussians.last_binning, plist, P, Ro, cam.W, cam.H)
         res["keys_mismatch"] = int((keys_o != st["point_list_keys"]).sum())
         rp = C.c_void_p(); ncp = C.c_void_p(); ftp = C.c_void_p()
         lib.gsr_debug_image_views(img.data_ptr(), cam.W, cam.H, C.byref(ftp), C.byref(ncp), C.byref(rp))
