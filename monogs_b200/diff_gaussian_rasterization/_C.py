@@ -44,6 +44,8 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     lib = _abi.load()
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:58-60
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D: expected a CUDA tensor (this rasterizer has no CPU path)")
     P, H, W = int(means3D.size(0)), int(image_height), int(image_width)
     dev = means3D.device
     fopt = dict(dtype=torch.float32, device=dev)
