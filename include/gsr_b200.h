@@ -133,6 +133,26 @@ int gsr_mark_visible(void* stream, int P, const float* means3D,
 int gsr_knn_dist2(void* stream, int P, const float* points, float* mean_dist2,
                   void* knn_ws);
 
+/* ---- measurement hook ------------------------------------------------------
+ * Per-stage device timing with CUDA events recorded on the CALLER's stream around each kernel group
+ * (bench.py's roofline leg). gsr_profile_enable(1) starts recording; gsr_profile_collect waits for the
+ * recorded events, writes ms_sum[GSR_NUM_STAGES] (total device milliseconds per stage since the last
+ * collect) and launches[GSR_NUM_STAGES] (how many times each stage ran) and clears the record. */
+#define GSR_STAGE_PREPROCESS 0      /* preprocess_fwd_kernel (+ digit offsets)            */
+#define GSR_STAGE_DEPTH_SORT 1      /* 4 onesweep passes over P (depth bits, id)           */
+#define GSR_STAGE_SCAN 2            /* chunk sums + scan -> num_rendered                   */
+#define GSR_STAGE_EMIT 3            /* emit_instances_kernel                               */
+#define GSR_STAGE_TILE_SORT 4       /* tile-digit histogram + 1-2 onesweep passes over R   */
+#define GSR_STAGE_RANGES 5          /* tile_ranges_kernel                                  */
+#define GSR_STAGE_RENDER_FWD 6      /* render_fwd_kernel                                   */
+#define GSR_STAGE_RENDER_BWD 7      /* render_bwd_kernel                                   */
+#define GSR_STAGE_PREPROCESS_BWD 8  /* preprocess_bwd_kernel + tau reduction               */
+#define GSR_NUM_STAGES 9
+int gsr_profile_enable(int on);
+int gsr_profile_collect(double* ms_sum, int* launches);
+/* Kernels launched by this library since it was loaded (always counted). */
+unsigned long long gsr_profile_kernel_launches(void);
+
 /* ---- test / parity hooks --------------------------------------------------*/
 /* Stable LSD radix sort of (u64 key, u32 value) pairs on key bits
  * [0, end_bit) -- the operation cub::DeviceRadixSort::SortPairs performs at

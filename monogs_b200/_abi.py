@@ -28,11 +28,17 @@ SIGNATURES = {
                            vp, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
     "gsr_mark_visible": (i32, [vp, i32, vp, vp, vp, vp]),
     "gsr_knn_dist2": (i32, [vp, i32, vp, vp, vp]),
+    "gsr_profile_enable": (i32, [i32]),
+    "gsr_profile_collect": (i32, [C.POINTER(C.c_double), C.POINTER(i32)]),
+    "gsr_profile_kernel_launches": (C.c_ulonglong, []),
     "gsr_sort_pairs_u64": (i32, [vp, i64, vp, vp, vp, vp, i32, vp]),
     "gsr_debug_geom_views": (i32, [vp, i32, i32, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "gsr_debug_image_views": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "gsr_debug_sorted_keys": (i32, [vp, vp, vp, vp, i32, i64, i32, i32, vp]),
 }
+
+STAGES = ("preprocess", "depth_sort", "scan", "emit", "tile_sort", "ranges", "render_fwd", "render_bwd",
+          "preprocess_bwd")
 
 ERRORS = {
     -1: "GSR_EINVAL: bad argument combination or size",

@@ -3,10 +3,17 @@
 // launches on the caller's stream.  See the header for which reference
 // interface each entry point replaces.
 #include <mutex>
+#include <vector>
 #include "common.cuh"
 #include "kernels.cuh"
 
+#include <atomic>
 using namespace gsr;
+
+namespace gsr {
+static std::atomic<unsigned long long> g_launches{0};
+unsigned long long count_launch(unsigned long long add) { return g_launches.fetch_add(add) + add; }
+}  // namespace gsr
 
 namespace {
 
@@ -36,6 +43,37 @@ int debug_sync(cudaStream_t st, int debug) {
   if (e == cudaSuccess) e = cudaGetLastError();
   return check(e);
 }
+// ---- optional per-stage CUDA-event timing (gsr_profile_*) --------------------------------------------------
+// When enabled, every kernel group of a call is bracketed by two events on the caller's stream; nothing is
+// synchronised until gsr_profile_collect. Used by bench.py to time the dominant kernel inside the timed region.
+struct StageSpan { int stage; cudaEvent_t a, b; };
+std::mutex g_prof_mu;
+bool g_prof_on = false;
+std::vector<StageSpan> g_spans;
+std::vector<cudaEvent_t> g_free_events;
+cudaEvent_t prof_event() {
+  cudaEvent_t e = nullptr;
+  if (!g_free_events.empty()) { e = g_free_events.back(); g_free_events.pop_back(); }
+  else cudaEventCreate(&e);
+  return e;
+}
+struct StageTimer {
+  cudaStream_t st; int idx = -1;
+  StageTimer(cudaStream_t s, int stage) : st(s) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (!g_prof_on) return;
+    StageSpan sp{stage, prof_event(), prof_event()};
+    cudaEventRecord(sp.a, st);
+    g_spans.push_back(sp);
+    idx = (int)g_spans.size() - 1;
+  }
+  ~StageTimer() {
+    if (idx < 0) return;
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (idx < (int)g_spans.size()) cudaEventRecord(g_spans[idx].b, st);
+  }
+};
+
 #define GSR_TRY(expr)                 \
   do {                                \
     int _rc = (expr);                 \
@@ -76,16 +114,25 @@ int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs, int widt
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
   GSR_TRY(check(cudaMemsetAsync((char*)geom_ws + g.zero_begin, 0, g.zero_end - g.zero_begin, st)));
+  {
+  StageTimer tm(st, GSR_STAGE_PREPROCESS);
   GSR_TRY(check(launch_preprocess_fwd(st, P, sh_degree, sh_coeffs, means3D, colors_precomp ? nullptr : shs,
                                       colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
                                       viewmatrix, projmatrix, campos, width, height, tan_fovx, tan_fovy,
                                       prefiltered, radii, g)));
+  }
   GSR_TRY(debug_sync(st, debug));
   // Gaussians into (depth bits, id) order: 4 stable passes, result back in dkeys_a / order_a
+  {
+  StageTimer tm(st, GSR_STAGE_DEPTH_SORT);
   GSR_TRY(check(sort_pairs_u32_prehist(st, P, g.dkeys_a, g.dkeys_b, g.order_a, g.order_b, 4, g.hist, g.tickets,
                                        g.lookback, nullptr)));
+  }
   GSR_TRY(debug_sync(st, debug));
+  {
+  StageTimer tm(st, GSR_STAGE_SCAN);
   GSR_TRY(check(launch_chunk_scan(st, P, g.order_a, g)));
+  }
   // the one host read of the forward (rasterizer_impl.cu:284)
   HostSlot slot;
   {
@@ -123,19 +170,31 @@ int gsr_forward_render(void* stream, int P, int width, int height, const float* 
     carve_binning((char*)binning_ws, num_rendered, &bv);
     const int n_tp = tile_passes_for(width, height);
     GSR_TRY(check(cudaMemsetAsync((char*)binning_ws + bv.zero_begin, 0, bv.zero_end - bv.zero_begin, st)));
+    {
+    StageTimer tm(st, GSR_STAGE_EMIT);
     GSR_TRY(check(launch_emit_instances(st, P, g.order_a, g, radii, tiles_x, tiles_y, bv.tkeys_a, bv.vals_a)));
+    }
     GSR_TRY(debug_sync(st, debug));
+    {
+    StageTimer tm(st, GSR_STAGE_TILE_SORT);
     GSR_TRY(check(launch_tile_digit_hist(st, bv.tkeys_a, num_rendered, n_tp, bv.hist)));
     GSR_TRY(check(sort_pairs_u32_prehist(st, num_rendered, bv.tkeys_a, bv.tkeys_b, bv.vals_a, bv.vals_b, n_tp,
                                          bv.hist, bv.tickets, bv.lookback, point_list)));
+    }
     GSR_TRY(debug_sync(st, debug));
+    {
+    StageTimer tm(st, GSR_STAGE_RANGES);
     GSR_TRY(check(launch_tile_ranges(st, num_rendered, (n_tp & 1) ? bv.tkeys_b : bv.tkeys_a, im.ranges,
                                      num_tiles(width, height))));
+    }
   } else {
     GSR_TRY(check(launch_tile_ranges(st, 0, nullptr, im.ranges, num_tiles(width, height))));
   }
+  {
+  StageTimer tm(st, GSR_STAGE_RENDER_FWD);
   GSR_TRY(check(launch_render_fwd(st, width, height, im, point_list, g, background, out_color, out_depth,
                                   out_opacity, n_touched)));
+  }
   return debug_sync(st, debug);
 }
 
@@ -168,11 +227,13 @@ int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs, int width, i
   carve_backward((char*)scratch, P, &bw);
   GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, sizeof(float) * GRAD_STRIDE * (size_t)P, st)));
   if (num_rendered > 0) {
+    StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
                                     dL_dout_depth, bw.packed)));
     GSR_TRY(debug_sync(st, debug));
   }
   const float* shs_used = colors_precomp ? nullptr : shs;
+  StageTimer tm_pb(st, GSR_STAGE_PREPROCESS_BWD);
   GSR_TRY(check(launch_preprocess_bwd(st, P, sh_degree, sh_coeffs, means3D, radii, shs_used, g.clamped, scales,
                                       rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
                                       projmatrix_raw, campos, width, height, tan_fovx, tan_fovy, bw, dL_dmeans2D,
@@ -209,11 +270,37 @@ int gsr_sort_pairs_u64(void* stream, int64_t n, const uint64_t* keys_in, const u
   GSR_TRY(check(cudaMemsetAsync((char*)ws + bv.zero_begin, 0, bv.zero_end - bv.zero_begin, st)));
   GSR_TRY(check(cudaMemcpyAsync(bv.keys64_a, keys_in, 8 * (size_t)n, cudaMemcpyDeviceToDevice, st)));
   GSR_TRY(check(cudaMemcpyAsync(bv.vals_a, values_in, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st)));
-  GSR_TRY(check(launch_digit_hist_u64(st, bv.keys64_a, n, n_passes, bv.hist)));
-  GSR_TRY(check(sort_pairs_u64_prehist(st, n, bv.keys64_a, bv.keys64_b, bv.vals_a, bv.vals_b, n_passes, bv.hist,
+  GSR_TRY(check(launch_digit_hist_u64(st, bv.keys64_a, n, n_passes, end_bit, bv.hist)));
+  GSR_TRY(check(sort_pairs_u64_prehist(st, n, bv.keys64_a, bv.keys64_b, bv.vals_a, bv.vals_b, n_passes, end_bit, bv.hist,
                                        bv.tickets, bv.lookback, values_out)));
   const uint64_t* sorted = (n_passes & 1) ? bv.keys64_b : bv.keys64_a;
   return check(cudaMemcpyAsync(keys_out, sorted, 8 * (size_t)n, cudaMemcpyDeviceToDevice, st));
+}
+
+int gsr_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_on = on != 0;
+  return GSR_OK;
+}
+
+unsigned long long gsr_profile_kernel_launches(void) { return count_launch(0); }
+
+int gsr_profile_collect(double* ms_sum, int* launches) {
+  if (!ms_sum || !launches) return GSR_EINVAL;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (int i = 0; i < GSR_NUM_STAGES; ++i) { ms_sum[i] = 0.0; launches[i] = 0; }
+  int rc = GSR_OK;
+  for (auto& sp : g_spans) {
+    float ms = 0.f;
+    cudaError_t e = cudaEventSynchronize(sp.b);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, sp.a, sp.b);
+    if (e != cudaSuccess) rc = (int)e;
+    else if (sp.stage >= 0 && sp.stage < GSR_NUM_STAGES) { ms_sum[sp.stage] += ms; launches[sp.stage] += 1; }
+    g_free_events.push_back(sp.a);
+    g_free_events.push_back(sp.b);
+  }
+  g_spans.clear();
+  return rc;
 }
 
 int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, const float** rec_a,

@@ -158,7 +158,7 @@ rebuild_keys_kernel(long long L, const uint32_t* __restrict__ tkeys_sorted, cons
 
 cudaError_t launch_emit_instances(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g,
                                   const int* radii, int tiles_x, int tiles_y, uint32_t* tkeys, uint32_t* vals) {
-  emit_instances_kernel<<<num_pre_blocks(P), DUP_THREADS, 0, st>>>(P, order, g.rec_a, radii, g.tiles_touched,
+  count_launch(); emit_instances_kernel<<<num_pre_blocks(P), DUP_THREADS, 0, st>>>(P, order, g.rec_a, radii, g.tiles_touched,
                                                                   g.chunk_offsets, tiles_x, tiles_y, tkeys, vals);
   return cudaGetLastError();
 }
@@ -167,8 +167,8 @@ cudaError_t launch_tile_digit_hist(cudaStream_t st, const uint32_t* tkeys, long 
                                    uint32_t* hist) {
   if (n <= 0) return cudaSuccess;
   const int blocks = (int)min((long long)148 * 8, (n + 255) / 256);
-  tile_digit_hist_kernel<<<blocks, 256, 0, st>>>(tkeys, n, n_passes, hist);
-  tile_digit_offsets_kernel<<<1, 64, 0, st>>>(hist, n_passes);
+  count_launch(); tile_digit_hist_kernel<<<blocks, 256, 0, st>>>(tkeys, n, n_passes, hist);
+  count_launch(); tile_digit_offsets_kernel<<<1, 64, 0, st>>>(hist, n_passes);
   return cudaGetLastError();
 }
 
@@ -176,14 +176,14 @@ cudaError_t launch_tile_ranges(cudaStream_t st, long long L, const uint32_t* tke
                                size_t n_tiles) {
   cudaError_t e = cudaMemsetAsync(ranges, 0, sizeof(uint2) * n_tiles, st);
   if (e != cudaSuccess || L <= 0) return e;
-  tile_ranges_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>(L, tkeys_sorted, ranges);
+  count_launch(); tile_ranges_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>(L, tkeys_sorted, ranges);
   return cudaGetLastError();
 }
 
 cudaError_t launch_rebuild_keys(cudaStream_t st, long long L, const uint32_t* tkeys_sorted,
                                 const uint32_t* point_list, const float4* rec_a, uint64_t* keys) {
   if (L <= 0) return cudaSuccess;
-  rebuild_keys_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>(L, tkeys_sorted, point_list, rec_a, keys);
+  count_launch(); rebuild_keys_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>(L, tkeys_sorted, point_list, rec_a, keys);
   return cudaGetLastError();
 }
 

@@ -7,6 +7,9 @@
 
 namespace gsr {
 
+// number of kernels launched by this library since load (gsr_profile_kernel_launches; bench.py's gpu_launches)
+unsigned long long count_launch(unsigned long long add = 1);
+
 constexpr int TILE_X = 16;   // binning tile: must equal the reference's BLOCK_X/BLOCK_Y
 constexpr int TILE_Y = 16;   // (config.h:15-17) or radii->tiles->keys->ranges would differ
 constexpr int TILE_PIX = TILE_X * TILE_Y;

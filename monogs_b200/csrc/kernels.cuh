@@ -27,14 +27,15 @@ cudaError_t launch_rebuild_keys(cudaStream_t st, long long L, const uint32_t* tk
 
 // radix_sort.cu
 cudaError_t sort_pairs_u64_prehist(cudaStream_t st, long long n, uint64_t* keys_a, uint64_t* keys_b,
-                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes,
+                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes, int end_bit,
                                    const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
                                    uint32_t* final_vals);
 cudaError_t sort_pairs_u32_prehist(cudaStream_t st, long long n, uint32_t* keys_a, uint32_t* keys_b,
                                    uint32_t* vals_a, uint32_t* vals_b, int n_passes,
                                    const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
                                    uint32_t* final_vals);
-cudaError_t launch_digit_hist_u64(cudaStream_t st, const uint64_t* keys, long long n, int n_passes, uint32_t* hist);
+cudaError_t launch_digit_hist_u64(cudaStream_t st, const uint64_t* keys, long long n, int n_passes, int end_bit,
+                                  uint32_t* hist);
 cudaError_t launch_digit_hist_u32(cudaStream_t st, const uint32_t* keys, long long n, int n_passes, uint32_t* hist);
 
 // render_fwd.cu

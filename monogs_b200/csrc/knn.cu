@@ -253,9 +253,9 @@ cudaError_t launch_knn(cudaStream_t st, int P, const float* points, float* mean_
   carve_knn((char*)ws, P, &v);
   cudaError_t e = cudaMemsetAsync((char*)ws + v.zero_begin, 0, v.zero_end - v.zero_begin, st);
   if (e != cudaSuccess) return e;
-  knn_init_minmax<<<1, 32, 0, st>>>(v.minmax);
-  knn_minmax_kernel<<<min(148 * 4, (P + 255) / 256), 256, 0, st>>>(P, points, v.minmax);
-  knn_morton_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, points, v.minmax, v.codes_a, v.idx_a);
+  count_launch(); knn_init_minmax<<<1, 32, 0, st>>>(v.minmax);
+  count_launch(); knn_minmax_kernel<<<min(148 * 4, (P + 255) / 256), 256, 0, st>>>(P, points, v.minmax);
+  count_launch(); knn_morton_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, points, v.minmax, v.codes_a, v.idx_a);
   e = launch_digit_hist_u32(st, v.codes_a, P, 4, v.hist);
   if (e != cudaSuccess) return e;
   e = sort_pairs_u32_prehist(st, P, v.codes_a, v.codes_b, v.idx_a, v.idx_b, 4, v.hist, v.tickets, v.lookback,
@@ -263,10 +263,10 @@ cudaError_t launch_knn(cudaStream_t st, int P, const float* points, float* mean_
   if (e != cudaSuccess) return e;
   // 4 passes: result is back in the "a" buffers
   const int n_l2 = (P + KNN_L2 - 1) / KNN_L2;
-  knn_gather_boxes_kernel<<<n_l2, 1024, 0, st>>>(P, points, v.idx_a, v.sorted, v.leaf, v.l2);
+  count_launch(); knn_gather_boxes_kernel<<<n_l2, 1024, 0, st>>>(P, points, v.idx_a, v.sorted, v.leaf, v.l2);
   const int n_l3 = (n_l2 + 31) / 32;
-  knn_l3_kernel<<<(n_l3 + 7) / 8, 256, 0, st>>>(n_l2, v.l2, v.l3);
-  knn_query_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, v.sorted, v.leaf, v.l2, v.l3, mean_dist2);
+  count_launch(); knn_l3_kernel<<<(n_l3 + 7) / 8, 256, 0, st>>>(n_l2, v.l2, v.l3);
+  count_launch(); knn_query_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, v.sorted, v.leaf, v.l2, v.l3, mean_dist2);
   return cudaGetLastError();
 }
 

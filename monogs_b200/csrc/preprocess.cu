@@ -395,25 +395,25 @@ cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const fl
   const float focal_y = H / (2.0f * tan_fovy);
   const float focal_x = W / (2.0f * tan_fovx);
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
-  preprocess_fwd_kernel<<<num_pre_blocks(P), PRE_THREADS, 0, st>>>(
+  count_launch(); preprocess_fwd_kernel<<<num_pre_blocks(P), PRE_THREADS, 0, st>>>(
       P, D, M, means3D, shs, colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
       viewmatrix, projmatrix, campos, W, H, tan_fovx, tan_fovy, focal_x, focal_y, tiles_x, tiles_y, prefiltered,
       radii, g);
-  digit_offsets4_kernel<<<1, 128, 0, st>>>(g.hist, 4);
+  count_launch(); digit_offsets4_kernel<<<1, 128, 0, st>>>(g.hist, 4);
   return cudaGetLastError();
 }
 
 // offsets of the depth-ordered chunks + total; `order` = Gaussian ids in depth order
 cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g) {
   const int nc = num_pre_blocks(P);
-  chunk_sums_kernel<<<nc, 256, 0, st>>>(P, order, g.tiles_touched, g.chunk_offsets);
-  chunk_scan_kernel<<<1, SCAN_THREADS, 0, st>>>(nc, g.chunk_offsets, g.total);
+  count_launch(); chunk_sums_kernel<<<nc, 256, 0, st>>>(P, order, g.tiles_touched, g.chunk_offsets);
+  count_launch(); chunk_scan_kernel<<<1, SCAN_THREADS, 0, st>>>(nc, g.chunk_offsets, g.total);
   return cudaGetLastError();
 }
 
 cudaError_t launch_mark_visible(cudaStream_t st, int P, const float* means3D, const float* viewmatrix,
                                 uint8_t* present) {
-  mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means3D, viewmatrix, present);
+  count_launch(); mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means3D, viewmatrix, present);
   return cudaGetLastError();
 }
 

@@ -390,13 +390,13 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
   const float focal_y = H / (2.0f * tan_fovy);
   const float focal_x = W / (2.0f * tan_fovx);
   const int nb = num_pre_blocks(P);
-  preprocess_bwd_kernel<<<nb, PB_THREADS, 0, st>>>(P, D, M, means3D, radii, shs, clamped, scales, rotations,
+  count_launch(); preprocess_bwd_kernel<<<nb, PB_THREADS, 0, st>>>(P, D, M, means3D, radii, shs, clamped, scales, rotations,
                                                    scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
                                                    projmatrix_raw, campos, focal_x, focal_y, tan_fovx, tan_fovy,
                                                    bw.packed, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D,
                                                    dL_dcov3D, dL_dsh, dL_dscales, dL_drots, dL_dtau_pg,
                                                    bw.tau_partial);
-  if (dL_dtau) tau_final_kernel<<<1, 256, 0, st>>>(nb, bw.tau_partial, dL_dtau);
+  if (dL_dtau) { count_launch(); tau_final_kernel<<<1, 256, 0, st>>>(nb, bw.tau_partial, dL_dtau); }
   return cudaGetLastError();
 }
 

@@ -52,7 +52,8 @@ template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS)
 onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, long long n,
-                     int shift, const uint32_t* __restrict__ digit_offsets /*[256] exclusive*/,
+                     int shift, uint32_t dmask /* digit mask: 255, or fewer bits in the pass that reaches end_bit */,
+                     const uint32_t* __restrict__ digit_offsets /*[256] exclusive*/,
                      uint32_t* __restrict__ ticket, uint32_t* __restrict__ lookback /*[nblocks][256]*/) {
   extern __shared__ __align__(16) unsigned char rs_smem_raw[];
   RsSmem<KeyT>& sm = *reinterpret_cast<RsSmem<KeyT>*>(rs_smem_raw);
@@ -87,7 +88,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 #pragma unroll
   for (int i = 0; i < RS_ITEMS; ++i) {
     const int t = wbase + i * 32 + lane;
-    const uint32_t d = (t < tile_n) ? (uint32_t)((key[i] >> shift) & (SORT_RADIX - 1)) : (uint32_t)(SORT_RADIX - 1);
+    const uint32_t d = (t < tile_n) ? (uint32_t)((key[i] >> shift) & dmask) : (uint32_t)(SORT_RADIX - 1);
     const uint32_t peers = __match_any_sync(0xffffffffu, d);
     const uint32_t below = __popc(peers & ((1u << lane) - 1u));
     uint32_t prev = 0;
@@ -152,7 +153,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 #pragma unroll
   for (int i = 0; i < RS_ITEMS; ++i) {
     const int t = wbase + i * 32 + lane;
-    const uint32_t d = (t < tile_n) ? (uint32_t)((key[i] >> shift) & (SORT_RADIX - 1)) : (uint32_t)(SORT_RADIX - 1);
+    const uint32_t d = (t < tile_n) ? (uint32_t)((key[i] >> shift) & dmask) : (uint32_t)(SORT_RADIX - 1);
     const uint32_t pos = sm.bin_start[d] + sm.warp_hist[w][d] + rank[i];
     sm.keys[pos] = key[i];
     sm.vals[pos] = val[i];
@@ -163,7 +164,7 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 #pragma unroll 4
   for (int p = tid; p < tile_n; p += RS_THREADS) {
     const KeyT k = sm.keys[p];
-    const uint32_t d = (uint32_t)((k >> shift) & (SORT_RADIX - 1));
+    const uint32_t d = (uint32_t)((k >> shift) & dmask);
     const uint32_t g = sm.global_base[d] + (uint32_t)p;
     keys_out[g] = k;
     vals_out[g] = sm.vals[p];
@@ -173,13 +174,17 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 // Generic digit histogram over the keys (test hook / kNN path).
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
-digit_hist_kernel(const KeyT* __restrict__ keys, long long n, int n_passes, uint32_t* __restrict__ hist) {
+digit_hist_kernel(const KeyT* __restrict__ keys, long long n, int n_passes, int end_bit,
+                  uint32_t* __restrict__ hist) {
   __shared__ uint32_t s[SORT_MAX_PASSES * SORT_RADIX];
   for (int i = threadIdx.x; i < n_passes * SORT_RADIX; i += 256) s[i] = 0;
   __syncthreads();
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
     KeyT k = keys[i];
-    for (int p = 0; p < n_passes; ++p) atomicAdd(&s[p * SORT_RADIX + (uint32_t)((k >> (8 * p)) & 255)], 1u);
+    for (int p = 0; p < n_passes; ++p) {
+      const int bits = min(8, end_bit - 8 * p);
+      atomicAdd(&s[p * SORT_RADIX + (uint32_t)((k >> (8 * p)) & ((1u << bits) - 1u))], 1u);
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < n_passes * SORT_RADIX; i += 256)
@@ -205,7 +210,7 @@ __global__ void digit_offsets_kernel(uint32_t* hist, int n_passes) {
 
 template <typename KeyT>
 static cudaError_t sort_passes_impl(cudaStream_t st, long long n, KeyT* keys_a, KeyT* keys_b, uint32_t* vals_a,
-                                    uint32_t* vals_b, int n_passes, const uint32_t* digit_offsets,
+                                    uint32_t* vals_b, int n_passes, int end_bit, const uint32_t* digit_offsets,
                                     uint32_t* tickets, uint32_t* lookback, uint32_t* final_vals) {
   static bool attr_set = false;
   const size_t smem = sizeof(RsSmem<KeyT>);
@@ -220,8 +225,9 @@ static cudaError_t sort_passes_impl(cudaStream_t st, long long n, KeyT* keys_a, 
   uint32_t* vin = vals_a; uint32_t* vout = vals_b;
   for (int p = 0; p < n_passes; ++p) {
     uint32_t* vdst = (p == n_passes - 1 && final_vals) ? final_vals : vout;
-    onesweep_pass_kernel<KeyT><<<nblocks, RS_THREADS, smem, st>>>(
-        kin, kout, vin, vdst, n, 8 * p, digit_offsets + p * SORT_RADIX, tickets + p,
+    count_launch(); onesweep_pass_kernel<KeyT><<<nblocks, RS_THREADS, smem, st>>>(
+        kin, kout, vin, vdst, n, 8 * p, (1u << min(8, end_bit - 8 * p)) - 1u, digit_offsets + p * SORT_RADIX,
+        tickets + p,
         lookback + (size_t)p * nblocks * SORT_RADIX);
     KeyT* tk = kin; kin = kout; kout = tk;
     uint32_t* tv = vin; vin = vout; vout = tv;
@@ -230,11 +236,11 @@ static cudaError_t sort_passes_impl(cudaStream_t st, long long n, KeyT* keys_a, 
 }
 
 cudaError_t sort_pairs_u64_prehist(cudaStream_t st, long long n, uint64_t* keys_a, uint64_t* keys_b,
-                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes,
+                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes, int end_bit,
                                    const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
                                    uint32_t* final_vals) {
   if (n <= 0) return cudaSuccess;
-  return sort_passes_impl<uint64_t>(st, n, keys_a, keys_b, vals_a, vals_b, n_passes, digit_offsets, tickets,
+  return sort_passes_impl<uint64_t>(st, n, keys_a, keys_b, vals_a, vals_b, n_passes, end_bit, digit_offsets, tickets,
                                     lookback, final_vals);
 }
 
@@ -243,16 +249,17 @@ cudaError_t sort_pairs_u32_prehist(cudaStream_t st, long long n, uint32_t* keys_
                                    const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
                                    uint32_t* final_vals) {
   if (n <= 0) return cudaSuccess;
-  return sort_passes_impl<uint32_t>(st, n, keys_a, keys_b, vals_a, vals_b, n_passes, digit_offsets, tickets,
+  return sort_passes_impl<uint32_t>(st, n, keys_a, keys_b, vals_a, vals_b, n_passes, 8 * n_passes, digit_offsets,
+                                    tickets,
                                     lookback, final_vals);
 }
 
-cudaError_t launch_digit_hist_u64(cudaStream_t st, const uint64_t* keys, long long n, int n_passes,
+cudaError_t launch_digit_hist_u64(cudaStream_t st, const uint64_t* keys, long long n, int n_passes, int end_bit,
                                   uint32_t* hist) {
   if (n <= 0) return cudaSuccess;
   int blocks = (int)min((long long)148 * 8, (n + 255) / 256);
-  digit_hist_kernel<uint64_t><<<blocks, 256, 0, st>>>(keys, n, n_passes, hist);
-  digit_offsets_kernel<<<1, 256, 0, st>>>(hist, n_passes);
+  count_launch(); digit_hist_kernel<uint64_t><<<blocks, 256, 0, st>>>(keys, n, n_passes, end_bit, hist);
+  count_launch(); digit_offsets_kernel<<<1, 256, 0, st>>>(hist, n_passes);
   return cudaGetLastError();
 }
 
@@ -260,8 +267,8 @@ cudaError_t launch_digit_hist_u32(cudaStream_t st, const uint32_t* keys, long lo
                                   uint32_t* hist) {
   if (n <= 0) return cudaSuccess;
   int blocks = (int)min((long long)148 * 8, (n + 255) / 256);
-  digit_hist_kernel<uint32_t><<<blocks, 256, 0, st>>>(keys, n, n_passes, hist);
-  digit_offsets_kernel<<<1, 256, 0, st>>>(hist, n_passes);
+  count_launch(); digit_hist_kernel<uint32_t><<<blocks, 256, 0, st>>>(keys, n, n_passes, 8 * n_passes, hist);
+  count_launch(); digit_offsets_kernel<<<1, 256, 0, st>>>(hist, n_passes);
   return cudaGetLastError();
 }
 

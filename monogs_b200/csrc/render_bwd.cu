@@ -247,7 +247,7 @@ cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& i
                               const float* dL_dpix_depth, float* packed) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y);
-  render_bwd_kernel<<<grid, RB_THREADS, 0, st>>>(im.ranges, point_list, W, H, tiles_x, bg, g.rec_a, g.rec_b,
+  count_launch(); render_bwd_kernel<<<grid, RB_THREADS, 0, st>>>(im.ranges, point_list, W, H, tiles_x, bg, g.rec_a, g.rec_b,
                                                  g.rec_c, im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, packed);
   return cudaGetLastError();
 }

@@ -164,7 +164,7 @@ cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& i
                               float* out_opacity, int* n_touched) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y);
-  render_fwd_kernel<<<grid, RF_THREADS, 0, st>>>(im.ranges, point_list, W, H, tiles_x, g.rec_a, g.rec_b, g.rec_c,
+  count_launch(); render_fwd_kernel<<<grid, RF_THREADS, 0, st>>>(im.ranges, point_list, W, H, tiles_x, g.rec_a, g.rec_b, g.rec_c,
                                                  bg, im.final_T, im.n_contrib, out_color, out_depth, out_opacity,
                                                  n_touched);
   return cudaGetLastError();
