@@ -1,0 +1,602 @@
+#!/usr/bin/env python
+"""bench.py -- rasterize fwd+bwd iterations/s (BASELINE.json's metric) on N B200s of one node.
+
+  python bench.py [--gpus N --steps K --warmup W] [--impl ours|reference] [--workload headline|c2|c3|c4|c5]
+
+A "step" is one pass of the hot path over one keyframe: rasterizer forward (preprocess, depth sort, instance
+emit, tile sort, ranges, render) + backward (render backward, fused preprocess backward incl. the SE(3) pose
+gradient) of the synthetic 640x480 / 1 M-Gaussian scene (`headline`, the config the metric is quoted on).
+At N > 1 the step is the sharded MAPPING WINDOW: N keyframes of the same Gaussian set, one per
+GPU, with the Gaussian-gradient allreduce (NCCL) inside the timed step -- per-GPU work fixed, scaling "weak";
+`value` = keyframe fwd+bwd iterations of all ranks / max-over-ranks device time.
+
+  value        inputs resident in HBM, straight through the C ABI (include/gsr_b200.h), CUDA-event timed
+  e2e          the same step through the public API (GaussianRasterizer autograd, what MonoGS's render()
+               calls) with the Gaussian parameters and targets in PINNED HOST memory: H2D copies, L1 loss,
+               backward and the D2H read of loss + pose gradient are inside the timed region
+  roofline     the dominant kernel, timed live with CUDA events on the launching stream (gsr_profile_*),
+               against MEASURED_PEAKS.json's HBM copy bandwidth, algorithmic bytes per DESIGN.md
+  cpu_baseline the CPU oracle port (oracle/cpu_ref.cpp, OpenMP) on the box's host cores, one bounded sample
+  --impl reference   the UNMODIFIED reference CUDA rasterizer (oracle/_ref, rebuilt for sm_100a) on the same
+               workload and metric; falls back to the CPU oracle port when oracle/_ref did not travel
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+WORKLOADS = {
+    # name: (P, camera kind, description)
+    "headline": (1_000_000, "tum", "640x480, 1M Gaussians, rasterize fwd+bwd incl. pose grads (metric config)"),
+    "c2": (100_000, "tum", "640x480, 100k Gaussians, tracking-step shape"),
+    "c3": (500_000, "replica", "1200x680, 500k Gaussians, mapping keyframe"),
+    "c4": (2_000_000, "replica", "1200x680, 2M Gaussians, mapping keyframe"),
+    "c5": (4_000_000, "hd", "1920x1080, 4M Gaussians, stress"),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="headline", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def dist_setup(n_gpus):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        torch.cuda.set_device(0)
+    return rank, world, local
+
+
+# ------------------------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md "clocks line")
+# ------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.split(",") for r in Path(self.f.name).read_text().splitlines() if r.count(",") >= 8]
+        os.unlink(self.f.name)
+        sm, reasons = [], set()
+        for r in rows:
+            r = [x.strip() for x in r]
+            try:
+                sm.append(float(r[1]))
+                out["sm_max_mhz"] = float(r[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if sm:
+            sm.sort()
+            out["sm_mhz"] = sm[len(sm) // 2]
+        out["reasons"] = sorted(reasons)
+        out["samples"] = len(sm)
+        return out
+
+
+# ------------------------------------------------------------------------------------------------------------
+# workload
+# ------------------------------------------------------------------------------------------------------------
+class Workload:
+    """Synthetic scene (monogs_b200.synth, seed 0) + one camera per rank on a 30 cm arc + fixed loss gradients."""
+
+    def __init__(self, name, rank, world, dev):
+        from monogs_b200 import synth
+        self.name = name
+        self.P, self.kind, self.desc = WORKLOADS[name]
+        cams = synth.arc_cameras(self.kind, max(world, 1)) if world > 1 else [
+            synth.make_camera(self.kind, rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))]
+        self.cam = cams[rank if world > 1 else 0]
+        centre = synth.make_camera(self.kind)
+        self.host = synth.make_scene(self.P, centre, seed=0, device="cpu")          # same Gaussians on every rank
+        self.dev = dev
+        self.scene = {k: v.to(dev) for k, v in self.host.items()}
+        self.view, self.proj, self.proj_raw, self.campos = self.cam.matrices(dev)
+        self.bg = torch.tensor([0.1, 0.2, 0.3], device=dev)
+        self.W, self.H = self.cam.W, self.cam.H
+        g = torch.Generator().manual_seed(7 + rank)
+        self.dcol = (torch.randn(3, self.H, self.W, generator=g) / (self.H * self.W)).to(dev)
+        self.ddep = (torch.randn(1, self.H, self.W, generator=g) / (self.H * self.W)).to(dev)
+        self.gt_image, self.gt_depth = synth.make_targets(self.cam, seed=rank, device="cpu")
+
+    @property
+    def N(self):
+        return self.W * self.H
+
+
+GRAD_COLS = (("means3D", 3), ("colors", 3), ("opacity", 1), ("scales", 3), ("rotations", 4))
+
+
+class OursDeviceStep:
+    """fwd+bwd straight through the C ABI with every buffer resident in HBM and reused across steps."""
+
+    def __init__(self, wl: Workload, world):
+        from monogs_b200 import _abi
+        self.lib = _abi.load()
+        self.wl, self.world = wl, world
+        lib, P, W, H, dev = self.lib, wl.P, wl.W, wl.H, wl.dev
+        u8 = lambda n: torch.empty(max(int(n), 256), dtype=torch.uint8, device=dev)
+        self.radii = torch.empty(P, dtype=torch.int32, device=dev)
+        self.n_touched = torch.zeros(P, dtype=torch.int32, device=dev)
+        self.geom, self.img = u8(lib.gsr_geom_bytes(P, W, H)), u8(lib.gsr_image_bytes(W, H))
+        self.scratch = u8(lib.gsr_backward_scratch_bytes(P))
+        self.binning, self.plist, self.cap = None, None, -1
+        self.color = torch.empty(3, H, W, device=dev)
+        self.depth = torch.empty(1, H, W, device=dev)
+        self.opacity = torch.empty(1, H, W, device=dev)
+        # one flat gradient buffer (column blocks) = the allreduce payload of the mapping window
+        self.flat = torch.empty(sum(n for _, n in GRAD_COLS) * P, device=dev)
+        self.g, o = {}, 0
+        for name, n in GRAD_COLS:
+            self.g[name] = self.flat[o:o + n * P].view(P, n)
+            o += n * P
+        self.means2D = torch.empty(P, 3, device=dev)
+        self.tau = torch.zeros(6, device=dev)
+        self.R = 0
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def step(self):
+        lib, wl, sc = self.lib, self.wl, self.wl.scene
+        P, W, H = wl.P, wl.W, wl.H
+        st = self._stream()
+        R = C.c_int64(0)
+        self.n_touched.zero_()
+        rc = lib.gsr_forward_plan(st, P, 0, 0, W, H, sc["means3D"].data_ptr(), None, sc["colors"].data_ptr(),
+                                  sc["opacities"].data_ptr(), sc["scales"].data_ptr(), 1.0,
+                                  sc["rotations"].data_ptr(), None, wl.view.data_ptr(), wl.proj.data_ptr(),
+                                  wl.campos.data_ptr(), wl.cam.tanfovx, wl.cam.tanfovy, 0, self.radii.data_ptr(),
+                                  self.geom.data_ptr(), C.byref(R), 0)
+        assert rc == 0, rc
+        R = int(R.value)
+        if R > self.cap:  # grow-only, like the reference's resizable byte tensors
+            self.cap = int(R * 1.25) + 1024
+            self.binning = torch.empty(lib.gsr_binning_bytes(self.cap), dtype=torch.uint8, device=wl.dev)
+            self.plist = torch.empty(lib.gsr_point_list_bytes(self.cap), dtype=torch.uint8, device=wl.dev)
+        rc = lib.gsr_forward_render(st, P, W, H, wl.bg.data_ptr(), self.radii.data_ptr(), self.geom.data_ptr(),
+                                    self.img.data_ptr(), self.binning.data_ptr(), self.plist.data_ptr(), R,
+                                    self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr(),
+                                    self.n_touched.data_ptr(), 0)
+        assert rc == 0, rc
+        g = self.g
+        rc = lib.gsr_backward(st, P, 0, 0, W, H, wl.bg.data_ptr(), sc["means3D"].data_ptr(), None,
+                              sc["colors"].data_ptr(), sc["scales"].data_ptr(), 1.0, sc["rotations"].data_ptr(), None,
+                              wl.view.data_ptr(), wl.proj.data_ptr(), wl.proj_raw.data_ptr(), wl.campos.data_ptr(),
+                              wl.cam.tanfovx, wl.cam.tanfovy, self.radii.data_ptr(), self.geom.data_ptr(),
+                              self.img.data_ptr(), self.plist.data_ptr(), R, wl.dcol.data_ptr(), wl.ddep.data_ptr(),
+                              self.scratch.data_ptr(), self.means2D.data_ptr(), g["colors"].data_ptr(),
+                              g["opacity"].data_ptr(), g["means3D"].data_ptr(), None, None, g["scales"].data_ptr(),
+                              g["rotations"].data_ptr(), None, self.tau.data_ptr(), 0)
+        assert rc == 0, rc
+        if self.world > 1:
+            dist.all_reduce(self.flat)  # the one exchange step of the sharded mapping window
+        self.R = R
+
+    def units(self):
+        """P, V, R, consumed instances (sum over tiles of the largest n_contrib) and N of the last step."""
+        wl = self.wl
+        nc_p, ft_p, rg_p = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self.lib.gsr_debug_image_views(self.img.data_ptr(), wl.W, wl.H, C.byref(ft_p), C.byref(nc_p), C.byref(rg_p))
+        off = nc_p.value - self.img.data_ptr()
+        nc = self.img[off:off + 4 * wl.N].view(torch.int32).view(wl.H, wl.W).float()
+        tiles = torch.nn.functional.max_pool2d(nc[None, None], 16, ceil_mode=True)
+        return dict(P=wl.P, V=int((self.radii > 0).sum()), R=int(self.R), R_consumed=int(tiles.sum()), N=wl.N)
+
+
+class RefDeviceStep:
+    """The unmodified reference CUDA rasterizer (oracle/_ref) on the same inputs, same outputs."""
+
+    def __init__(self, wl: Workload, world):
+        from oracle import ref_cuda
+        self.ref, self.wl, self.world = ref_cuda, wl, world
+        ref_cuda.load()
+        self.R = 0
+        self.radii = None
+
+    def step(self):
+        wl, sc, ref = self.wl, self.wl.scene, self.ref
+        e = torch.empty(0, device=wl.dev)
+        R, col, radii, _, _, _, dep, opa, nt = ref.rasterize_gaussians(
+            wl.bg, sc["means3D"], sc["colors"], sc["opacities"], sc["scales"], sc["rotations"], 1.0, e, wl.view,
+            wl.proj, wl.proj_raw, wl.cam.tanfovx, wl.cam.tanfovy, wl.H, wl.W, e, 0, wl.campos, False, False)
+        out = ref.rasterize_gaussians_backward(
+            wl.bg, sc["means3D"], radii, sc["colors"], sc["scales"], sc["rotations"], 1.0, e, wl.view, wl.proj,
+            wl.proj_raw, wl.cam.tanfovx, wl.cam.tanfovy, wl.dcol, wl.ddep, e, 0, wl.campos, None, R, None, None, False)
+        tau = out[8].sum(0)  # diff_gaussian_rasterization/__init__.py:152-154
+        if self.world > 1:
+            flat = torch.cat([out[3].reshape(-1), out[1].reshape(-1), out[2].reshape(-1), out[6].reshape(-1),
+                              out[7].reshape(-1)])
+            dist.all_reduce(flat)
+        self.R, self.radii, self.tau = R, radii, tau
+
+    def units(self):
+        wl = self.wl
+        return dict(P=wl.P, V=int((self.radii > 0).sum()), R=int(self.R), R_consumed=None, N=wl.N)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# end to end through the public API, inputs in pinned host memory
+# ------------------------------------------------------------------------------------------------------------
+class _RefFunction(torch.autograd.Function):
+    """Autograd node over oracle/_ref with the data flow of the reference's own Python wrapper
+    (diff_gaussian_rasterization/__init__.py:48-171): forward, backward, torch.sum of dL_dtau."""
+
+    @staticmethod
+    def forward(ctx, ref, wl, means3D, means2D, colors, opacities, scales, rotations, theta, rho):
+        e = torch.empty(0, device=means3D.device)
+        R, col, radii, _, _, _, dep, opa, nt = ref.rasterize_gaussians(
+            wl.bg, means3D, colors, opacities, scales, rotations, 1.0, e, wl.view, wl.proj, wl.proj_raw,
+            wl.cam.tanfovx, wl.cam.tanfovy, wl.H, wl.W, e, 0, wl.campos, False, False)
+        ctx.ref, ctx.wl, ctx.R = ref, wl, R
+        ctx.save_for_backward(means3D, colors, scales, rotations, radii)
+        ctx.mark_non_differentiable(radii, nt)
+        return col, radii, dep, opa, nt
+
+    @staticmethod
+    def backward(ctx, g_col, g_radii, g_dep, g_opa, g_nt):
+        means3D, colors, scales, rotations, radii = ctx.saved_tensors
+        wl = ctx.wl
+        e = torch.empty(0, device=means3D.device)
+        if g_dep is None:
+            g_dep = torch.zeros(1, wl.H, wl.W, device=means3D.device)
+        o = ctx.ref.rasterize_gaussians_backward(
+            wl.bg, means3D, radii, colors, scales, rotations, 1.0, e, wl.view, wl.proj, wl.proj_raw, wl.cam.tanfovx,
+            wl.cam.tanfovy, g_col.contiguous(), g_dep.contiguous(), e, 0, wl.campos, None, ctx.R, None, None, False)
+        tau = torch.sum(o[8].view(-1, 6), dim=0)
+        return None, None, o[3], o[0], o[1], o[2], o[6], o[7], tau[3:].view(1, -1), tau[:3].view(1, -1)
+
+
+class E2EStep:
+    """One mapping-shaped iteration the way a MonoGS caller does it: parameters arrive from PINNED HOST memory,
+    render through the public API, 0.9 L1(rgb) + 0.1 L1(depth) loss (utils/slam_utils.py:101-146 without the masks),
+    backward, and the loss + pose gradient are read back to the host."""
+
+    NAMES = ("means3D", "colors", "opacities", "scales", "rotations")
+
+    def __init__(self, wl: Workload, world, impl):
+        self.wl, self.world, self.impl = wl, world, impl
+        self.pinned = {k: wl.host[k].contiguous().pin_memory() for k in self.NAMES}
+        self.pinned_img = wl.gt_image.contiguous().pin_memory()
+        self.pinned_dep = wl.gt_depth.contiguous().pin_memory()
+        self.dev_buf = {k: torch.empty_like(wl.host[k], device=wl.dev) for k in self.NAMES}
+        self.dev_img = torch.empty_like(wl.gt_image, device=wl.dev)
+        self.dev_dep = torch.empty_like(wl.gt_depth, device=wl.dev)
+        self.host_out = torch.empty(7, dtype=torch.float32).pin_memory()
+        self.h2d = sum(t.numel() * 4 for t in self.pinned.values()) + (self.pinned_img.numel() + self.pinned_dep.numel()) * 4
+        self.d2h = 7 * 4
+        if impl == "ours":
+            from monogs_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+            s = GaussianRasterizationSettings(wl.H, wl.W, wl.cam.tanfovx, wl.cam.tanfovy, wl.bg, 1.0, wl.view, wl.proj,
+                                              wl.proj_raw, 0, wl.campos, False, False)
+            self.rasterizer = GaussianRasterizer(s)
+        else:
+            from oracle import ref_cuda
+            self.ref = ref_cuda
+
+    def step(self):
+        wl = self.wl
+        leaves = {}
+        for k in self.NAMES:
+            self.dev_buf[k].copy_(self.pinned[k], non_blocking=True)
+            leaves[k] = self.dev_buf[k].detach().requires_grad_(True)
+        self.dev_img.copy_(self.pinned_img, non_blocking=True)
+        self.dev_dep.copy_(self.pinned_dep, non_blocking=True)
+        means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        theta = torch.zeros(3, device=wl.dev, requires_grad=True)
+        rho = torch.zeros(3, device=wl.dev, requires_grad=True)
+        if self.impl == "ours":
+            color, radii, depth, opacity, n_touched = self.rasterizer(
+                means3D=leaves["means3D"], means2D=means2D, shs=None, colors_precomp=leaves["colors"],
+                opacities=leaves["opacities"], scales=leaves["scales"], rotations=leaves["rotations"],
+                cov3D_precomp=None, theta=theta, rho=rho)
+        else:
+            color, radii, depth, opacity, n_touched = _RefFunction.apply(
+                self.ref, wl, leaves["means3D"], means2D, leaves["colors"], leaves["opacities"], leaves["scales"],
+                leaves["rotations"], theta, rho)
+        loss = 0.9 * (color - self.dev_img).abs().mean() + 0.1 * (depth - self.dev_dep).abs().mean()
+        loss.backward()
+        if self.world > 1:
+            flat = torch.cat([leaves[k].grad.reshape(-1) for k in self.NAMES])
+            dist.all_reduce(flat)
+        out = torch.cat([loss.detach().view(1), rho.grad.view(-1), theta.grad.view(-1)])
+        self.host_out.copy_(out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller reads the loss / pose gradient on the host
+        return float(self.host_out[0])
+
+
+# ------------------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle port on the host cores (bounded sample)
+# ------------------------------------------------------------------------------------------------------------
+def cpu_baseline(wl: Workload, budget_s=25.0):
+    from oracle import cpu_oracle as co
+    n = lambda t: t.detach().cpu().numpy()
+    h = wl.host
+    view, proj, proj_raw, campos = [n(t) for t in (wl.view, wl.proj, wl.proj_raw, wl.campos)]
+    dcol, ddep, bg = n(wl.dcol), n(wl.ddep), n(wl.bg)
+    co.load()
+    times = []
+    t_begin = time.perf_counter()
+    while True:
+        t0 = time.perf_counter()
+        f = co.forward(n(h["means3D"]), n(h["scales"]), n(h["rotations"]), n(h["opacities"]), n(h["colors"]), view,
+                       proj, campos, wl.W, wl.H, wl.cam.tanfovx, wl.cam.tanfovy, bg)
+        co.backward(f, n(h["means3D"]), n(h["scales"]), n(h["rotations"]), view, proj, proj_raw, wl.W, wl.H,
+                    wl.cam.tanfovx, wl.cam.tanfovy, bg, dcol, ddep)
+        times.append(time.perf_counter() - t0)
+        if len(times) >= 3 or time.perf_counter() - t_begin > budget_s * 0.6:
+            break
+    best = min(times)
+    cores = int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))
+    return {"value": 1.0 / best, "unit": "it/s", "cores": cores, "kind": "port",
+            "sample": f"{len(times)} full fwd+bwd iteration(s) of the same {wl.name} workload "
+                      f"({wl.W}x{wl.H}, P={wl.P}) with oracle/cpu_ref.cpp (OpenMP), best of {len(times)}"}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# timing helpers
+# ------------------------------------------------------------------------------------------------------------
+def barrier(world):
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(x, world, dev):
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def timed_steps(step_fn, steps, warmup, world, dev, flush):
+    """W untimed steps, then K steps each bracketed by its own CUDA-event pair on the launching stream, the L2
+    flushed (256 MiB write, outside the event pairs) before every step. Returns device seconds for K steps
+    (max over ranks), bracketed by barrier + synchronize on both sides."""
+    for _ in range(warmup):
+        flush.zero_()
+        step_fn()
+    barrier(world)
+    pairs = []
+    for _ in range(steps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step_fn()
+        b.record()
+        pairs.append((a, b))
+    barrier(world)
+    ms = sum(a.elapsed_time(b) for a, b in pairs)
+    return max_over_ranks(ms / 1e3, world, dev)
+
+
+def stage_bytes(u):
+    """Algorithmic bytes per launch of each stage (SURVEY 8d terms; DESIGN.md 'Kernels and rooflines').
+    Render stages use the instances actually consumed (early termination skips the rest of a tile's list)."""
+    P, V, R, N = u["P"], u["V"], u["R"], u["N"]
+    Rc = u["R_consumed"] if u.get("R_consumed") is not None else R
+    return {
+        "preprocess": 44 * P + 8 * P + 52 * V,
+        "depth_sort": 16 * P,
+        "scan": 8 * P,
+        "emit": 12 * R,
+        "tile_sort": 24 * R,
+        "ranges": 8 * R,
+        "render_fwd": 44 * Rc + 28 * N + 4 * P,
+        "render_bwd": 84 * Rc + 24 * N,
+        "preprocess_bwd": 164 * V + 48 * P,
+    }
+
+
+def step_bytes(u):
+    """Whole fwd+bwd iteration, the single formula of SURVEY 8d / BASELINE.md section 4 (with the full R)."""
+    P, V, R, N = u["P"], u["V"], u["R"], u["N"]
+    return (64 * P + 52 * V + 88 * R + 28 * N) + (84 * R + 24 * N + 164 * V + 48 * P)
+
+
+def measured_peak():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(kernel):
+    """dram bytes per launch of the dominant kernel from the committed ncu --set full summary, if present."""
+    p = ROOT / "profiles" / "traffic.json"
+    if p.exists():
+        try:
+            return json.loads(p.read_text()).get(kernel)
+        except Exception:
+            return None
+    return None
+
+
+def main():
+    a = parse_args()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the rasterizer has no CPU path (use gpurun)")
+    rank, world, local = dist_setup(a.gpus)
+    dev = torch.device("cuda", local if world > 1 else 0)
+    wl_name = a.workload
+
+    # ---- which implementation is measured --------------------------------------------------------------------
+    impl, ref_kind = a.impl, None
+    if impl == "reference":
+        from oracle import ref_cuda
+        if ref_cuda.available():
+            ref_kind = "reference"  # the unmodified reference CUDA kernels, rebuilt for sm_100a
+        else:
+            ref_kind = "port"       # oracle/_ref did not travel: the CPU oracle port on the host cores
+    if impl == "reference" and ref_kind == "port":
+        if rank == 0:
+            wl = Workload(wl_name, 0, 1, dev)
+            cb = cpu_baseline(wl, budget_s=60.0)
+            line = {"impl": "reference", "metric": "rasterize fwd+bwd it/s", "value": cb["value"], "unit": "it/s",
+                    "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 / cb["value"],
+                    "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                    "data": "synthetic", "config": {"workload": wl_name, "detail": wl.desc},
+                    "cpu_baseline": cb,
+                    "e2e": {"value": cb["value"], "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            print(json.dumps(line), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    wl = Workload(wl_name, rank, world, dev)
+    stepper = OursDeviceStep(wl, world) if impl == "ours" else RefDeviceStep(wl, world)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    lib = None
+    if impl == "ours":
+        from monogs_b200 import _abi
+        lib = _abi.load()
+
+    # ---- device-resident value --------------------------------------------------------------------------------
+    sampler = ClockSampler(local if world > 1 else 0) if rank == 0 else None
+    launches0 = lib.gsr_profile_kernel_launches() if lib else 0
+    for _ in range(a.warmup):
+        flush.zero_()
+        stepper.step()
+    barrier(world)
+    if lib:
+        lib.gsr_profile_collect((C.c_double * 9)(), (C.c_int * 9)())  # drop anything recorded so far
+        lib.gsr_profile_enable(1)
+        launches0 = lib.gsr_profile_kernel_launches()
+    secs = timed_steps(stepper.step, a.steps, 0, world, dev, flush)
+    gpu_launches = None
+    stage_ms, stage_n = None, None
+    if lib:
+        gpu_launches = int(lib.gsr_profile_kernel_launches() - launches0)
+        ms_arr, n_arr = (C.c_double * 9)(), (C.c_int * 9)()
+        lib.gsr_profile_enable(0)
+        rc = lib.gsr_profile_collect(ms_arr, n_arr)
+        assert rc == 0, rc
+        stage_ms, stage_n = list(ms_arr), list(n_arr)
+    clocks = sampler.stop() if sampler else None
+    units = stepper.units()
+    value = world * a.steps / secs
+
+    # ---- end to end ---------------------------------------------------------------------------------------------
+    e2e = None
+    if not a.no_e2e:
+        es = E2EStep(wl, world, impl)
+        k_e2e = max(3, min(a.steps, 20))
+        for _ in range(3):
+            es.step()
+        barrier(world)
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        w0 = time.perf_counter()
+        t0.record()
+        for _ in range(k_e2e):
+            es.step()
+        t1.record()
+        barrier(world)
+        wall = time.perf_counter() - w0
+        dev_s = t0.elapsed_time(t1) / 1e3
+        e2e_s = max_over_ranks(max(dev_s, 0.0), world, dev)
+        e2e = {"value": world * k_e2e / e2e_s, "unit": "it/s", "h2d_bytes_per_step": es.h2d,
+               "d2h_bytes_per_step": es.d2h, "steps": k_e2e, "wall_s": round(wall, 4),
+               "api": "GaussianRasterizer.forward + loss.backward()" if impl == "ours" else
+                      "reference CUDA via oracle/_ref + loss.backward()"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    line = {
+        "metric": "rasterize fwd+bwd it/s", "value": value, "unit": "it/s", "n_gpus": world, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": secs / a.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl_name, "detail": wl.desc, "image": [wl.W, wl.H], "gaussians": wl.P,
+                   "l2": "256 MiB flush write before every timed step (outside the event pairs)",
+                   "multi_gpu": "mapping window: one keyframe per GPU, NCCL allreduce of the [P,14] Gaussian-gradient "
+                                "buffer inside the step" if world > 1 else "single keyframe",
+                   "units": units},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches,
+    }
+    if impl == "reference":
+        line["impl"] = "reference"
+        line["cpu_baseline"] = {"value": value, "unit": "it/s", "cores": 0, "kind": "reference",
+                                "sample": "the reference has no CPU implementation of this path: these are its own "
+                                          "CUDA kernels (oracle/_ref, unmodified sources rebuilt for sm_100a) on the GPU"}
+        line["gpu_launches"] = None
+    else:
+        sb = stage_bytes(units)
+        from monogs_b200._abi import STAGES
+        per_launch_ms = {s: (stage_ms[i] / stage_n[i] if stage_n[i] else 0.0) for i, s in enumerate(STAGES)}
+        dom = max(per_launch_ms, key=per_launch_ms.get)
+        achieved = sb[dom] / (per_launch_ms[dom] * 1e-3) / 1e9 if per_launch_ms[dom] > 0 else 0.0
+        line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                            "frac": achieved / peak, "traffic": ncu_traffic(dom), "peak_source": peak_src,
+                            "algorithmic_bytes_per_launch": sb[dom], "ms_per_launch": per_launch_ms[dom]}
+        line["stages_ms_per_step"] = {s: round(per_launch_ms[s], 5) for s in STAGES}
+        line["stages_frac_of_hbm_peak"] = {s: round(sb[s] / (per_launch_ms[s] * 1e-3) / 1e9 / peak, 4)
+                                           if per_launch_ms[s] > 0 else None for s in STAGES}
+        tb = step_bytes(units)
+        line["step_roofline"] = {"algorithmic_bytes": tb, "achieved": tb / (secs / a.steps) / 1e9, "unit": "GB/s",
+                                 "frac": tb / (secs / a.steps) / 1e9 / peak}
+        if world == 1 and not a.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(wl)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

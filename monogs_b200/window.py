@@ -1,0 +1,167 @@
+"""Mapping-window sharding across the GPUs of one box (the only stage of the path that shards).
+
+The reference's `Mapper.optimize_map` (utils/slam_mapper.py:244-500) renders every keyframe of the window,
+sums the mapping losses and calls ONE backward, so the Gaussian-parameter gradients are sums over keyframes
+(:273-322, :394).  Keyframes are independent rasterizer problems over the same Gaussian set, so here keyframe k
+is rendered on rank k mod G and the per-rank partial sums meet in ONE exchange step:
+
+  * allreduce(sum) of a flat [P, 14+2] fp32 buffer: d/d(xyz 3, colour 3, opacity 1, scale 3, rotation 4) plus the
+    two densification accumulators (sum of ||d mean2D[:, :2]|| and the visibility count,
+    gaussian_model.py:888-892) -- NCCL over NVLink/NVSwitch on GPUs, gloo in the CPU tests;
+  * allreduce(max) of the screen radii (max_radii_2d, slam_mapper.py:453-457);
+  * pose gradients (theta/rho) stay with the rank that owns the keyframe (they belong to one keyframe).
+
+One process per GPU (torchrun); the Gaussian parameters are replicated and every rank applies the identical
+optimizer step afterwards, so no broadcast is needed.  The render backend is injected (`render_fn`) so the
+host logic is testable on CPU with world_size 2 / gloo; the product default is the sm_100a rasterizer.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+PARAM_COLUMNS = (("means3D", 3), ("colors", 3), ("opacities", 1), ("scales", 3), ("rotations", 4))
+AUX_COLUMNS = (("grad2d_norm", 1), ("vis_count", 1))
+N_COLS = sum(n for _, n in PARAM_COLUMNS) + sum(n for _, n in AUX_COLUMNS)  # 16
+
+
+def shard_keyframes(n_keyframes: int, world_size: int, rank: int) -> List[int]:
+    """Indices of the window's keyframes rendered by `rank` (round robin: k -> k mod G)."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError(f"bad rank/world_size {rank}/{world_size}")
+    return list(range(rank, n_keyframes, world_size))
+
+
+def column_slices() -> Dict[str, slice]:
+    out, c = {}, 0
+    for name, n in PARAM_COLUMNS + AUX_COLUMNS:
+        out[name] = slice(c, c + n)
+        c += n
+    return out
+
+
+@dataclass
+class KeyframeResult:
+    """What one keyframe contributes (the per-keyframe items of slam_mapper.py:319-322)."""
+    index: int
+    radii: torch.Tensor                 # i32[P]
+    n_touched: torch.Tensor             # i32[P]
+    grad_tau: Optional[torch.Tensor]    # f32[6] = [rho | theta], stays local
+    loss: Optional[torch.Tensor] = None
+
+
+@dataclass
+class WindowStepResult:
+    grads: Dict[str, torch.Tensor]            # summed over ALL keyframes of the window (every rank identical)
+    grad2d_norm: torch.Tensor                 # f32[P]  sum over keyframes of ||dL/dmean2D[:, :2]||
+    vis_count: torch.Tensor                   # f32[P]  number of keyframes in which the Gaussian is visible
+    max_radii: torch.Tensor                   # i32[P]
+    local: List[KeyframeResult] = field(default_factory=list)
+
+
+# render_fn(keyframe_index, params, flat_out) -> KeyframeResult.  It must ADD this keyframe's Gaussian-parameter
+# gradients and aux columns into flat_out[P, N_COLS] (fp32, on the parameters' device).
+RenderFn = Callable[[int, Dict[str, torch.Tensor], torch.Tensor], KeyframeResult]
+
+
+class MappingWindow:
+    def __init__(self, render_fn: RenderFn, group: Optional[dist.ProcessGroup] = None):
+        self.render_fn = render_fn
+        self.group = group
+        self._flat: Optional[torch.Tensor] = None
+        self._radii: Optional[torch.Tensor] = None
+
+    @property
+    def world_size(self) -> int:
+        return dist.get_world_size(self.group) if dist.is_available() and dist.is_initialized() else 1
+
+    @property
+    def rank(self) -> int:
+        return dist.get_rank(self.group) if dist.is_available() and dist.is_initialized() else 0
+
+    def _buffers(self, P: int, device) -> None:
+        if self._flat is None or self._flat.shape[0] != P or self._flat.device != torch.device(device):
+            self._flat = torch.empty(P, N_COLS, dtype=torch.float32, device=device)
+            self._radii = torch.empty(P, dtype=torch.int32, device=device)
+
+    def step(self, params: Dict[str, torch.Tensor], n_keyframes: int) -> WindowStepResult:
+        """One window iteration: local keyframes -> partial sums -> exchange. `params` maps the names of
+        PARAM_COLUMNS to replicated tensors."""
+        P = int(params["means3D"].shape[0])
+        dev = params["means3D"].device
+        self._buffers(P, dev)
+        flat, radii = self._flat, self._radii
+        flat.zero_()
+        radii.zero_()
+        local = []
+        for k in shard_keyframes(n_keyframes, self.world_size, self.rank):
+            r = self.render_fn(k, params, flat)
+            torch.maximum(radii, r.radii.to(torch.int32), out=radii)
+            local.append(r)
+        if self.world_size > 1:
+            # the one exchange step of the path; async so the max-reduce overlaps the sum-reduce
+            h1 = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            h2 = dist.all_reduce(radii, op=dist.ReduceOp.MAX, group=self.group, async_op=True)
+            h1.wait()
+            h2.wait()
+        sl = column_slices()
+        grads = {name: flat[:, sl[name]] for name, _ in PARAM_COLUMNS}
+        return WindowStepResult(grads=grads, grad2d_norm=flat[:, sl["grad2d_norm"]].squeeze(1),
+                                vis_count=flat[:, sl["vis_count"]].squeeze(1), max_radii=radii, local=local)
+
+
+def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
+                        loss_grad: Optional[Callable] = None) -> RenderFn:
+    """Product backend: the sm_100a rasterizer through the `_C` mirror (C ABI), writing its Gaussian gradients
+    straight into column blocks of a per-keyframe staging buffer that is then added to `flat`.
+
+    cameras[k] is a synth.Camera-like object with .matrices(device), .W, .H, .tanfovx, .tanfovy; targets[k] =
+    (gt_image[3,H,W], gt_depth[1,H,W]).  loss_grad(color, depth, gt_image, gt_depth) -> (loss, dL_dcolor,
+    dL_ddepth); default = the mapping loss of utils/slam_utils.py:101-146 (0.9 L1 rgb + 0.1 L1 depth over gt_depth>0).
+    """
+    from .diff_gaussian_rasterization import _C
+
+    cached = {}
+
+    def default_loss_grad(color, depth, gt_image, gt_depth):
+        diff = color - gt_image
+        n_rgb = diff.numel()
+        valid = gt_depth > 0
+        n_d = valid.sum().clamp_min(1)
+        ddiff = (depth - gt_depth) * valid
+        loss = 0.9 * diff.abs().sum() / n_rgb + 0.1 * ddiff.abs().sum() / n_d
+        return loss, 0.9 * torch.sign(diff) / n_rgb, 0.1 * torch.sign(ddiff) / n_d
+
+    lg = loss_grad or default_loss_grad
+    sl = column_slices()
+
+    def render(k: int, params: Dict[str, torch.Tensor], flat: torch.Tensor) -> KeyframeResult:
+        cam = cameras[k]
+        dev = flat.device
+        if k not in cached:
+            cached[k] = cam.matrices(dev)
+        view, proj, proj_raw, campos = cached[k]
+        e = torch.empty(0, device=dev)
+        R, color, radii, geom, plist, img, depth, opacity, n_touched = _C.rasterize_gaussians(
+            bg, params["means3D"], params["colors"], params["opacities"], params["scales"], params["rotations"], 1.0,
+            e, view, proj, proj_raw, cam.tanfovx, cam.tanfovy, cam.H, cam.W, e, 0, campos, False, False)
+        gt_image, gt_depth = targets[k]
+        loss, dcol, ddep = lg(color, depth, gt_image, gt_depth)
+        out, tau = _C.rasterize_gaussians_backward_fused(
+            bg, params["means3D"], radii, params["colors"], params["scales"], params["rotations"], 1.0, e, view, proj,
+            proj_raw, cam.tanfovx, cam.tanfovy, dcol.contiguous(), ddep.contiguous(), e, 0, campos, geom, R, plist,
+            img, False, want=dict(sh=False, cov3D=False))
+        flat[:, sl["means3D"]] += out["means3D"]
+        flat[:, sl["colors"]] += out["colors"]
+        flat[:, sl["opacities"]] += out["opacity"]
+        flat[:, sl["scales"]] += out["scales"]
+        flat[:, sl["rotations"]] += out["rotations"]
+        vis = radii > 0
+        flat[:, sl["grad2d_norm"]] += (out["means2D"][:, :2].norm(dim=1, keepdim=True) * vis[:, None])
+        flat[:, sl["vis_count"]] += vis[:, None].float()
+        return KeyframeResult(index=k, radii=radii, n_touched=n_touched, grad_tau=tau, loss=loss)
+
+    return render
