@@ -19,6 +19,10 @@ ncufull)
   CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
   $CMD > gpurun_out/plain2.log 2>&1 && \
   ncu --set full --clock-control none --import-source on -k regex:render_ -s 2 -c 4 -f -o gpurun_out/prof_render $CMD > gpurun_out/ncu_full.log 2>&1 ;;
+ncuother)
+  CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
+  $CMD > gpurun_out/plain3.log 2>&1 && \
+  ncu --set full --clock-control none --import-source on -k regex:"onesweep|preprocess_|emit_|tile_|chunk_" -s 14 -c 14 -f -o gpurun_out/prof_other $CMD > gpurun_out/ncu_other.log 2>&1 ;;
 esac
 done
 tail -n 3 gpurun_out/pytest_gpu.log gpurun_out/smoke.log gpurun_out/bench_ours.err gpurun_out/bench_ref.err 2>/dev/null
