@@ -182,9 +182,15 @@ class OursDeviceStep:
         self.means2D = torch.empty(P, 3, device=dev)
         self.tau = torch.zeros(6, device=dev)
         self.R = 0
+        self.rows, self.chunks = None, None
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def _grow(self, R):  # grow-only, like the reference's resizable byte tensors
+        self.cap = int(R * 1.25) + 1024
+        self.binning = torch.empty(self.lib.gsr_binning_bytes(self.cap), dtype=torch.uint8, device=self.wl.dev)
+        self.plist = torch.empty(self.lib.gsr_point_list_bytes(self.cap), dtype=torch.uint8, device=self.wl.dev)
 
     def step(self):
         lib, wl, sc = self.lib, self.wl, self.wl.scene
@@ -192,35 +198,70 @@ class OursDeviceStep:
         st = self._stream()
         R = C.c_int64(0)
         self.n_touched.zero_()
-        rc = lib.gsr_forward_plan(st, P, 0, 0, W, H, sc["means3D"].data_ptr(), None, sc["colors"].data_ptr(),
-                                  sc["opacities"].data_ptr(), sc["scales"].data_ptr(), 1.0,
-                                  sc["rotations"].data_ptr(), None, wl.view.data_ptr(), wl.proj.data_ptr(),
-                                  wl.campos.data_ptr(), wl.cam.tanfovx, wl.cam.tanfovy, 0, self.radii.data_ptr(),
-                                  self.geom.data_ptr(), C.byref(R), 0)
-        assert rc == 0, rc
+        if self.cap < 0:  # first call of this shape: two-phase forward sizes the instance buffers
+            rc = lib.gsr_forward_plan(st, P, 0, 0, W, H, sc["means3D"].data_ptr(), None, sc["colors"].data_ptr(),
+                                      sc["opacities"].data_ptr(), sc["scales"].data_ptr(), 1.0,
+                                      sc["rotations"].data_ptr(), None, wl.view.data_ptr(), wl.proj.data_ptr(),
+                                      wl.campos.data_ptr(), wl.cam.tanfovx, wl.cam.tanfovy, 0, self.radii.data_ptr(),
+                                      self.geom.data_ptr(), C.byref(R), 0)
+            assert rc == 0, rc
+            self._grow(int(R.value))
+            rc = lib.gsr_forward_render(st, P, W, H, wl.bg.data_ptr(), self.radii.data_ptr(), self.geom.data_ptr(),
+                                        self.img.data_ptr(), self.binning.data_ptr(), self.plist.data_ptr(),
+                                        int(R.value), self.color.data_ptr(), self.depth.data_ptr(),
+                                        self.opacity.data_ptr(), self.n_touched.data_ptr(), 0)
+            assert rc == 0, rc
+        else:             # steady state: one bubble-free call for the remembered capacity
+            rc = lib.gsr_forward(st, P, 0, 0, W, H, wl.bg.data_ptr(), sc["means3D"].data_ptr(), None,
+                                 sc["colors"].data_ptr(), sc["opacities"].data_ptr(), sc["scales"].data_ptr(), 1.0,
+                                 sc["rotations"].data_ptr(), None, wl.view.data_ptr(), wl.proj.data_ptr(),
+                                 wl.campos.data_ptr(), wl.cam.tanfovx, wl.cam.tanfovy, 0, self.radii.data_ptr(),
+                                 self.geom.data_ptr(), self.img.data_ptr(), self.binning.data_ptr(),
+                                 self.plist.data_ptr(), self.cap, self.color.data_ptr(), self.depth.data_ptr(),
+                                 self.opacity.data_ptr(), self.n_touched.data_ptr(), C.byref(R), 0)
+            assert rc == 0, rc  # (a GSR_ECAPACITY retry is not needed here: the scene is fixed)
         R = int(R.value)
-        if R > self.cap:  # grow-only, like the reference's resizable byte tensors
-            self.cap = int(R * 1.25) + 1024
-            self.binning = torch.empty(lib.gsr_binning_bytes(self.cap), dtype=torch.uint8, device=wl.dev)
-            self.plist = torch.empty(lib.gsr_point_list_bytes(self.cap), dtype=torch.uint8, device=wl.dev)
-        rc = lib.gsr_forward_render(st, P, W, H, wl.bg.data_ptr(), self.radii.data_ptr(), self.geom.data_ptr(),
-                                    self.img.data_ptr(), self.binning.data_ptr(), self.plist.data_ptr(), R,
-                                    self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr(),
-                                    self.n_touched.data_ptr(), 0)
-        assert rc == 0, rc
-        g = self.g
-        rc = lib.gsr_backward(st, P, 0, 0, W, H, wl.bg.data_ptr(), sc["means3D"].data_ptr(), None,
-                              sc["colors"].data_ptr(), sc["scales"].data_ptr(), 1.0, sc["rotations"].data_ptr(), None,
-                              wl.view.data_ptr(), wl.proj.data_ptr(), wl.proj_raw.data_ptr(), wl.campos.data_ptr(),
-                              wl.cam.tanfovx, wl.cam.tanfovy, self.radii.data_ptr(), self.geom.data_ptr(),
-                              self.img.data_ptr(), self.plist.data_ptr(), R, wl.dcol.data_ptr(), wl.ddep.data_ptr(),
-                              self.scratch.data_ptr(), self.means2D.data_ptr(), g["colors"].data_ptr(),
-                              g["opacity"].data_ptr(), g["means3D"].data_ptr(), None, None, g["scales"].data_ptr(),
-                              g["rotations"].data_ptr(), None, self.tau.data_ptr(), 0)
-        assert rc == 0, rc
         if self.world > 1:
-            dist.all_reduce(self.flat)  # the one exchange step of the sharded mapping window
+            self._backward_window(st, R)
+        else:
+            g = self.g
+            rc = lib.gsr_backward(st, P, 0, 0, W, H, wl.bg.data_ptr(), sc["means3D"].data_ptr(), None,
+                                  sc["colors"].data_ptr(), sc["scales"].data_ptr(), 1.0, sc["rotations"].data_ptr(),
+                                  None, wl.view.data_ptr(), wl.proj.data_ptr(), wl.proj_raw.data_ptr(),
+                                  wl.campos.data_ptr(), wl.cam.tanfovx, wl.cam.tanfovy, self.radii.data_ptr(),
+                                  self.geom.data_ptr(), self.img.data_ptr(), self.plist.data_ptr(), R,
+                                  wl.dcol.data_ptr(), wl.ddep.data_ptr(), self.scratch.data_ptr(),
+                                  self.means2D.data_ptr(), g["colors"].data_ptr(), g["opacity"].data_ptr(),
+                                  g["means3D"].data_ptr(), None, None, g["scales"].data_ptr(),
+                                  g["rotations"].data_ptr(), None, self.tau.data_ptr(), 0)
+            assert rc == 0, rc
         self.R = R
+
+    def _backward_window(self, st, R):
+        """Sharded mapping window (monogs_b200/window.py): per-pixel half, then the per-Gaussian half range by
+        range into 64-byte window rows; each finished range goes to an async NCCL allreduce (the one exchange step
+        of the path) while the next range is computed; the step ends when the last allreduce has completed."""
+        from monogs_b200.window import window_chunks
+        lib, wl, sc = self.lib, self.wl, self.wl.scene
+        P, W, H = wl.P, wl.W, wl.H
+        if self.rows is None:
+            self.rows = torch.empty(P, 16, device=wl.dev)
+            self.chunks = window_chunks(P, 4)
+        rc = lib.gsr_backward_render(st, P, W, H, wl.bg.data_ptr(), self.geom.data_ptr(), self.img.data_ptr(),
+                                     self.plist.data_ptr(), R, wl.dcol.data_ptr(), wl.ddep.data_ptr(),
+                                     self.scratch.data_ptr(), 0)
+        assert rc == 0, rc
+        works = []
+        for (p0, p1) in self.chunks:
+            rc = lib.gsr_backward_rows(st, P, p0, p1, W, H, sc["means3D"].data_ptr(), sc["scales"].data_ptr(), 1.0,
+                                       sc["rotations"].data_ptr(), wl.view.data_ptr(), wl.proj.data_ptr(),
+                                       wl.proj_raw.data_ptr(), wl.cam.tanfovx, wl.cam.tanfovy, self.radii.data_ptr(),
+                                       self.geom.data_ptr(), self.scratch.data_ptr(), self.rows.data_ptr(), 0,
+                                       self.means2D.data_ptr(), self.tau.data_ptr(), 0)
+            assert rc == 0, rc
+            works.append(dist.all_reduce(self.rows[p0:p1], async_op=True))
+        for w in works:
+            w.wait()  # the current stream waits for the exchange: it is part of the timed step
 
     def units(self):
         """P, V, R, consumed instances (sum over tiles of the largest n_contrib) and N of the last step."""
@@ -582,8 +623,10 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl_name, "detail": wl.desc, "image": [wl.W, wl.H], "gaussians": wl.P,
                    "l2": "256 MiB flush write before every timed step (outside the event pairs)",
-                   "multi_gpu": "mapping window: one keyframe per GPU, NCCL allreduce of the [P,14] Gaussian-gradient "
-                                "buffer inside the step" if world > 1 else "single keyframe",
+                   "multi_gpu": ("mapping window: one keyframe per GPU; NCCL allreduce of the [P,16] window rows "
+                                 "(14 gradient + 2 densification columns) inside the step, issued per Gaussian "
+                                 "range and overlapped with the per-Gaussian backward of the next range")
+                                if world > 1 else "single keyframe",
                    "units": units},
         "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches,
     }

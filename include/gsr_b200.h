@@ -54,6 +54,7 @@ extern "C" {
 #define GSR_ENOCOV (-3)     /* neither scales+rotations nor cov3D_precomp  */
 #define GSR_EPREFILTER (-4) /* prefiltered=1 but a point was culled        */
 #define GSR_EOVERFLOW (-5)  /* num_rendered does not fit the index type    */
+#define GSR_ECAPACITY (-6)  /* gsr_forward: num_rendered > capacity; re-run gsr_forward_render with *num_rendered */
 
 /* Library / build identification ("sm_100a", version). */
 const char* gsr_version(void);
@@ -98,6 +99,23 @@ int gsr_forward_render(void* stream, int P, int width, int height,
                        float* out_color, float* out_depth, float* out_opacity,
                        int* n_touched, int debug);
 
+/* ---- forward, single call without a GPU bubble ---------------------------
+ * Same work as gsr_forward_plan + gsr_forward_render, but the instance-level kernels are enqueued for a
+ * caller-chosen `capacity` (binning_ws / point_list sized with gsr_binning_bytes(capacity) /
+ * gsr_point_list_bytes(capacity)) and read the actual count from device memory, so the host wait for
+ * num_rendered (rasterizer_impl.cu:284) overlaps the rest of the forward. Returns GSR_ECAPACITY when
+ * *num_rendered > capacity: the per-Gaussian state in geom_ws is valid, the images are not -- allocate for
+ * *num_rendered and call gsr_forward_render. n_touched must be zero on entry (and re-zeroed before that retry). */
+int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs /*M*/, int width, int height,
+                const float* background, const float* means3D, const float* shs,
+                const float* colors_precomp, const float* opacities, const float* scales,
+                float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                const float* viewmatrix, const float* projmatrix, const float* campos,
+                float tan_fovx, float tan_fovy, int prefiltered, int* radii, void* geom_ws,
+                void* image_ws, void* binning_ws, uint32_t* point_list, int64_t capacity,
+                float* out_color, float* out_depth, float* out_opacity, int* n_touched,
+                int64_t* num_rendered, int debug);
+
 /* ---- backward -----------------------------------------------------------
  * Outputs (all optional except where noted; NULL = not wanted):
  *   dL_dmeans2D[P,3], dL_dcolors[P,3], dL_dopacity[P,1], dL_dmeans3D[P,3],
@@ -123,6 +141,28 @@ int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs,
                  float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
                  float* dL_dscales, float* dL_drotations,
                  float* dL_dtau_per_gaussian, float* dL_dtau, int debug);
+
+/* ---- backward for the sharded mapping window (monogs_b200/window.py; no reference counterpart: it forms
+ * the sums loss.backward() makes over the window's keyframes, utils/slam_mapper.py:273-322,394) ------------
+ * gsr_backward_render: the per-pixel half (zeroes the partial-gradient scratch, then the backward tile renderer).
+ * gsr_backward_rows:    the per-Gaussian half on the Gaussian range [p_begin, p_end) (p_begin a multiple of
+ *   256), written -- or ADDED when accumulate != 0 -- into 64-byte window rows
+ *   rows[P][16] = { dL/dxyz 3 | dL/drgb 3 | dL/dopacity 1 | dL/dscale 3 | dL/drotation 4 |
+ *                   ||dL/dmean2D[:2]|| (densification statistic, gaussian_model.py:888-892) | visible (radii>0) }.
+ *   A Gaussian range is one contiguous slice of `rows`, so the caller can hand finished ranges to an
+ *   allreduce while later ranges are still being computed. Ranges must be issued in ascending order; the
+ *   call with p_end == P also writes dL_dtau[6] (rho | theta). dL_dmeans2D[P,3] is optional.
+ *   Precomputed colours + scales/rotations only (what MonoGS's mapper renders with). */
+int gsr_backward_render(void* stream, int P, int width, int height, const float* background,
+                        const void* geom_ws, const void* image_ws, const uint32_t* point_list,
+                        int64_t num_rendered, const float* dL_dout_color, const float* dL_dout_depth,
+                        void* scratch, int debug);
+int gsr_backward_rows(void* stream, int P, int p_begin, int p_end, int width, int height,
+                      const float* means3D, const float* scales, float scale_modifier,
+                      const float* rotations, const float* viewmatrix, const float* projmatrix,
+                      const float* projmatrix_raw, float tan_fovx, float tan_fovy, const int* radii,
+                      const void* geom_ws, void* scratch, float* rows, int accumulate,
+                      float* dL_dmeans2D, float* dL_dtau, int debug);
 
 /* present[P] (uint8 0/1) = p_view.z > 0.2  (auxiliary.h:139-164). */
 int gsr_mark_visible(void* stream, int P, const float* means3D,

@@ -24,8 +24,13 @@ SIGNATURES = {
     "gsr_forward_plan": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, f32, f32,
                                i32, vp, vp, C.POINTER(i64), i32]),
     "gsr_forward_render": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, i32]),
+    "gsr_forward": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, f32, f32, i32,
+                          vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, C.POINTER(i64), i32]),
     "gsr_backward": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, f32, f32,
                            vp, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
+    "gsr_backward_render": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, i64, vp, vp, vp, i32]),
+    "gsr_backward_rows": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, f32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, i32,
+                                vp, vp, i32]),
     "gsr_mark_visible": (i32, [vp, i32, vp, vp, vp, vp]),
     "gsr_knn_dist2": (i32, [vp, i32, vp, vp, vp]),
     "gsr_profile_enable": (i32, [i32]),
@@ -40,12 +45,15 @@ SIGNATURES = {
 STAGES = ("preprocess", "depth_sort", "scan", "emit", "tile_sort", "ranges", "render_fwd", "render_bwd",
           "preprocess_bwd")
 
+GSR_ECAPACITY = -6
+
 ERRORS = {
     -1: "GSR_EINVAL: bad argument combination or size",
     -2: "GSR_ENOCOLOR: neither shs nor colors_precomp given",
     -3: "GSR_ENOCOV: neither scales+rotations nor cov3D_precomp given",
     -4: "GSR_EPREFILTER: point is filtered although prefiltered is set",
     -5: "GSR_EOVERFLOW: num_rendered exceeds 2^30 instances",
+    -6: "GSR_ECAPACITY: num_rendered exceeds the capacity passed to gsr_forward",
 }
 
 _lib = None

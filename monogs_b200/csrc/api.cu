@@ -23,12 +23,6 @@ int higher_msb(uint32_t n) {
   while (n >> b) ++b;
   return b;
 }
-// radix passes over the tile id alone (the 32 depth bits are handled by the per-Gaussian depth sort)
-int tile_passes_for(int W, int H) {
-  const int bits = higher_msb((uint32_t)num_tiles(W, H));
-  return (bits + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
-}
-
 struct HostSlot {
   unsigned long long total;
   int error_flag;
@@ -93,6 +87,115 @@ size_t gsr_binning_bytes(int64_t R) { return carve_binning(nullptr, R, nullptr);
 size_t gsr_backward_scratch_bytes(int P) { return carve_backward(nullptr, P, nullptr); }
 size_t gsr_knn_bytes(int P) { return knn_workspace_bytes(P); }
 
+// ---- forward building blocks (enqueue only; no host synchronisation) ---------------------------------------
+static int check_forward_args(int P, int sh_degree, int sh_coeffs, int width, int height, const float* means3D,
+                              const float* shs, const float* colors_precomp, const float* opacities,
+                              const float* scales, const float* rotations, const float* cov3D_precomp,
+                              const float* viewmatrix, const float* projmatrix, const float* campos,
+                              const int* radii, const void* geom_ws) {
+  if (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !geom_ws) return GSR_EINVAL;
+  if (!shs && !colors_precomp) return GSR_ENOCOLOR;       // rasterizer_impl.cu:245-248
+  if (shs && !colors_precomp && (!campos || sh_coeffs < (sh_degree + 1) * (sh_degree + 1) || sh_degree > 3))
+    return GSR_EINVAL;
+  if (!cov3D_precomp && (!scales || !rotations)) return GSR_ENOCOV;
+  if (num_tiles(width, height) > 65536) return GSR_EINVAL;  // tile id must fit two 8-bit digits
+  if ((width + TILE_X - 1) / TILE_X > 65535 || (height + TILE_Y - 1) / TILE_Y > 65535) return GSR_EINVAL;
+  return GSR_OK;
+}
+
+// preprocess + depth sort of the Gaussians + rectangles into depth order + scan -> g.total (device)
+static int enqueue_plan(cudaStream_t st, int P, int sh_degree, int sh_coeffs, int width, int height,
+                        const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+                        const float* scales, float scale_modifier, const float* rotations,
+                        const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                        const float* campos, float tan_fovx, float tan_fovy, int prefiltered, int* radii,
+                        char* geom_ws, const GeomViews& g, int debug) {
+  GSR_TRY(check(cudaMemsetAsync(geom_ws + g.zero_begin, 0, g.zero_end - g.zero_begin, st)));
+  {
+    StageTimer tm(st, GSR_STAGE_PREPROCESS);
+    GSR_TRY(check(launch_preprocess_fwd(st, P, sh_degree, sh_coeffs, means3D, colors_precomp ? nullptr : shs,
+                                        colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
+                                        viewmatrix, projmatrix, campos, width, height, tan_fovx, tan_fovy,
+                                        prefiltered, radii, g)));
+  }
+  GSR_TRY(debug_sync(st, debug));
+  {  // Gaussians into (depth bits, id) order: 4 stable passes, result back in dkeys_a / order_a
+    StageTimer tm(st, GSR_STAGE_DEPTH_SORT);
+    const SortPlan plan = make_sort_plan(32);
+    GSR_TRY(check(sort_pairs_u32_prehist(st, P, nullptr, g.dkeys_a, g.dkeys_b, g.order_a, g.order_b, plan, g.hist,
+                                         g.tickets, g.lookback, nullptr)));
+  }
+  GSR_TRY(debug_sync(st, debug));
+  {
+    StageTimer tm(st, GSR_STAGE_SCAN);
+    GSR_TRY(check(launch_chunk_scan(st, P, g.order_a, g)));
+  }
+  return GSR_OK;
+}
+
+static SortPlan tile_sort_plan(int W, int H) { return make_sort_plan(higher_msb((uint32_t)num_tiles(W, H))); }
+
+// instance emit + tile sort + ranges + render. `cap` bounds the instances written; the actual count is read
+// from n_dev (device) when given, else it IS cap.
+static int enqueue_render(cudaStream_t st, int P, int width, int height, const float* background,
+                          const GeomViews& g, const ImageViews& im, char* binning_ws, uint32_t* point_list,
+                          long long cap, const unsigned long long* n_dev, float* out_color, float* out_depth,
+                          float* out_opacity, int* n_touched, int debug) {
+  const int tiles_x = (width + TILE_X - 1) / TILE_X;
+  if (cap > 0) {
+    BinningViews bv;
+    carve_binning(binning_ws, cap, &bv);
+    const SortPlan plan = tile_sort_plan(width, height);
+    GSR_TRY(check(cudaMemsetAsync(binning_ws + bv.zero_begin, 0, bv.zero_end(plan.n_passes) - bv.zero_begin, st)));
+    {
+      StageTimer tm(st, GSR_STAGE_EMIT);
+      GSR_TRY(check(launch_emit_instances(st, P, g.order_a, g, tiles_x, cap, plan, bv.tkeys_a, bv.vals_a, bv.hist)));
+    }
+    GSR_TRY(debug_sync(st, debug));
+    {
+      StageTimer tm(st, GSR_STAGE_TILE_SORT);
+      GSR_TRY(check(sort_pairs_u32_prehist(st, cap, n_dev, bv.tkeys_a, bv.tkeys_b, bv.vals_a, bv.vals_b, plan,
+                                           bv.hist, bv.tickets, bv.lookback, point_list)));
+    }
+    GSR_TRY(debug_sync(st, debug));
+    {
+      StageTimer tm(st, GSR_STAGE_RANGES);
+      GSR_TRY(check(launch_tile_ranges(st, cap, n_dev, (plan.n_passes & 1) ? bv.tkeys_b : bv.tkeys_a, im.ranges,
+                                       num_tiles(width, height))));
+    }
+  } else {
+    GSR_TRY(check(launch_tile_ranges(st, 0, nullptr, nullptr, im.ranges, num_tiles(width, height))));
+  }
+  {
+    StageTimer tm(st, GSR_STAGE_RENDER_FWD);
+    GSR_TRY(check(launch_render_fwd(st, width, height, im, point_list, g, background, out_color, out_depth,
+                                    out_opacity, n_touched)));
+  }
+  return debug_sync(st, debug);
+}
+
+// num_rendered + prefilter flag -> pinned host slot; returns after the two copies have completed on `ev`.
+struct HostRead {
+  std::unique_lock<std::mutex> lk;
+  cudaEvent_t ev = nullptr;
+};
+static cudaEvent_t g_read_event = nullptr;
+static int enqueue_total_read(cudaStream_t st, const GeomViews& g) {
+  if (!g_pinned) GSR_TRY(check(cudaHostAlloc((void**)&g_pinned, sizeof(HostSlot), cudaHostAllocDefault)));
+  if (!g_read_event) GSR_TRY(check(cudaEventCreateWithFlags(&g_read_event, cudaEventDisableTiming)));
+  GSR_TRY(check(cudaMemcpyAsync(&g_pinned->total, g.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st)));
+  GSR_TRY(check(cudaMemcpyAsync(&g_pinned->error_flag, g.error_flag, sizeof(int), cudaMemcpyDeviceToHost, st)));
+  return check(cudaEventRecord(g_read_event, st));
+}
+static int finish_total_read(int64_t* num_rendered) {
+  GSR_TRY(check(cudaEventSynchronize(g_read_event)));
+  const HostSlot slot = *g_pinned;
+  if (slot.error_flag) return GSR_EPREFILTER;
+  if (slot.total >= (1ull << 30)) return GSR_EOVERFLOW;
+  *num_rendered = (int64_t)slot.total;
+  return GSR_OK;
+}
+
 int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
                      const float* means3D, const float* shs, const float* colors_precomp,
                      const float* opacities, const float* scales, float scale_modifier,
@@ -103,50 +206,18 @@ int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs, int widt
   *num_rendered = 0;
   if (P < 0 || width <= 0 || height <= 0) return GSR_EINVAL;
   if (P == 0) return GSR_OK;
-  if (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !geom_ws) return GSR_EINVAL;
-  if (!shs && !colors_precomp) return GSR_ENOCOLOR;       // rasterizer_impl.cu:245-248
-  if (shs && !colors_precomp && (!campos || sh_coeffs < (sh_degree + 1) * (sh_degree + 1) || sh_degree > 3))
-    return GSR_EINVAL;
-  if (!cov3D_precomp && (!scales || !rotations)) return GSR_ENOCOV;
-  if (num_tiles(width, height) > 65536) return GSR_EINVAL;  // two 8-bit tile digits
+  GSR_TRY(check_forward_args(P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
+                             rotations, cov3D_precomp, viewmatrix, projmatrix, campos, radii, geom_ws));
   cudaStream_t st = (cudaStream_t)stream;
-
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
-  GSR_TRY(check(cudaMemsetAsync((char*)geom_ws + g.zero_begin, 0, g.zero_end - g.zero_begin, st)));
-  {
-  StageTimer tm(st, GSR_STAGE_PREPROCESS);
-  GSR_TRY(check(launch_preprocess_fwd(st, P, sh_degree, sh_coeffs, means3D, colors_precomp ? nullptr : shs,
-                                      colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
-                                      viewmatrix, projmatrix, campos, width, height, tan_fovx, tan_fovy,
-                                      prefiltered, radii, g)));
-  }
-  GSR_TRY(debug_sync(st, debug));
-  // Gaussians into (depth bits, id) order: 4 stable passes, result back in dkeys_a / order_a
-  {
-  StageTimer tm(st, GSR_STAGE_DEPTH_SORT);
-  GSR_TRY(check(sort_pairs_u32_prehist(st, P, g.dkeys_a, g.dkeys_b, g.order_a, g.order_b, 4, g.hist, g.tickets,
-                                       g.lookback, nullptr)));
-  }
-  GSR_TRY(debug_sync(st, debug));
-  {
-  StageTimer tm(st, GSR_STAGE_SCAN);
-  GSR_TRY(check(launch_chunk_scan(st, P, g.order_a, g)));
-  }
+  GSR_TRY(enqueue_plan(st, P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
+                       scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy,
+                       prefiltered, radii, (char*)geom_ws, g, debug));
   // the one host read of the forward (rasterizer_impl.cu:284)
-  HostSlot slot;
-  {
-    std::lock_guard<std::mutex> lk(g_mu);
-    if (!g_pinned) GSR_TRY(check(cudaHostAlloc((void**)&g_pinned, sizeof(HostSlot), cudaHostAllocDefault)));
-    GSR_TRY(check(cudaMemcpyAsync(&g_pinned->total, g.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st)));
-    GSR_TRY(check(cudaMemcpyAsync(&g_pinned->error_flag, g.error_flag, sizeof(int), cudaMemcpyDeviceToHost, st)));
-    GSR_TRY(check(cudaStreamSynchronize(st)));
-    slot = *g_pinned;
-  }
-  if (slot.error_flag) return GSR_EPREFILTER;
-  if (slot.total >= (1ull << 30)) return GSR_EOVERFLOW;
-  *num_rendered = (int64_t)slot.total;
-  return GSR_OK;
+  std::lock_guard<std::mutex> lk(g_mu);
+  GSR_TRY(enqueue_total_read(st, g));
+  return finish_total_read(num_rendered);
 }
 
 int gsr_forward_render(void* stream, int P, int width, int height, const float* background, const int* radii,
@@ -163,39 +234,40 @@ int gsr_forward_render(void* stream, int P, int width, int height, const float* 
   carve_geom((char*)geom_ws, P, width, height, &g);
   ImageViews im;
   carve_image((char*)image_ws, width, height, &im);
-  const int tiles_x = (width + TILE_X - 1) / TILE_X, tiles_y = (height + TILE_Y - 1) / TILE_Y;
+  return enqueue_render(st, P, width, height, background, g, im, (char*)binning_ws, point_list, num_rendered,
+                        nullptr, out_color, out_depth, out_opacity, n_touched, debug);
+}
 
-  if (num_rendered > 0) {
-    BinningViews bv;
-    carve_binning((char*)binning_ws, num_rendered, &bv);
-    const int n_tp = tile_passes_for(width, height);
-    GSR_TRY(check(cudaMemsetAsync((char*)binning_ws + bv.zero_begin, 0, bv.zero_end - bv.zero_begin, st)));
-    {
-    StageTimer tm(st, GSR_STAGE_EMIT);
-    GSR_TRY(check(launch_emit_instances(st, P, g.order_a, g, radii, tiles_x, tiles_y, bv.tkeys_a, bv.vals_a)));
-    }
-    GSR_TRY(debug_sync(st, debug));
-    {
-    StageTimer tm(st, GSR_STAGE_TILE_SORT);
-    GSR_TRY(check(launch_tile_digit_hist(st, bv.tkeys_a, num_rendered, n_tp, bv.hist)));
-    GSR_TRY(check(sort_pairs_u32_prehist(st, num_rendered, bv.tkeys_a, bv.tkeys_b, bv.vals_a, bv.vals_b, n_tp,
-                                         bv.hist, bv.tickets, bv.lookback, point_list)));
-    }
-    GSR_TRY(debug_sync(st, debug));
-    {
-    StageTimer tm(st, GSR_STAGE_RANGES);
-    GSR_TRY(check(launch_tile_ranges(st, num_rendered, (n_tp & 1) ? bv.tkeys_b : bv.tkeys_a, im.ranges,
-                                     num_tiles(width, height))));
-    }
-  } else {
-    GSR_TRY(check(launch_tile_ranges(st, 0, nullptr, im.ranges, num_tiles(width, height))));
-  }
-  {
-  StageTimer tm(st, GSR_STAGE_RENDER_FWD);
-  GSR_TRY(check(launch_render_fwd(st, width, height, im, point_list, g, background, out_color, out_depth,
-                                  out_opacity, n_touched)));
-  }
-  return debug_sync(st, debug);
+int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height, const float* background,
+                const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+                const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
+                float tan_fovy, int prefiltered, int* radii, void* geom_ws, void* image_ws, void* binning_ws,
+                uint32_t* point_list, int64_t capacity, float* out_color, float* out_depth, float* out_opacity,
+                int* n_touched, int64_t* num_rendered, int debug) {
+  if (!num_rendered) return GSR_EINVAL;
+  *num_rendered = 0;
+  if (P < 0 || width <= 0 || height <= 0 || capacity < 0 || capacity >= (1ll << 30)) return GSR_EINVAL;
+  if (P == 0) return GSR_OK;
+  GSR_TRY(check_forward_args(P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
+                             rotations, cov3D_precomp, viewmatrix, projmatrix, campos, radii, geom_ws));
+  if (!background || !image_ws || !out_color || !out_depth || !out_opacity || !n_touched) return GSR_EINVAL;
+  if (capacity > 0 && (!binning_ws || !point_list)) return GSR_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  GeomViews g;
+  carve_geom((char*)geom_ws, P, width, height, &g);
+  ImageViews im;
+  carve_image((char*)image_ws, width, height, &im);
+  GSR_TRY(enqueue_plan(st, P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
+                       scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy,
+                       prefiltered, radii, (char*)geom_ws, g, debug));
+  std::lock_guard<std::mutex> lk(g_mu);
+  GSR_TRY(enqueue_total_read(st, g));
+  // everything downstream is enqueued BEFORE the host waits for num_rendered: the GPU never idles on the read
+  GSR_TRY(enqueue_render(st, P, width, height, background, g, im, (char*)binning_ws, point_list, capacity, g.total,
+                         out_color, out_depth, out_opacity, n_touched, debug));
+  GSR_TRY(finish_total_read(num_rendered));
+  return *num_rendered > capacity ? GSR_ECAPACITY : GSR_OK;
 }
 
 int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
@@ -238,7 +310,57 @@ int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs, int width, i
                                       rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
                                       projmatrix_raw, campos, width, height, tan_fovx, tan_fovy, bw, dL_dmeans2D,
                                       dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
-                                      dL_drotations, dL_dtau_per_gaussian, dL_dtau)));
+                                      dL_drotations, dL_dtau_per_gaussian, dL_dtau, 0, P, nullptr, 0)));
+  return debug_sync(st, debug);
+}
+
+int gsr_backward_render(void* stream, int P, int width, int height, const float* background, const void* geom_ws,
+                        const void* image_ws, const uint32_t* point_list, int64_t num_rendered,
+                        const float* dL_dout_color, const float* dL_dout_depth, void* scratch, int debug) {
+  if (P < 0 || width <= 0 || height <= 0 || num_rendered < 0) return GSR_EINVAL;
+  if (P == 0) return GSR_OK;
+  if (!background || !geom_ws || !image_ws || !scratch) return GSR_EINVAL;
+  if (num_rendered > 0 && !point_list) return GSR_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  GeomViews g;
+  carve_geom((char*)geom_ws, P, width, height, &g);
+  ImageViews im;
+  carve_image((char*)image_ws, width, height, &im);
+  BackwardViews bw;
+  carve_backward((char*)scratch, P, &bw);
+  GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, sizeof(float) * GRAD_STRIDE * (size_t)P, st)));
+  if (num_rendered > 0) {
+    StageTimer tm(st, GSR_STAGE_RENDER_BWD);
+    GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
+                                    dL_dout_depth, bw.packed)));
+  }
+  return debug_sync(st, debug);
+}
+
+int gsr_backward_rows(void* stream, int P, int p_begin, int p_end, int width, int height, const float* means3D,
+                      const float* scales, float scale_modifier, const float* rotations, const float* viewmatrix,
+                      const float* projmatrix, const float* projmatrix_raw, float tan_fovx, float tan_fovy,
+                      const int* radii, const void* geom_ws, void* scratch, float* rows, int accumulate,
+                      float* dL_dmeans2D, float* dL_dtau, int debug) {
+  if (P < 0 || width <= 0 || height <= 0 || p_begin < 0 || p_end < p_begin || p_end > P) return GSR_EINVAL;
+  if (p_begin % 256 != 0) return GSR_EINVAL;  // ranges start on a 256-Gaussian boundary (tau block partials)
+  cudaStream_t st = (cudaStream_t)stream;
+  if (P == 0) {
+    if (dL_dtau) GSR_TRY(check(cudaMemsetAsync(dL_dtau, 0, 6 * sizeof(float), st)));
+    return GSR_OK;
+  }
+  if (!means3D || !scales || !rotations || !viewmatrix || !projmatrix || !projmatrix_raw || !radii || !geom_ws ||
+      !scratch || !rows)
+    return GSR_EINVAL;
+  GeomViews g;
+  carve_geom((char*)geom_ws, P, width, height, &g);
+  BackwardViews bw;
+  carve_backward((char*)scratch, P, &bw);
+  StageTimer tm_pb(st, GSR_STAGE_PREPROCESS_BWD);
+  GSR_TRY(check(launch_preprocess_bwd(st, P, 0, 0, means3D, radii, nullptr, g.clamped, scales, rotations,
+                                      scale_modifier, nullptr, viewmatrix, projmatrix, projmatrix_raw, nullptr, width,
+                                      height, tan_fovx, tan_fovy, bw, dL_dmeans2D, nullptr, nullptr, nullptr, nullptr,
+                                      nullptr, nullptr, nullptr, nullptr, dL_dtau, p_begin, p_end, rows, accumulate)));
   return debug_sync(st, debug);
 }
 
@@ -266,12 +388,13 @@ int gsr_sort_pairs_u64(void* stream, int64_t n, const uint64_t* keys_in, const u
   cudaStream_t st = (cudaStream_t)stream;
   BinningViews bv;
   carve_binning((char*)ws, n, &bv);
-  const int n_passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
-  GSR_TRY(check(cudaMemsetAsync((char*)ws + bv.zero_begin, 0, bv.zero_end - bv.zero_begin, st)));
+  const SortPlan plan = make_sort_plan(end_bit);
+  const int n_passes = plan.n_passes;
+  GSR_TRY(check(cudaMemsetAsync((char*)ws + bv.zero_begin, 0, bv.zero_end(n_passes) - bv.zero_begin, st)));
   GSR_TRY(check(cudaMemcpyAsync(bv.keys64_a, keys_in, 8 * (size_t)n, cudaMemcpyDeviceToDevice, st)));
   GSR_TRY(check(cudaMemcpyAsync(bv.vals_a, values_in, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st)));
-  GSR_TRY(check(launch_digit_hist_u64(st, bv.keys64_a, n, n_passes, end_bit, bv.hist)));
-  GSR_TRY(check(sort_pairs_u64_prehist(st, n, bv.keys64_a, bv.keys64_b, bv.vals_a, bv.vals_b, n_passes, end_bit, bv.hist,
+  GSR_TRY(check(launch_digit_hist_u64(st, bv.keys64_a, n, plan, bv.hist)));
+  GSR_TRY(check(sort_pairs_u64_prehist(st, n, nullptr, bv.keys64_a, bv.keys64_b, bv.vals_a, bv.vals_b, plan, bv.hist,
                                        bv.tickets, bv.lookback, values_out)));
   const uint64_t* sorted = (n_passes & 1) ? bv.keys64_b : bv.keys64_a;
   return check(cudaMemcpyAsync(keys_out, sorted, 8 * (size_t)n, cudaMemcpyDeviceToDevice, st));
@@ -333,7 +456,7 @@ int gsr_debug_sorted_keys(void* stream, const void* geom_ws, const void* binning
   carve_geom((char*)geom_ws, P, width, height, &g);
   BinningViews bv;
   carve_binning((char*)binning_ws, num_rendered, &bv);
-  const uint32_t* tk = (tile_passes_for(width, height) & 1) ? bv.tkeys_b : bv.tkeys_a;
+  const uint32_t* tk = (tile_sort_plan(width, height).n_passes & 1) ? bv.tkeys_b : bv.tkeys_a;
   return check(launch_rebuild_keys((cudaStream_t)stream, num_rendered, tk, point_list, g.rec_a, keys_sorted));
 }
 

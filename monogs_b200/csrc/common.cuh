@@ -29,6 +29,8 @@ struct GeomViews {
   float4* rec_b;
   float4* rec_c;
   uint32_t* tiles_touched;   // [P]
+  uint2* rect;               // [P] tile rectangle x0 | x1 << 16, y0 | y1 << 16 (empty when culled)
+  uint2* rect_sorted;        // [P] the same in (depth, id) order
   uint8_t* clamped;          // [3P] SH clamp flags (forward.cu:69-71)
   // depth-order machinery (forward only)
   uint32_t* dkeys_a;         // [P] float bits of view depth (0xFFFFFFFF for culled Gaussians)
@@ -49,10 +51,33 @@ __host__ __device__ inline int num_pre_blocks(int P) { return (P + 255) / 256; }
 __host__ __device__ inline size_t num_tiles(int W, int H) {
   return (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
 }
-constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX_BITS = 8;   // widest digit of a pass
 constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
-constexpr int SORT_TILE = 256 * 16;  // keys per thread block per pass
-__host__ __device__ inline size_t sort_blocks(int64_t n) { return (size_t)((n + SORT_TILE - 1) / SORT_TILE); }
+constexpr int SORT_TILE_MIN = 256 * 8;             // smallest tile a sort pass uses (look-back words are sized for it)
+constexpr long long SORT_SMALL_N = 1ll << 21;      // up to here the 2048-key tile is used (more CTAs in flight)
+constexpr int SORT_MAX_PASSES = 8;
+__host__ __device__ inline size_t sort_blocks(int64_t n) { return (size_t)((n + SORT_TILE_MIN - 1) / SORT_TILE_MIN); }
+
+// Digit layout of an LSD sort on key bits [0, total_bits): ceil(bits/8) passes of (nearly) EQUAL width, so that
+// e.g. an 11-bit tile id is sorted as 6+5 bits (two passes of long runs) rather than 8+3.
+struct SortPlan {
+  int n_passes;
+  int shift[SORT_MAX_PASSES];
+  int bits[SORT_MAX_PASSES];
+};
+inline SortPlan make_sort_plan(int total_bits) {
+  SortPlan pl{};
+  if (total_bits < 1) total_bits = 1;
+  pl.n_passes = (total_bits + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+  const int base = total_bits / pl.n_passes, rem = total_bits % pl.n_passes;
+  int sh = 0;
+  for (int p = 0; p < pl.n_passes; ++p) {
+    pl.bits[p] = base + (p < rem ? 1 : 0);
+    pl.shift[p] = sh;
+    sh += pl.bits[p];
+  }
+  return pl;
+}
 
 __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, GeomViews* v) {
   (void)W; (void)H;
@@ -62,6 +87,7 @@ __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, Ge
   char* b = take(sizeof(float4) * (size_t)P);
   char* c = take(sizeof(float4) * (size_t)P);
   char* t = take(sizeof(uint32_t) * (size_t)P);
+  char* rc = take(sizeof(uint2) * (size_t)P); char* rs = take(sizeof(uint2) * (size_t)P);
   char* cl = take((size_t)3 * P);
   char* ka = take(4 * (size_t)P); char* kb = take(4 * (size_t)P);
   char* oa = take(4 * (size_t)P); char* ob = take(4 * (size_t)P);
@@ -75,6 +101,7 @@ __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, Ge
   if (v) {
     v->rec_a = (float4*)a; v->rec_b = (float4*)b; v->rec_c = (float4*)c;
     v->tiles_touched = (uint32_t*)t; v->clamped = (uint8_t*)cl;
+    v->rect = (uint2*)rc; v->rect_sorted = (uint2*)rs;
     v->dkeys_a = (uint32_t*)ka; v->dkeys_b = (uint32_t*)kb; v->order_a = (uint32_t*)oa; v->order_b = (uint32_t*)ob;
     v->chunk_offsets = (uint32_t*)co;
     v->hist = (uint32_t*)h; v->tickets = (uint32_t*)tk; v->lookback = (uint32_t*)lb;
@@ -112,10 +139,11 @@ struct BinningViews {
   uint32_t* hist;        // [8 * 256] digit histograms -> exclusive offsets
   uint32_t* tickets;     // [8]
   uint32_t* lookback;    // [8 * sort_blocks(R) * 256]
-  size_t zero_begin;     // byte range [zero_begin, zero_end) must be zeroed before a sort
-  size_t zero_end;
+  size_t zero_begin;     // byte range [zero_begin, zero_end(n_passes)) must be zeroed before a sort
+  size_t lookback_off;   // byte offset of `lookback`
+  size_t lookback_pass_bytes;
+  size_t zero_end(int n_passes) const { return lookback_off + (size_t)n_passes * lookback_pass_bytes; }
 };
-constexpr int SORT_MAX_PASSES = 8;
 __host__ __device__ inline size_t carve_binning(char* base, int64_t R, BinningViews* v) {
   size_t off = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
@@ -125,12 +153,13 @@ __host__ __device__ inline size_t carve_binning(char* base, int64_t R, BinningVi
   char* h = take(4 * (size_t)SORT_MAX_PASSES * SORT_RADIX);
   char* t = take(4 * (size_t)SORT_MAX_PASSES);
   char* lb = take(4 * (size_t)SORT_MAX_PASSES * sort_blocks(n) * SORT_RADIX);
-  size_t ze = off;
   if (v) {
     v->tkeys_a = (uint32_t*)ka; v->tkeys_b = (uint32_t*)kb; v->vals_a = (uint32_t*)va; v->vals_b = (uint32_t*)vb;
     v->keys64_a = (uint64_t*)ka; v->keys64_b = (uint64_t*)kb;
     v->hist = (uint32_t*)h; v->tickets = (uint32_t*)t; v->lookback = (uint32_t*)lb;
-    v->zero_begin = zb; v->zero_end = ze;
+    v->zero_begin = zb;
+    v->lookback_off = (size_t)(lb - base);
+    v->lookback_pass_bytes = 4 * sort_blocks(n) * SORT_RADIX;
   }
   return off;
 }

@@ -16,27 +16,29 @@ cudaError_t launch_mark_visible(cudaStream_t st, int P, const float* means3D, co
                                 uint8_t* present);
 
 // binning.cu
-cudaError_t launch_emit_instances(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g,
-                                  const int* radii, int tiles_x, int tiles_y, uint32_t* tkeys, uint32_t* vals);
-cudaError_t launch_tile_digit_hist(cudaStream_t st, const uint32_t* tkeys, long long n, int n_passes,
-                                   uint32_t* hist);
-cudaError_t launch_tile_ranges(cudaStream_t st, long long L, const uint32_t* tkeys_sorted, uint2* ranges,
-                               size_t n_tiles);
+cudaError_t launch_gather_rects(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g);
+cudaError_t launch_emit_instances(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g, int tiles_x,
+                                  long long cap, const SortPlan& plan, uint32_t* tkeys, uint32_t* vals,
+                                  uint32_t* hist);
+cudaError_t launch_tile_ranges(cudaStream_t st, long long cap, const unsigned long long* n_dev,
+                               const uint32_t* tkeys_sorted, uint2* ranges, size_t n_tiles);
 cudaError_t launch_rebuild_keys(cudaStream_t st, long long L, const uint32_t* tkeys_sorted,
                                 const uint32_t* point_list, const float4* rec_a, uint64_t* keys);
 
-// radix_sort.cu
-cudaError_t sort_pairs_u64_prehist(cudaStream_t st, long long n, uint64_t* keys_a, uint64_t* keys_b,
-                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes, int end_bit,
-                                   const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
-                                   uint32_t* final_vals);
-cudaError_t sort_pairs_u32_prehist(cudaStream_t st, long long n, uint32_t* keys_a, uint32_t* keys_b,
-                                   uint32_t* vals_a, uint32_t* vals_b, int n_passes,
-                                   const uint32_t* digit_offsets, uint32_t* tickets, uint32_t* lookback,
-                                   uint32_t* final_vals);
-cudaError_t launch_digit_hist_u64(cudaStream_t st, const uint64_t* keys, long long n, int n_passes, int end_bit,
+// radix_sort.cu  (n_cap = element count or capacity; n_dev = optional device-resident count <= n_cap)
+cudaError_t sort_pairs_u64_prehist(cudaStream_t st, long long n_cap, const unsigned long long* n_dev,
+                                   uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
+                                   const SortPlan& plan, const uint32_t* digit_offsets, uint32_t* tickets,
+                                   uint32_t* lookback, uint32_t* final_vals);
+cudaError_t sort_pairs_u32_prehist(cudaStream_t st, long long n_cap, const unsigned long long* n_dev,
+                                   uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
+                                   const SortPlan& plan, const uint32_t* digit_offsets, uint32_t* tickets,
+                                   uint32_t* lookback, uint32_t* final_vals);
+cudaError_t launch_digit_hist_u64(cudaStream_t st, const uint64_t* keys, long long n, const SortPlan& plan,
                                   uint32_t* hist);
-cudaError_t launch_digit_hist_u32(cudaStream_t st, const uint32_t* keys, long long n, int n_passes, uint32_t* hist);
+cudaError_t launch_digit_hist_u32(cudaStream_t st, const uint32_t* keys, long long n, const SortPlan& plan,
+                                  uint32_t* hist);
+cudaError_t launch_digit_offsets(cudaStream_t st, uint32_t* hist, int n_passes);
 
 // render_fwd.cu
 cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
@@ -56,7 +58,8 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
                                   const float* campos, int W, int H, float tan_fovx, float tan_fovy,
                                   const BackwardViews& bw, float* dL_dmeans2D, float* dL_dcolors,
                                   float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
-                                  float* dL_dscales, float* dL_drots, float* dL_dtau_pg, float* dL_dtau);
+                                  float* dL_dscales, float* dL_drots, float* dL_dtau_pg, float* dL_dtau,
+                                  int p_begin, int p_end, float* rows, int accumulate);
 
 // knn.cu
 size_t knn_workspace_bytes(int P);

@@ -256,10 +256,11 @@ cudaError_t launch_knn(cudaStream_t st, int P, const float* points, float* mean_
   count_launch(); knn_init_minmax<<<1, 32, 0, st>>>(v.minmax);
   count_launch(); knn_minmax_kernel<<<min(148 * 4, (P + 255) / 256), 256, 0, st>>>(P, points, v.minmax);
   count_launch(); knn_morton_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, points, v.minmax, v.codes_a, v.idx_a);
-  e = launch_digit_hist_u32(st, v.codes_a, P, 4, v.hist);
+  const SortPlan plan = make_sort_plan(30);  // 30-bit Morton codes: 4 passes (8+8+7+7)
+  e = launch_digit_hist_u32(st, v.codes_a, P, plan, v.hist);
   if (e != cudaSuccess) return e;
-  e = sort_pairs_u32_prehist(st, P, v.codes_a, v.codes_b, v.idx_a, v.idx_b, 4, v.hist, v.tickets, v.lookback,
-                             nullptr);
+  e = sort_pairs_u32_prehist(st, P, nullptr, v.codes_a, v.codes_b, v.idx_a, v.idx_b, plan, v.hist, v.tickets,
+                             v.lookback, nullptr);
   if (e != cudaSuccess) return e;
   // 4 passes: result is back in the "a" buffers
   const int n_l2 = (P + KNN_L2 - 1) / KNN_L2;

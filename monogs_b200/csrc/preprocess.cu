@@ -151,14 +151,25 @@ GSR_DEVINL void tile_rect(float px, float py, int radius, int tiles_x, int tiles
 
 constexpr int PRE_THREADS = 256;
 
-// Coalesced load of `n_floats` consecutive floats per thread-block row into smem.
-template <int PER>
-GSR_DEVINL void stage_block(const float* __restrict__ g, float* s, long long base_elem, long long total_elem) {
-  // block covers PRE_THREADS * PER floats starting at base_elem
-  for (int i = threadIdx.x; i < PRE_THREADS * PER; i += PRE_THREADS) {
-    long long e = base_elem + i;
-    s[i] = (e < total_elem) ? __ldg(g + e) : 0.0f;
+// Coalesced 128-bit load of the block's PRE_THREADS * 3 consecutive floats ([P,3] AoS input) -- the first 192
+// threads fetch one float4 each; the value is parked in a register so that all staging loads of the kernel are in
+// flight together, and stored to shared memory afterwards (stage_store3).
+GSR_DEVINL float4 stage_load3(const float* __restrict__ g, long long base_elem, long long total_elem) {
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int t = threadIdx.x;
+  if (t < PRE_THREADS * 3 / 4) {
+    const long long e = base_elem + 4ll * t;  // base_elem is a multiple of 768 floats -> 16-byte aligned
+    if (e + 4 <= total_elem) v = __ldg(reinterpret_cast<const float4*>(g + e));
+    else {
+      if (e < total_elem) v.x = __ldg(g + e);
+      if (e + 1 < total_elem) v.y = __ldg(g + e + 1);
+      if (e + 2 < total_elem) v.z = __ldg(g + e + 2);
+    }
   }
+  return v;
+}
+GSR_DEVINL void stage_store3(float* s, float4 v) {
+  if (threadIdx.x < PRE_THREADS * 3 / 4) reinterpret_cast<float4*>(s)[threadIdx.x] = v;
 }
 
 __global__ void __launch_bounds__(PRE_THREADS)
@@ -170,9 +181,8 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       const float* __restrict__ campos, int W, int H, float tan_fovx, float tan_fovy,
                       float focal_x, float focal_y, int tiles_x, int tiles_y, int prefiltered,
                       int* __restrict__ radii, GeomViews g) {
-  __shared__ float s_mean[PRE_THREADS * 3];
-  __shared__ float s_scale[PRE_THREADS * 3];
-  __shared__ float s_rot[PRE_THREADS * 4];
+  __shared__ __align__(16) float s_mean[PRE_THREADS * 3];
+  __shared__ __align__(16) float s_scale[PRE_THREADS * 3];
   __shared__ float s_cam[36];
   __shared__ uint32_t s_hist[4 * 256];
 
@@ -184,14 +194,25 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   else if (tid < 32) s_cam[tid] = projmatrix[tid - 16];
   else if (tid < 35) s_cam[tid] = campos ? campos[tid - 32] : 0.0f;
   for (int i = tid; i < 4 * 256; i += PRE_THREADS) s_hist[i] = 0;
-  stage_block<3>(means3D, s_mean, blk_base * 3, (long long)P * 3);
+  // all global input loads of this thread are issued back to back
+  const float4 ld_mean = stage_load3(means3D, blk_base * 3, (long long)P * 3);
+  float4 ld_scale = make_float4(0.f, 0.f, 0.f, 0.f), my_rot = make_float4(1.f, 0.f, 0.f, 0.f);
   if (cov3D_precomp == nullptr) {
-    stage_block<3>(scales, s_scale, blk_base * 3, (long long)P * 3);
-    stage_block<4>(rotations, s_rot, blk_base * 4, (long long)P * 4);
+    ld_scale = stage_load3(scales, blk_base * 3, (long long)P * 3);
+    if (idx < P) my_rot = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
   }
+  const float my_opac = idx < P ? __ldg(opacities + idx) : 0.f;
+  float3 my_col = make_float3(0.f, 0.f, 0.f);
+  if (colors_precomp != nullptr && idx < P)
+    my_col = make_float3(__ldg(colors_precomp + (size_t)idx * 3), __ldg(colors_precomp + (size_t)idx * 3 + 1),
+                         __ldg(colors_precomp + (size_t)idx * 3 + 2));
+  stage_store3(s_mean, ld_mean);
+  stage_store3(s_scale, ld_scale);
   __syncthreads();
 
   uint32_t my_tiles = 0;
+  uint2 my_rect = make_uint2(0u, 0u);  // x0 | x1 << 16, y0 | y1 << 16 (empty for culled Gaussians)
+  uint32_t my_dkey = 0u;
   if (idx < P) {
     const float* view = s_cam;
     const float* proj = s_cam + 16;
@@ -218,9 +239,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
         for (int k = 0; k < 6; ++k) cov[k] = __ldg(cov3D_precomp + (size_t)idx * 6 + k);
       } else {
         cov3d_from_scale_rot(make_float3(s_scale[3 * tid], s_scale[3 * tid + 1], s_scale[3 * tid + 2]),
-                             scale_modifier,
-                             make_float4(s_rot[4 * tid], s_rot[4 * tid + 1], s_rot[4 * tid + 2], s_rot[4 * tid + 3]),
-                             cov);
+                             scale_modifier, my_rot, cov);
       }
       const float tx = affine_row(view, 0, px, py, pz);
       const float ty = affine_row(view, 1, px, py, pz);
@@ -244,7 +263,8 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
           alive = false;
           my_radius_i = 0;
         } else {
-          const float opac = __ldg(opacities + idx);
+          my_rect = make_uint2(rmin.x | (rmax.x << 16), rmin.y | (rmax.y << 16));
+          const float opac = my_opac;
           // Conservative per-axis reach of alpha >= 1/255 (see DESIGN.md "culling"):
           // q(d) <= 2*ln(255*o); inflated so fp32 rounding in `power` can never
           // make a pixel outside the box pass the reference's alpha test.
@@ -258,8 +278,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
           }
           float3 rgb;
           if (colors_precomp != nullptr) {
-            rgb = make_float3(__ldg(colors_precomp + (size_t)idx * 3), __ldg(colors_precomp + (size_t)idx * 3 + 1),
-                              __ldg(colors_precomp + (size_t)idx * 3 + 2));
+            rgb = my_col;
           } else {
             rgb = sh_to_rgb(D, M, shs + (size_t)idx * M * 3, make_float3(px, py, pz),
                             make_float3(s_cam[32], s_cam[33], s_cam[34]));
@@ -277,57 +296,31 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     }
     radii[idx] = my_radius_i;
     g.tiles_touched[idx] = my_tiles;
+    g.rect[idx] = my_rect;
     g.rec_a[idx] = ra;
     g.rec_b[idx] = rb;
     g.rec_c[idx] = rc;
     // depth sort key: positive floats order like their bit patterns; culled Gaussians go last
     const uint32_t dkey = my_tiles ? __float_as_uint(ra.z) : 0xFFFFFFFFu;
     g.dkeys_a[idx] = dkey;
+    my_dkey = dkey;
     g.order_a[idx] = (uint32_t)idx;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) atomicAdd(&s_hist[k * 256 + ((dkey >> (8 * k)) & 255u)], 1u);
+    atomicAdd(&s_hist[dkey & 255u], 1u);
+    atomicAdd(&s_hist[256 + ((dkey >> 8) & 255u)], 1u);
+  }
+  {  // the two high depth digits take few distinct values per warp: one shared atomic per distinct value
+    const uint32_t hi = idx < P ? (my_dkey >> 16) : 0x10000u;
+    const uint32_t peers = __match_any_sync(0xffffffffu, hi);
+    if (idx < P && (__ffs(peers) - 1) == (tid & 31)) {
+      const uint32_t c = __popc(peers);
+      atomicAdd(&s_hist[512 + (hi & 255u)], c);
+      atomicAdd(&s_hist[768 + (hi >> 8)], c);
+    }
   }
   __syncthreads();
   for (int i = tid; i < 4 * 256; i += PRE_THREADS) {
     uint32_t c = s_hist[i];
     if (c) atomicAdd(&g.hist[i], c);
-  }
-}
-
-// Exclusive prefix over the 256 bins of each pass' digit histogram (one warp per pass).
-__global__ void digit_offsets4_kernel(uint32_t* hist, int n_passes) {
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (w >= n_passes) return;
-  uint32_t run = 0;
-  for (int c = 0; c < 8; ++c) {
-    uint32_t v = hist[w * 256 + c * 32 + lane];
-    uint32_t inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
-    }
-    hist[w * 256 + c * 32 + lane] = run + inc - v;
-    run += __shfl_sync(0xffffffffu, inc, 31);
-  }
-}
-
-// Instance count of every 256-Gaussian chunk of the DEPTH-ordered list.
-__global__ void __launch_bounds__(256)
-chunk_sums_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles_touched,
-                  uint32_t* __restrict__ chunk_sums) {
-  __shared__ uint32_t s_w[8];
-  const int s = blockIdx.x * 256 + threadIdx.x;
-  uint32_t v = s < P ? tiles_touched[order[s]] : 0u;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t t = 0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) t += s_w[w];
-    chunk_sums[blockIdx.x] = t;
   }
 }
 
@@ -399,14 +392,14 @@ cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const fl
       P, D, M, means3D, shs, colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
       viewmatrix, projmatrix, campos, W, H, tan_fovx, tan_fovy, focal_x, focal_y, tiles_x, tiles_y, prefiltered,
       radii, g);
-  count_launch(); digit_offsets4_kernel<<<1, 128, 0, st>>>(g.hist, 4);
-  return cudaGetLastError();
+  return launch_digit_offsets(st, g.hist, 4);
 }
 
 // offsets of the depth-ordered chunks + total; `order` = Gaussian ids in depth order
 cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g) {
   const int nc = num_pre_blocks(P);
-  count_launch(); chunk_sums_kernel<<<nc, 256, 0, st>>>(P, order, g.tiles_touched, g.chunk_offsets);
+  cudaError_t e = launch_gather_rects(st, P, order, g);
+  if (e != cudaSuccess) return e;
   count_launch(); chunk_scan_kernel<<<1, SCAN_THREADS, 0, st>>>(nc, g.chunk_offsets, g.total);
   return cudaGetLastError();
 }

@@ -95,7 +95,7 @@ GSR_DEVINL V3 sh_backward(int deg, int M, const float* __restrict__ sh, const ui
   return dnorm(dir_orig, dL_ddir);
 }
 
-__global__ void __launch_bounds__(PB_THREADS)
+__global__ void __launch_bounds__(PB_THREADS, 3)
 preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
                       const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
                       const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
@@ -106,7 +106,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
                       float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
                       float* __restrict__ dL_dscales, float* __restrict__ dL_drots,
-                      float* __restrict__ dL_dtau_pg, double* __restrict__ tau_partial) {
+                      float* __restrict__ dL_dtau_pg, double* __restrict__ tau_partial, int p_begin,
+                      float* __restrict__ rows /*[P,16] window rows or NULL*/, int accumulate) {
   __shared__ float s_cam[40];
   __shared__ double s_red[PB_THREADS / 32][6];
   const int tid = threadIdx.x;
@@ -120,7 +121,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   const float* v = s_cam;
   const float* p = s_cam + 16;
 
-  const int idx = blockIdx.x * PB_THREADS + tid;
+  const int idx = p_begin + blockIdx.x * PB_THREADS + tid;  // P = end of this launch's Gaussian range
   float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   float g2x = 0.f, g2y = 0.f, gop = 0.f, gcr = 0.f, gcg = 0.f, gcb = 0.f;
   V3 dmean = v3(0, 0, 0);
@@ -128,18 +129,33 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   float dscale[3] = {0.f, 0.f, 0.f};
   float drot[4] = {0.f, 0.f, 0.f, 0.f};
   const bool in_range = idx < P;
-  const bool visible = in_range && radii[idx] > 0;
+  // every global load of this thread is issued up front, unconditionally (the kernel is latency-bound: a chain
+  // radii -> packed -> inputs would serialise three DRAM round trips)
+  int my_radius = 0;
+  float4 pk0 = make_float4(0.f, 0.f, 0.f, 0.f), pk1 = pk0, pk2 = pk0, ld_rot = pk0;
+  float ld_m[3] = {0.f, 0.f, 0.f}, ld_s[3] = {0.f, 0.f, 0.f};
+  if (in_range) {
+    my_radius = __ldg(radii + idx);
+    pk0 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE));
+    pk1 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 4));
+    pk2 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 8));
+#pragma unroll
+    for (int k = 0; k < 3; ++k) ld_m[k] = __ldg(means3D + 3 * (size_t)idx + k);
+    if (!cov3D_precomp) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) ld_s[k] = __ldg(scales + 3 * (size_t)idx + k);
+      ld_rot = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+    }
+  }
+  const bool visible = in_range && my_radius > 0;
 
   if (visible) {
-    const float4 pk0 = *reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE);
-    const float4 pk1 = *reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 4);
-    const float4 pk2 = *reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 8);
     g2x = pk0.x; g2y = pk0.y;
     const float dcx = pk0.z, dcy = pk0.w, dcz = pk1.x;
     gop = pk1.y; gcr = pk1.z; gcg = pk1.w; gcb = pk2.x;
     const float gdepth = pk2.y;
 
-    const V3 m = v3(means3D[3 * (size_t)idx], means3D[3 * (size_t)idx + 1], means3D[3 * (size_t)idx + 2]);
+    const V3 m = v3(ld_m[0], ld_m[1], ld_m[2]);
 
     // ---- 3D covariance (recomputed; it is not stored by the forward) ----
     float cov[6];
@@ -150,11 +166,10 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
 #pragma unroll
       for (int k = 0; k < 6; ++k) cov[k] = cov3D_precomp[(size_t)idx * 6 + k];
     } else {
-      s[0] = scale_modifier * scales[3 * (size_t)idx];
-      s[1] = scale_modifier * scales[3 * (size_t)idx + 1];
-      s[2] = scale_modifier * scales[3 * (size_t)idx + 2];
-      qr = rotations[4 * (size_t)idx]; qx = rotations[4 * (size_t)idx + 1];
-      qy = rotations[4 * (size_t)idx + 2]; qz = rotations[4 * (size_t)idx + 3];
+      s[0] = scale_modifier * ld_s[0];
+      s[1] = scale_modifier * ld_s[1];
+      s[2] = scale_modifier * ld_s[2];
+      qr = ld_rot.x; qx = ld_rot.y; qy = ld_rot.z; qz = ld_rot.w;
       Rg[0][0] = 1.f - 2.f * (qy * qy + qz * qz); Rg[0][1] = 2.f * (qx * qy - qr * qz); Rg[0][2] = 2.f * (qx * qz + qr * qy);
       Rg[1][0] = 2.f * (qx * qy + qr * qz); Rg[1][1] = 1.f - 2.f * (qx * qx + qz * qz); Rg[1][2] = 2.f * (qy * qz - qr * qx);
       Rg[2][0] = 2.f * (qx * qz - qr * qy); Rg[2][1] = 2.f * (qy * qz + qr * qx); Rg[2][2] = 1.f - 2.f * (qx * qx + qy * qy);
@@ -332,6 +347,23 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
 #pragma unroll
       for (int k = 0; k < 6; ++k) dL_dtau_pg[6 * (size_t)idx + k] = tau[k];
     }
+    if (rows) {
+      // mapping-window row (monogs_b200/window.py): xyz 3 | rgb 3 | opacity 1 | scale 3 | rotation 4 |
+      // ||dL/dmean2D[:2]|| | visible -- one 64-byte row per Gaussian, so a Gaussian range is one contiguous slice
+      float4* r4 = reinterpret_cast<float4*>(rows + 16 * (size_t)idx);
+      float4 o0 = make_float4(dmean.x, dmean.y, dmean.z, gcr);
+      float4 o1 = make_float4(gcg, gcb, gop, dscale[0]);
+      float4 o2 = make_float4(dscale[1], dscale[2], drot[0], drot[1]);
+      float4 o3 = make_float4(drot[2], drot[3], visible ? sqrtf(g2x * g2x + g2y * g2y) : 0.f, visible ? 1.f : 0.f);
+      if (accumulate) {
+        const float4 a0 = r4[0], a1 = r4[1], a2 = r4[2], a3 = r4[3];
+        o0.x += a0.x; o0.y += a0.y; o0.z += a0.z; o0.w += a0.w;
+        o1.x += a1.x; o1.y += a1.y; o1.z += a1.z; o1.w += a1.w;
+        o2.x += a2.x; o2.y += a2.y; o2.z += a2.z; o2.w += a2.w;
+        o3.x += a3.x; o3.y += a3.y; o3.z += a3.z; o3.w += a3.w;
+      }
+      r4[0] = o0; r4[1] = o1; r4[2] = o2; r4[3] = o3;
+    }
   }
 
   // ---- block reduction of dL/dtau in fp64 ----
@@ -351,7 +383,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     double sacc = 0.0;
 #pragma unroll
     for (int w2 = 0; w2 < PB_THREADS / 32; ++w2) sacc += s_red[w2][tid];
-    tau_partial[(size_t)blockIdx.x * 6 + tid] = sacc;
+    tau_partial[((size_t)(p_begin / PB_THREADS) + blockIdx.x) * 6 + tid] = sacc;
   }
 }
 
@@ -386,17 +418,24 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
                                   const float* campos, int W, int H, float tan_fovx, float tan_fovy,
                                   const BackwardViews& bw, float* dL_dmeans2D, float* dL_dcolors,
                                   float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
-                                  float* dL_dscales, float* dL_drots, float* dL_dtau_pg, float* dL_dtau) {
+                                  float* dL_dscales, float* dL_drots, float* dL_dtau_pg, float* dL_dtau,
+                                  int p_begin, int p_end, float* rows, int accumulate) {
   const float focal_y = H / (2.0f * tan_fovy);
   const float focal_x = W / (2.0f * tan_fovx);
-  const int nb = num_pre_blocks(P);
-  count_launch(); preprocess_bwd_kernel<<<nb, PB_THREADS, 0, st>>>(P, D, M, means3D, radii, shs, clamped, scales, rotations,
-                                                   scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
-                                                   projmatrix_raw, campos, focal_x, focal_y, tan_fovx, tan_fovy,
-                                                   bw.packed, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D,
-                                                   dL_dcov3D, dL_dsh, dL_dscales, dL_drots, dL_dtau_pg,
-                                                   bw.tau_partial);
-  if (dL_dtau) { count_launch(); tau_final_kernel<<<1, 256, 0, st>>>(nb, bw.tau_partial, dL_dtau); }
+  const int nb = num_pre_blocks(p_end - p_begin);  // p_begin is a multiple of 256 (checked by the caller)
+  if (nb > 0) {
+    count_launch();
+    preprocess_bwd_kernel<<<nb, PB_THREADS, 0, st>>>(p_end, D, M, means3D, radii, shs, clamped, scales, rotations,
+                                                     scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                                                     projmatrix_raw, campos, focal_x, focal_y, tan_fovx, tan_fovy,
+                                                     bw.packed, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D,
+                                                     dL_dcov3D, dL_dsh, dL_dscales, dL_drots, dL_dtau_pg,
+                                                     bw.tau_partial, p_begin, rows, accumulate);
+  }
+  // the pose gradient is complete once the LAST range has run (ranges are issued in ascending order)
+  if (dL_dtau && p_end == P) {
+    count_launch(); tau_final_kernel<<<1, 256, 0, st>>>(num_pre_blocks(P), bw.tau_partial, dL_dtau);
+  }
   return cudaGetLastError();
 }
 

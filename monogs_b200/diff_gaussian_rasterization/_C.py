@@ -13,6 +13,7 @@ import torch
 from .. import _abi
 
 NUM_CHANNELS = 3
+_capacity = {}  # (P, W, H, device) -> instance capacity for the bubble-free gsr_forward path
 
 
 def _ptr(t):
@@ -73,20 +74,38 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 
         R = C.c_int64(0)
         st = _stream()
-        rc = lib.gsr_forward_plan(st, P, int(degree), M, W, H, _ptr(means3D_c), _ptr(sh_c), _ptr(colors_c),
-                                  _ptr(opacity_c), _ptr(scales_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c),
-                                  _ptr(view_c), _ptr(proj_c), _ptr(campos_c), float(tan_fovx), float(tan_fovy),
-                                  int(bool(prefiltered)), radii.data_ptr(), geom.data_ptr(), C.byref(R),
-                                  int(bool(debug)))
-        _abi.check(rc, "gsr_forward_plan")
+        plan_args = (st, P, int(degree), M, W, H)
+        in_args = (_ptr(means3D_c), _ptr(sh_c), _ptr(colors_c), _ptr(opacity_c), _ptr(scales_c),
+                   float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(view_c), _ptr(proj_c), _ptr(campos_c),
+                   float(tan_fovx), float(tan_fovy), int(bool(prefiltered)))
+        out_args = (out_color.data_ptr(), out_depth.data_ptr(), out_opacity.data_ptr(), n_touched.data_ptr())
+        key = (P, W, H, dev.index)
+        cap = _capacity.get(key)
+        done = False
+        if cap is not None and not debug:
+            # single call, no GPU bubble: the instance-level kernels are enqueued for a capacity remembered from
+            # the last call of this shape; the host wait for num_rendered overlaps them
+            point_list = torch.empty(lib.gsr_point_list_bytes(cap), dtype=torch.uint8, device=dev)
+            binning = torch.empty(lib.gsr_binning_bytes(cap), dtype=torch.uint8, device=dev)
+            rc = lib.gsr_forward(*plan_args, _ptr(bg_c), *in_args, radii.data_ptr(), geom.data_ptr(), img.data_ptr(),
+                                 binning.data_ptr(), point_list.data_ptr(), cap, *out_args, C.byref(R), 0)
+            if rc != _abi.GSR_ECAPACITY:
+                _abi.check(rc, "gsr_forward")
+                done = True
+            else:
+                n_touched.zero_()
+        else:
+            rc = lib.gsr_forward_plan(*plan_args, *in_args, radii.data_ptr(), geom.data_ptr(), C.byref(R),
+                                      int(bool(debug)))
+            _abi.check(rc, "gsr_forward_plan")
         R = int(R.value)
-        point_list = torch.empty(lib.gsr_point_list_bytes(R), dtype=torch.uint8, device=dev)
-        binning = torch.empty(lib.gsr_binning_bytes(R) if R > 0 else 0, dtype=torch.uint8, device=dev)
-        rc = lib.gsr_forward_render(st, P, W, H, _ptr(bg_c), radii.data_ptr(), geom.data_ptr(), img.data_ptr(),
-                                    _ptr(binning), point_list.data_ptr(), R, out_color.data_ptr(),
-                                    out_depth.data_ptr(), out_opacity.data_ptr(), n_touched.data_ptr(),
-                                    int(bool(debug)))
-        _abi.check(rc, "gsr_forward_render")
+        if not done:
+            point_list = torch.empty(lib.gsr_point_list_bytes(R), dtype=torch.uint8, device=dev)
+            binning = torch.empty(lib.gsr_binning_bytes(R) if R > 0 else 0, dtype=torch.uint8, device=dev)
+            rc = lib.gsr_forward_render(st, P, W, H, _ptr(bg_c), radii.data_ptr(), geom.data_ptr(), img.data_ptr(),
+                                        _ptr(binning), point_list.data_ptr(), R, *out_args, int(bool(debug)))
+            _abi.check(rc, "gsr_forward_render")
+        _capacity[key] = int(R * 1.25) + 65536
         if debug:
             rasterize_gaussians.last_binning = binning  # test hook: sorted keys live in here
     return R, out_color, radii, geom, point_list, img, out_depth, out_opacity, n_touched
@@ -189,3 +208,43 @@ def mark_visible(means3D, viewmatrix, projmatrix):
                                       _f32(projmatrix, "projmatrix").data_ptr(), present.data_ptr())
             _abi.check(rc, "gsr_mark_visible")
     return present
+
+
+def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotations, scale_modifier, viewmatrix,
+                                      projmatrix, projmatrix_raw, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth,
+                                      geomBuffer, R, point_list, imageBuffer, rows, accumulate, chunks=None,
+                                      chunk_done=None, want_means2D=False, debug=False):
+    """Backward of one keyframe of the sharded mapping window (gsr_backward_render + gsr_backward_rows): the
+    Gaussian gradients are written / added into `rows` f32[P,16] (layout: include/gsr_b200.h) range by range;
+    `chunk_done(p0, p1)` is called right after each range has been enqueued (the caller starts its allreduce of
+    rows[p0:p1] there). Returns (dL_dtau[6], dL_dmeans2D[P,3] or None)."""
+    lib = _abi.load()
+    P = int(means3D.size(0))
+    dev = means3D.device
+    H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    if rows.shape != (P, 16) or rows.dtype != torch.float32 or not rows.is_contiguous():
+        raise RuntimeError("rows must be a contiguous float32 [P,16] tensor")
+    tau = torch.zeros(6, dtype=torch.float32, device=dev)
+    m2d = torch.empty(P, 3, dtype=torch.float32, device=dev) if want_means2D else None
+    if P == 0:
+        return tau, m2d
+    chunks = chunks or [(0, P)]
+    with torch.cuda.device(dev):
+        scratch = torch.empty(lib.gsr_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
+        gc, gd = _f32(dL_dout_color, "dL_dout_color"), _f32(dL_dout_depth, "dL_dout_depth")
+        bg_c, m3, sc, ro = _f32(background, "bg"), _f32(means3D, "means3D"), _f32(scales, "scales"), _f32(rotations, "rotations")
+        vm, pm, pr = _f32(viewmatrix, "viewmatrix"), _f32(projmatrix, "projmatrix"), _f32(projmatrix_raw, "projmatrix_raw")
+        radii_c = radii.contiguous()
+        st = _stream()
+        rc = lib.gsr_backward_render(st, P, W, H, _ptr(bg_c), geomBuffer.data_ptr(), imageBuffer.data_ptr(),
+                                     _ptr(point_list), int(R), _ptr(gc), _ptr(gd), scratch.data_ptr(), int(bool(debug)))
+        _abi.check(rc, "gsr_backward_render")
+        for (p0, p1) in chunks:
+            rc = lib.gsr_backward_rows(st, P, int(p0), int(p1), W, H, _ptr(m3), _ptr(sc), float(scale_modifier),
+                                       _ptr(ro), _ptr(vm), _ptr(pm), _ptr(pr), float(tan_fovx), float(tan_fovy),
+                                       radii_c.data_ptr(), geomBuffer.data_ptr(), scratch.data_ptr(), rows.data_ptr(),
+                                       int(bool(accumulate)), _ptr(m2d), tau.data_ptr(), int(bool(debug)))
+            _abi.check(rc, "gsr_backward_rows")
+            if chunk_done is not None:
+                chunk_done(p0, p1)
+    return tau, m2d

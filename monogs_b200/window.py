@@ -43,6 +43,23 @@ def column_slices() -> Dict[str, slice]:
     return out
 
 
+def window_chunks(P: int, n_chunks: int = 4) -> List[tuple]:
+    """Gaussian ranges [p0, p1) of the window backward: 256-aligned, shrinking (40/30/20/10 %) so that the
+    allreduce of the LAST range -- the only one nothing is left to overlap with -- is the smallest. A pure
+    function of (P, n_chunks): every rank derives the same ranges, so the collectives line up."""
+    if P <= 0:
+        return []
+    if n_chunks <= 1 or P < 4096:
+        return [(0, P)]
+    weights = list(range(n_chunks, 0, -1))
+    total, bounds, acc = float(sum(weights)), [0], 0
+    for w in weights[:-1]:
+        acc += w
+        bounds.append(min(P, int(P * acc / total) // 256 * 256))
+    bounds.append(P)
+    return [(a, b) for a, b in zip(bounds[:-1], bounds[1:]) if b > a]
+
+
 @dataclass
 class KeyframeResult:
     """What one keyframe contributes (the per-keyframe items of slam_mapper.py:319-322)."""
@@ -62,15 +79,18 @@ class WindowStepResult:
     local: List[KeyframeResult] = field(default_factory=list)
 
 
-# render_fn(keyframe_index, params, flat_out) -> KeyframeResult.  It must ADD this keyframe's Gaussian-parameter
-# gradients and aux columns into flat_out[P, N_COLS] (fp32, on the parameters' device).
-RenderFn = Callable[[int, Dict[str, torch.Tensor], torch.Tensor], KeyframeResult]
+# render_fn(keyframe_index, params, flat, accumulate, chunks, chunk_done) -> KeyframeResult.
+# It must WRITE (accumulate False) or ADD (accumulate True) this keyframe's Gaussian-parameter gradients and aux
+# columns into flat[P, N_COLS] (fp32, on the parameters' device), and -- when chunk_done is given -- call
+# chunk_done(p0, p1) for every range of `chunks`, in order, as soon as rows [p0, p1) are final on the current stream.
+RenderFn = Callable[..., KeyframeResult]
 
 
 class MappingWindow:
-    def __init__(self, render_fn: RenderFn, group: Optional[dist.ProcessGroup] = None):
+    def __init__(self, render_fn: RenderFn, group: Optional[dist.ProcessGroup] = None, n_chunks: int = 4):
         self.render_fn = render_fn
         self.group = group
+        self.n_chunks = n_chunks
         self._flat: Optional[torch.Tensor] = None
         self._radii: Optional[torch.Tensor] = None
 
@@ -89,56 +109,69 @@ class MappingWindow:
 
     def step(self, params: Dict[str, torch.Tensor], n_keyframes: int) -> WindowStepResult:
         """One window iteration: local keyframes -> partial sums -> exchange. `params` maps the names of
-        PARAM_COLUMNS to replicated tensors."""
+        PARAM_COLUMNS to replicated tensors. The exchange is started range by range while the last local
+        keyframe's per-Gaussian backward is still running (async allreduce per finished range of rows)."""
         P = int(params["means3D"].shape[0])
         dev = params["means3D"].device
         self._buffers(P, dev)
         flat, radii = self._flat, self._radii
-        flat.zero_()
-        radii.zero_()
+        world = self.world_size
+        chunks = window_chunks(P, self.n_chunks if world > 1 else 1)
+        works = []
+
+        def chunk_done(p0, p1):
+            if world > 1:
+                works.append(dist.all_reduce(flat[p0:p1], op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+
+        mine = shard_keyframes(n_keyframes, world, self.rank)
         local = []
-        for k in shard_keyframes(n_keyframes, self.world_size, self.rank):
-            r = self.render_fn(k, params, flat)
+        radii.zero_()
+        if not mine:  # more GPUs than keyframes: contribute zeros, but take part in every collective
+            flat.zero_()
+            for c in chunks:
+                chunk_done(*c)
+        for i, k in enumerate(mine):
+            last = i == len(mine) - 1
+            r = self.render_fn(k, params, flat, i > 0, chunks, chunk_done if last else None)
             torch.maximum(radii, r.radii.to(torch.int32), out=radii)
             local.append(r)
-        if self.world_size > 1:
-            # the one exchange step of the path; async so the max-reduce overlaps the sum-reduce
-            h1 = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-            h2 = dist.all_reduce(radii, op=dist.ReduceOp.MAX, group=self.group, async_op=True)
-            h1.wait()
-            h2.wait()
+        if world > 1:
+            works.append(dist.all_reduce(radii, op=dist.ReduceOp.MAX, group=self.group, async_op=True))
+            for w in works:
+                w.wait()
         sl = column_slices()
         grads = {name: flat[:, sl[name]] for name, _ in PARAM_COLUMNS}
         return WindowStepResult(grads=grads, grad2d_norm=flat[:, sl["grad2d_norm"]].squeeze(1),
                                 vis_count=flat[:, sl["vis_count"]].squeeze(1), max_radii=radii, local=local)
 
 
+def mapping_loss_grad(color, depth, gt_image, gt_depth):
+    """0.9 L1(rgb) + 0.1 L1(depth over gt_depth > 0) and its gradient w.r.t. the rendered images
+    (get_loss_mapping, utils/slam_utils.py:101-146, RGB-D branch without exposure / rgb-boundary masks)."""
+    diff = color - gt_image
+    n_rgb = diff.numel()
+    valid = gt_depth > 0
+    n_d = valid.sum().clamp_min(1)
+    ddiff = (depth - gt_depth) * valid
+    loss = 0.9 * diff.abs().sum() / n_rgb + 0.1 * ddiff.abs().sum() / n_d
+    return loss, 0.9 * torch.sign(diff) / n_rgb, 0.1 * torch.sign(ddiff) / n_d
+
+
 def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
                         loss_grad: Optional[Callable] = None) -> RenderFn:
-    """Product backend: the sm_100a rasterizer through the `_C` mirror (C ABI), writing its Gaussian gradients
-    straight into column blocks of a per-keyframe staging buffer that is then added to `flat`.
+    """Product backend: the sm_100a rasterizer through the `_C` mirror (C ABI). The per-Gaussian half of the
+    backward writes 64-byte window rows straight into `flat` (gsr_backward_rows), range by range.
 
     cameras[k] is a synth.Camera-like object with .matrices(device), .W, .H, .tanfovx, .tanfovy; targets[k] =
     (gt_image[3,H,W], gt_depth[1,H,W]).  loss_grad(color, depth, gt_image, gt_depth) -> (loss, dL_dcolor,
-    dL_ddepth); default = the mapping loss of utils/slam_utils.py:101-146 (0.9 L1 rgb + 0.1 L1 depth over gt_depth>0).
+    dL_ddepth); default = mapping_loss_grad.
     """
     from .diff_gaussian_rasterization import _C
 
     cached = {}
+    lg = loss_grad or mapping_loss_grad
 
-    def default_loss_grad(color, depth, gt_image, gt_depth):
-        diff = color - gt_image
-        n_rgb = diff.numel()
-        valid = gt_depth > 0
-        n_d = valid.sum().clamp_min(1)
-        ddiff = (depth - gt_depth) * valid
-        loss = 0.9 * diff.abs().sum() / n_rgb + 0.1 * ddiff.abs().sum() / n_d
-        return loss, 0.9 * torch.sign(diff) / n_rgb, 0.1 * torch.sign(ddiff) / n_d
-
-    lg = loss_grad or default_loss_grad
-    sl = column_slices()
-
-    def render(k: int, params: Dict[str, torch.Tensor], flat: torch.Tensor) -> KeyframeResult:
+    def render(k, params, flat, accumulate, chunks, chunk_done) -> KeyframeResult:
         cam = cameras[k]
         dev = flat.device
         if k not in cached:
@@ -150,18 +183,10 @@ def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
             e, view, proj, proj_raw, cam.tanfovx, cam.tanfovy, cam.H, cam.W, e, 0, campos, False, False)
         gt_image, gt_depth = targets[k]
         loss, dcol, ddep = lg(color, depth, gt_image, gt_depth)
-        out, tau = _C.rasterize_gaussians_backward_fused(
-            bg, params["means3D"], radii, params["colors"], params["scales"], params["rotations"], 1.0, e, view, proj,
-            proj_raw, cam.tanfovx, cam.tanfovy, dcol.contiguous(), ddep.contiguous(), e, 0, campos, geom, R, plist,
-            img, False, want=dict(sh=False, cov3D=False))
-        flat[:, sl["means3D"]] += out["means3D"]
-        flat[:, sl["colors"]] += out["colors"]
-        flat[:, sl["opacities"]] += out["opacity"]
-        flat[:, sl["scales"]] += out["scales"]
-        flat[:, sl["rotations"]] += out["rotations"]
-        vis = radii > 0
-        flat[:, sl["grad2d_norm"]] += (out["means2D"][:, :2].norm(dim=1, keepdim=True) * vis[:, None])
-        flat[:, sl["vis_count"]] += vis[:, None].float()
+        tau, _ = _C.rasterize_gaussians_backward_rows(
+            bg, params["means3D"], radii, params["scales"], params["rotations"], 1.0, view, proj, proj_raw,
+            cam.tanfovx, cam.tanfovy, dcol.contiguous(), ddep.contiguous(), geom, R, plist, img, flat, accumulate,
+            chunks=chunks, chunk_done=chunk_done)
         return KeyframeResult(index=k, radii=radii, n_touched=n_touched, grad_tau=tau, loss=loss)
 
     return render

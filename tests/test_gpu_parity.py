@@ -327,3 +327,108 @@ def test_mark_visible(built):
     m = ours.mark_visible(sc["means3D"], view, proj)
     want = co.mark_visible(sc["means3D"].cpu().numpy(), view.cpu().numpy())
     assert m.dtype == torch.bool and (m.cpu().numpy() == want).all() and 0 < int(m.sum()) < 5000
+
+
+def test_single_call_forward_equals_two_phase(built):
+    """gsr_forward (instance kernels enqueued for a remembered capacity, count read on the device) must give the
+    bits of gsr_forward_plan + gsr_forward_render, also through the GSR_ECAPACITY retry."""
+    cam = synth.make_camera("tum_half", rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))
+    sc = synth.make_scene(30_000, cam, seed=21, device=DEV)
+    bg = torch.tensor([0.1, 0.2, 0.3], device=DEV)
+    key = (30_000, cam.W, cam.H, torch.device(DEV, torch.cuda.current_device()).index)
+    ours._capacity.pop(key, None)
+    fa = _fargs(cam, sc, bg, debug=False)
+    first = ours.rasterize_gaussians(*fa)                 # two-phase (no capacity known yet)
+    assert key in ours._capacity or any(k[:3] == key[:3] for k in ours._capacity)
+    second = ours.rasterize_gaussians(*fa)                # single call
+    for k in list(ours._capacity):
+        if k[:3] == key[:3]:
+            ours._capacity[k] = 1000                      # far too small -> GSR_ECAPACITY -> retry
+    third = ours.rasterize_gaussians(*fa)
+    R = first[0]
+    for other in (second, third):
+        assert other[0] == R
+        for i in (1, 2, 6, 7, 8):                         # color, radii, depth, opacity, n_touched
+            assert torch.equal(first[i], other[i]), i
+        assert torch.equal(first[4].view(torch.int32)[:R], other[4].view(torch.int32)[:R])  # point_list
+        _, nc0, rg0 = _image_state(first[5], cam.W, cam.H)
+        _, nc1, rg1 = _image_state(other[5], cam.W, cam.H)
+        assert (nc0 == nc1).all() and (rg0 == rg1).all()
+    # and the backward consumes the capacity-sized point list
+    dcol = torch.ones(3, cam.H, cam.W, device=DEV) / (cam.H * cam.W)
+    g1 = ours.rasterize_gaussians_backward(*_bargs(fa, first[2], R, first[3], first[4], first[5], dcol, None))
+    g2 = ours.rasterize_gaussians_backward(*_bargs(fa, second[2], R, second[3], second[4], second[5], dcol, None))
+    for a, b in zip(g1, g2):
+        if a.numel():
+            assert rel_inf(b.cpu().numpy(), a.cpu().numpy()) <= 1e-5
+
+
+def test_window_rows_backward_equals_plain_backward(built):
+    """gsr_backward_render + gsr_backward_rows (chunked, write then accumulate) == gsr_backward column for column."""
+    from monogs_b200 import window
+    cam = synth.make_camera("tum_half", rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))
+    P = 20_000
+    sc = synth.make_scene(P, cam, seed=31, anisotropic=True, device=DEV)
+    bg = torch.tensor([0.1, 0.2, 0.3], device=DEV)
+    g = torch.Generator().manual_seed(5)
+    dcol = (torch.randn(3, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
+    ddep = (torch.randn(1, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
+    fa = _fargs(cam, sc, bg, debug=False)
+    R, col, radii, geom, plist, img, dep, opa, nt = ours.rasterize_gaussians(*fa)
+    plain = ours.rasterize_gaussians_backward(*_bargs(fa, radii, R, geom, plist, img, dcol, ddep))
+    view, proj, proj_raw, campos = cam.matrices(DEV)
+    rows = torch.full((P, 16), 7.0, device=DEV)       # garbage: accumulate=False must overwrite it
+    chunks = window.window_chunks(P, 4)
+    assert len(chunks) == 4
+    seen = []
+    tau, m2d = ours.rasterize_gaussians_backward_rows(
+        bg, sc["means3D"], radii, sc["scales"], sc["rotations"], 1.0, view, proj, proj_raw, cam.tanfovx, cam.tanfovy,
+        dcol, ddep, geom, R, plist, img, rows, False, chunks=chunks, chunk_done=lambda a, b: seen.append((a, b)),
+        want_means2D=True)
+    assert seen == chunks
+    n = lambda t: t.detach().cpu().numpy()
+    sl = window.column_slices()
+    vis = (radii > 0)
+    for name, i in (("means3D", 3), ("colors", 1), ("opacities", 2), ("scales", 6), ("rotations", 7)):
+        assert rel_inf(n(rows[:, sl[name]]), n(plain[i])) <= 1e-5, name
+    assert rel_inf(n(m2d), n(plain[0])) <= 1e-5
+    assert torch.equal(rows[:, 15], vis.float())
+    assert rel_inf(n(rows[:, 14]), n(plain[0][:, :2].norm(dim=1) * vis)) <= 1e-5
+    assert rel_inf(n(tau), n(plain[8]).astype(np.float64).sum(0)) <= 1e-4
+    # second keyframe added on top: rows == 2 x single (same keyframe twice)
+    once = rows.clone()
+    ours.rasterize_gaussians_backward_rows(
+        bg, sc["means3D"], radii, sc["scales"], sc["rotations"], 1.0, view, proj, proj_raw, cam.tanfovx, cam.tanfovy,
+        dcol, ddep, geom, R, plist, img, rows, True, chunks=[(0, P)])
+    assert rel_inf(n(rows), 2 * n(once)) <= 1e-5
+
+
+def test_mapping_window_cuda_backend_single_gpu(built):
+    """MappingWindow with the product backend on one GPU: 3 keyframes summed == sum of 3 plain backward calls."""
+    from monogs_b200 import window
+    cams = synth.arc_cameras("tum_half", 3)
+    P = 15_000
+    sc = synth.make_scene(P, cams[1], seed=41, device=DEV)
+    bg = torch.tensor([0.0, 0.0, 0.0], device=DEV)
+    targets = [tuple(t.to(DEV) for t in synth.make_targets(c, seed=i)) for i, c in enumerate(cams)]
+    params = dict(sc)
+    w = window.MappingWindow(window.make_cuda_render_fn(cams, targets, bg))
+    res = w.step(params, 3)
+    assert [r.index for r in res.local] == [0, 1, 2] and all(r.grad_tau.shape == (6,) for r in res.local)
+    want = {k: torch.zeros_like(v) for k, v in res.grads.items()}
+    vis_count = torch.zeros(P, device=DEV)
+    max_r = torch.zeros(P, dtype=torch.int32, device=DEV)
+    for cam, (gi, gd) in zip(cams, targets):
+        fa = _fargs(cam, sc, bg, debug=False)
+        R, col, radii, geom, plist, img, dep, opa, nt = ours.rasterize_gaussians(*fa)
+        loss, dcol, ddep = window.mapping_loss_grad(col, dep, gi, gd)
+        o = ours.rasterize_gaussians_backward(*_bargs(fa, radii, R, geom, plist, img, dcol.contiguous(),
+                                                      ddep.contiguous()))
+        for name, i in (("means3D", 3), ("colors", 1), ("opacities", 2), ("scales", 6), ("rotations", 7)):
+            want[name] += o[i]
+        vis_count += (radii > 0).float()
+        max_r = torch.maximum(max_r, radii)
+    n = lambda t: t.detach().cpu().numpy()
+    for name in want:
+        assert rel_inf(n(res.grads[name]), n(want[name])) <= 1e-4, name
+    assert torch.equal(res.vis_count, vis_count) and torch.equal(res.max_radii, max_r)

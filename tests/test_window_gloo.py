@@ -15,7 +15,7 @@ from conftest import ROOT
 from monogs_b200 import synth, window
 
 N_KF = 5
-P = 600
+P = 6000
 
 
 def _free_port():
@@ -30,7 +30,9 @@ def _oracle_render_fn(cams, params_np, bg):
     from oracle import cpu_oracle as co
     sl = window.column_slices()
 
-    def render(k, params, flat):
+    def render(k, params, flat, accumulate, chunks, chunk_done):
+        if not accumulate:
+            flat.zero_()
         cam = cams[k]
         view, proj, proj_raw, campos = [t.numpy() for t in cam.matrices()]
         n = lambda t: t.numpy()
@@ -50,6 +52,9 @@ def _oracle_render_fn(cams, params_np, bg):
         vis = t(f["radii"] > 0)
         flat[:, sl["grad2d_norm"]] += t(b["means2D"])[:, :2].norm(dim=1, keepdim=True) * vis[:, None]
         flat[:, sl["vis_count"]] += vis[:, None].float()
+        if chunk_done is not None:
+            for c in chunks:
+                chunk_done(*c)
         return window.KeyframeResult(k, t(f["radii"]), t(f["n_touched"]), t(b["tau_sum"].astype(np.float32)))
 
     return render
@@ -68,7 +73,7 @@ def _worker(rank, world, port, out_dir):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     cams, sc = _scene()
     bg = np.array([0.1, 0.2, 0.3], np.float32)
-    w = window.MappingWindow(_oracle_render_fn(cams, None, bg))
+    w = window.MappingWindow(_oracle_render_fn(cams, None, bg), n_chunks=3)
     res = w.step(sc, N_KF)
     assert [r.index for r in res.local] == window.shard_keyframes(N_KF, world, rank)
     torch.save(dict(grads={k: v.clone() for k, v in res.grads.items()}, g2=res.grad2d_norm.clone(),
@@ -87,6 +92,13 @@ def test_shard_keyframes():
     with pytest.raises(ValueError):
         window.shard_keyframes(8, 2, 2)
     assert window.N_COLS == 16 and window.column_slices()["rotations"] == slice(10, 14)
+    # ranges: 256-aligned, contiguous cover of [0, P), shrinking, identical on every rank
+    for P in (1, 255, 4096, 100_001, 1_000_000):
+        ch = window.window_chunks(P, 4)
+        assert ch[0][0] == 0 and ch[-1][1] == P and all(a[1] == b[0] for a, b in zip(ch[:-1], ch[1:]))
+        assert all(a % 256 == 0 for a, _ in ch)
+    ch = window.window_chunks(1_000_000, 4)
+    assert len(ch) == 4 and (ch[0][1] - ch[0][0]) > (ch[-1][1] - ch[-1][0])
 
 
 def test_two_ranks_equal_one_rank(built, tmp_path):
