@@ -241,12 +241,13 @@ class OursDeviceStep:
         """Sharded mapping window (monogs_b200/window.py): per-pixel half, then the per-Gaussian half range by
         range into 64-byte window rows; each finished range goes to an async NCCL allreduce (the one exchange step
         of the path) while the next range is computed; the step ends when the last allreduce has completed."""
-        from monogs_b200.window import window_chunks
+        from monogs_b200.window import RowExchange, window_chunks
         lib, wl, sc = self.lib, self.wl, self.wl.scene
         P, W, H = wl.P, wl.W, wl.H
         if self.rows is None:
-            self.rows = torch.empty(P, 16, device=wl.dev)
-            self.chunks = window_chunks(P, 4)
+            self.exchange = RowExchange()
+            self.rows = self.exchange.allocate(P, wl.dev)   # symmetric memory when NVLS multicast is available
+            self.chunks = window_chunks(P, 1)
         rc = lib.gsr_backward_render(st, P, W, H, wl.bg.data_ptr(), self.geom.data_ptr(), self.img.data_ptr(),
                                      self.plist.data_ptr(), R, wl.dcol.data_ptr(), wl.ddep.data_ptr(),
                                      self.scratch.data_ptr(), 0)
@@ -259,7 +260,9 @@ class OursDeviceStep:
                                        self.geom.data_ptr(), self.scratch.data_ptr(), self.rows.data_ptr(), 0,
                                        self.means2D.data_ptr(), self.tau.data_ptr(), 0)
             assert rc == 0, rc
-            works.append(dist.all_reduce(self.rows[p0:p1], async_op=True))
+            w = self.exchange.reduce(self.rows, p0, p1)
+            if w is not None:
+                works.append(w)
         for w in works:
             w.wait()  # the current stream waits for the exchange: it is part of the timed step
 
@@ -623,9 +626,9 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl_name, "detail": wl.desc, "image": [wl.W, wl.H], "gaussians": wl.P,
                    "l2": "256 MiB flush write before every timed step (outside the event pairs)",
-                   "multi_gpu": ("mapping window: one keyframe per GPU; NCCL allreduce of the [P,16] window rows "
-                                 "(14 gradient + 2 densification columns) inside the step, issued per Gaussian "
-                                 "range and overlapped with the per-Gaussian backward of the next range")
+                   "multi_gpu": ("mapping window: one keyframe per GPU; sum of the [P,16] window rows (14 gradient + 2 "
+                                 "densification columns) over the ranks inside the step, exchange = "
+                                 + getattr(getattr(stepper, "exchange", None), "mode", "all_reduce"))
                                 if world > 1 else "single keyframe",
                    "units": units},
         "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches,

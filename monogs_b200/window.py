@@ -86,11 +86,78 @@ class WindowStepResult:
 RenderFn = Callable[..., KeyframeResult]
 
 
+class RowExchange:
+    """The one exchange step: sum of the [P,16] window rows over the ranks.
+
+    On NVSwitch boxes the rows live in symmetric memory and are reduced IN THE SWITCH (NVLS multimem
+    ld_reduce / st through torch.distributed._symmetric_memory): measured on 8 x B200 at 64 MB: 0.172 ms vs
+    0.278 ms for ncclAllReduce (gpurun_out/nccl_probe2_n8.json, profiles/r01_nccl_probe_n8.json). Elsewhere
+    (gloo on CPU, no multicast support) it is a plain all_reduce. Splitting the rows into ranges to overlap the
+    allreduce with the per-Gaussian backward was measured and rejected: 4 pieces cost 0.47 ms (latency-bound
+    collectives) against 0.064 ms of overlappable compute -- so the default is ONE range."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.mode = "all_reduce"
+        self._name = None
+
+    def allocate(self, P: int, device) -> torch.Tensor:
+        device = torch.device(device)
+        world = dist.get_world_size(self.group) if dist.is_initialized() else 1
+        if device.type == "cuda" and world > 1:
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+                grp = self.group if self.group is not None else dist.group.WORLD
+                t = symm_mem.empty(P * N_COLS, dtype=torch.float32, device=device)
+                hdl = symm_mem.rendezvous(t, grp.group_name)
+                if getattr(hdl, "multicast_ptr", 0) and hasattr(torch.ops.symm_mem, "multimem_all_reduce_"):
+                    self._name = grp.group_name
+                    flat = t.view(P, N_COLS)
+                    self.mode = self._pick(flat)
+                    return flat
+            except Exception:  # no symmetric memory / multicast on this system: NCCL ring/tree instead
+                pass
+        return torch.empty(P, N_COLS, dtype=torch.float32, device=device)
+
+    def _pick(self, flat: torch.Tensor) -> str:
+        """Time both exchanges once on the real buffer and keep the faster (the in-switch reduction wins at 8 GPUs,
+        ncclAllReduce at 2); the decision is made identical on every rank with a MAX-allreduce of the timings."""
+        flat.zero_()
+        times = []
+        for mode in ("multimem", "all_reduce"):
+            self.mode = mode
+            for _ in range(2):
+                w = self.reduce(flat, 0, flat.shape[0])
+                if w is not None:
+                    w.wait()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(flat.device)
+            a.record()
+            for _ in range(3):
+                w = self.reduce(flat, 0, flat.shape[0])
+                if w is not None:
+                    w.wait()
+            b.record()
+            torch.cuda.synchronize(flat.device)
+            times.append(a.elapsed_time(b))
+        t = torch.tensor(times, dtype=torch.float64, device=flat.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return "multimem" if float(t[0]) < float(t[1]) else "all_reduce"
+
+    def reduce(self, flat: torch.Tensor, p0: int, p1: int):
+        """Start the sum of rows [p0, p1); returns a handle with .wait() or None when already stream-ordered."""
+        if self.mode == "multimem":
+            torch.ops.symm_mem.multimem_all_reduce_(flat.view(-1)[p0 * N_COLS:p1 * N_COLS], "sum", self._name)
+            return None
+        return dist.all_reduce(flat[p0:p1], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+
+
 class MappingWindow:
-    def __init__(self, render_fn: RenderFn, group: Optional[dist.ProcessGroup] = None, n_chunks: int = 4):
+    def __init__(self, render_fn: RenderFn, group: Optional[dist.ProcessGroup] = None, n_chunks: int = 1):
         self.render_fn = render_fn
         self.group = group
         self.n_chunks = n_chunks
+        self.exchange = RowExchange(group)
         self._flat: Optional[torch.Tensor] = None
         self._radii: Optional[torch.Tensor] = None
 
@@ -104,7 +171,7 @@ class MappingWindow:
 
     def _buffers(self, P: int, device) -> None:
         if self._flat is None or self._flat.shape[0] != P or self._flat.device != torch.device(device):
-            self._flat = torch.empty(P, N_COLS, dtype=torch.float32, device=device)
+            self._flat = self.exchange.allocate(P, device)
             self._radii = torch.empty(P, dtype=torch.int32, device=device)
 
     def step(self, params: Dict[str, torch.Tensor], n_keyframes: int) -> WindowStepResult:
@@ -121,7 +188,9 @@ class MappingWindow:
 
         def chunk_done(p0, p1):
             if world > 1:
-                works.append(dist.all_reduce(flat[p0:p1], op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+                w = self.exchange.reduce(flat, p0, p1)
+                if w is not None:
+                    works.append(w)
 
         mine = shard_keyframes(n_keyframes, world, self.rank)
         local = []
