@@ -342,7 +342,7 @@ class _RefFunction(torch.autograd.Function):
 
 class E2EStep:
     """One mapping-shaped iteration the way a MonoGS caller does it: parameters arrive from PINNED HOST memory,
-    render through the public API, 0.9 L1(rgb) + 0.1 L1(depth) loss (utils/slam_utils.py:101-146 without the masks),
+    render through the public API, the mapping loss 0.9 L1(rgb) + 0.1 L1(depth over gt_depth > 0) (utils/slam_utils.py:101-146),
     backward, and the loss + pose gradient are read back to the host."""
 
     NAMES = ("means3D", "colors", "opacities", "scales", "rotations")
@@ -365,7 +365,7 @@ class E2EStep:
         self.host_out = torch.empty(7, dtype=torch.float32).pin_memory()
         self.h2d = sum(t.numel() * 4 for t in self.pinned.values()) + (self.pinned_img.numel() + self.pinned_dep.numel()) * 4
         self.d2h = 7 * 4
-        if impl == "ours":
+        if impl in ("ours", "ours-fused"):
             from monogs_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
             s = GaussianRasterizationSettings(wl.H, wl.W, wl.cam.tanfovx, wl.cam.tanfovy, wl.bg, 1.0, wl.view, wl.proj,
                                               wl.proj_raw, 0, wl.campos, False, False)
@@ -394,7 +394,13 @@ class E2EStep:
         means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
         theta = torch.zeros(3, device=wl.dev, requires_grad=True)
         rho = torch.zeros(3, device=wl.dev, requires_grad=True)
-        if self.impl == "ours":
+        if self.impl == "ours-fused":
+            from monogs_b200.fused_loss import render_l1_loss
+            loss = render_l1_loss(self.rasterizer.raster_settings, leaves["means3D"], means2D, leaves["opacities"],
+                                  colors_precomp=leaves["colors"], scales=leaves["scales"],
+                                  rotations=leaves["rotations"], theta=theta, rho=rho, gt_rgb=dev_img,
+                                  gt_depth=dev_dep, kind="mapping")[0]
+        elif self.impl == "ours":
             color, radii, depth, opacity, n_touched = self.rasterizer(
                 means3D=leaves["means3D"], means2D=means2D, shs=None, colors_precomp=leaves["colors"],
                 opacities=leaves["opacities"], scales=leaves["scales"], rotations=leaves["rotations"],
@@ -403,7 +409,11 @@ class E2EStep:
             color, radii, depth, opacity, n_touched = _RefFunction.apply(
                 self.ref, wl, leaves["means3D"], means2D, leaves["colors"], leaves["opacities"], leaves["scales"],
                 leaves["rotations"], theta, rho)
-        loss = 0.9 * (color - dev_img).abs().mean() + 0.1 * (depth - dev_dep).abs().mean()
+        if self.impl != "ours-fused":
+            # get_loss_mapping (utils/slam_utils.py:101-146): 0.9 L1(rgb) + 0.1 L1(depth over gt_depth > 0)
+            valid = (dev_dep > 0).float()
+            loss = 0.9 * (color - dev_img).abs().mean() + \
+                0.1 * ((depth - dev_dep).abs() * valid).sum() / valid.sum().clamp_min(1.0)
         loss.backward()
         if self.world > 1:
             flat = torch.cat([leaves[k].grad.reshape(-1) for k in self.NAMES])
@@ -614,6 +624,24 @@ def main():
                "api": "GaussianRasterizer.forward + loss.backward()" if impl == "ours" else
                       "reference CUDA via oracle/_ref + loss.backward()"}
 
+    e2e_fused = None
+    if not a.no_e2e and impl == "ours":
+        # the same iteration through the ADDITIONAL fused entry point (monogs_b200.fused_loss.render_l1_loss)
+        ef = E2EStep(wl, world, "ours-fused")
+        for _ in range(3):
+            ef.step()
+        barrier(world)
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(k_e2e):
+            ef.step()
+        t1.record()
+        barrier(world)
+        ef_s = max_over_ranks(t0.elapsed_time(t1) / 1e3, world, dev)
+        e2e_fused = {"value": world * k_e2e / ef_s, "unit": "it/s", "h2d_bytes_per_step": ef.h2d,
+                     "d2h_bytes_per_step": ef.d2h, "api": "fused_loss.render_l1_loss + loss.backward()"}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -633,6 +661,8 @@ def main():
                    "units": units},
         "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches,
     }
+    if e2e_fused:
+        line["e2e_fused_loss"] = e2e_fused
     if impl == "reference":
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": value, "unit": "it/s", "cores": 0, "kind": "reference",

@@ -142,6 +142,56 @@ int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs,
                  float* dL_dscales, float* dL_drotations,
                  float* dL_dtau_per_gaussian, float* dL_dtau, int debug);
 
+/* ---- fused L1 photometric + depth loss (north star (d); the callers' losses, utils/slam_utils.py:58-146) ----
+ * gsr_l1_loss_forward reduces the rendered images against the targets: out[8] (device) =
+ *   { loss, l1_rgb, l1_depth, k_rgb, k_depth, dL/d exposure_a, dL/d exposure_b, mean opacity }.
+ *   GSR_LOSS_MAPPING : lambda_rgb * mean_{mask,3ch}|e^a I + b - gt| + (1 - lambda_rgb) * mean_{gtD>0}|D - gtD|
+ *                      (get_loss_mapping :101-146; lambda_rgb is its `lambda_depth` = 0.9)
+ *   GSR_LOSS_TRACKING: 0.5 * mean(opacity) * mean_{3HW}(m|e^a I + b - gt|) + mean_{gtD>0, opacity>0.99}|D - gtD|,
+ *                      m = mask * grad_mask * (opacity > 0.99)   (get_loss_tracking :58-98)
+ *   mask / grad_mask: uint8 0/1 [H,W] or NULL (= all ones); exposure_a/b: device scalars or NULL (a = b = 0);
+ *   gt_depth may be NULL (no depth term). scratch: 64 bytes of device memory.
+ * gsr_backward_l1 is gsr_backward with dL/dpixel formed inside the backward tile renderer from the same
+ * images (no gradient images are materialised): loss->out is the out[8] above, loss->upstream the device scalar
+ * dL/dloss (NULL = 1). */
+#define GSR_LOSS_NONE 0
+#define GSR_LOSS_MAPPING 1
+#define GSR_LOSS_TRACKING 2
+typedef struct gsr_l1_loss {
+  int kind;
+  const float* color;      /* [3,H,W] rendered (forward output) */
+  const float* depth;      /* [1,H,W] */
+  const float* opacity;    /* [1,H,W] */
+  const float* gt_rgb;     /* [3,H,W] */
+  const float* gt_depth;   /* [1,H,W] or NULL */
+  const uint8_t* mask;     /* [H,W] or NULL */
+  const uint8_t* grad_mask;/* [H,W] or NULL (tracking) */
+  const float* exposure_a; /* device scalar or NULL */
+  const float* exposure_b; /* device scalar or NULL */
+  const float* out;        /* out[8] of gsr_l1_loss_forward */
+  const float* upstream;   /* device scalar dL/dloss or NULL */
+} gsr_l1_loss;
+int gsr_l1_loss_forward(void* stream, int kind, int width, int height, const float* color,
+                        const float* depth, const float* opacity, const float* gt_rgb,
+                        const float* gt_depth, const uint8_t* mask, const uint8_t* grad_mask,
+                        const float* exposure_a, const float* exposure_b, float lambda_rgb,
+                        void* scratch, float* out);
+int gsr_backward_l1(void* stream, int P, int sh_degree, int sh_coeffs,
+                    int width, int height, const float* background,
+                    const float* means3D, const float* shs,
+                    const float* colors_precomp, const float* scales,
+                    float scale_modifier, const float* rotations,
+                    const float* cov3D_precomp, const float* viewmatrix,
+                    const float* projmatrix, const float* projmatrix_raw,
+                    const float* campos, float tan_fovx, float tan_fovy,
+                    const int* radii, const void* geom_ws, const void* image_ws,
+                    const uint32_t* point_list, int64_t num_rendered,
+                    const gsr_l1_loss* loss, void* scratch,
+                    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                    float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                    float* dL_dscales, float* dL_drotations,
+                    float* dL_dtau_per_gaussian, float* dL_dtau, int debug);
+
 /* ---- backward for the sharded mapping window (monogs_b200/window.py; no reference counterpart: it forms
  * the sums loss.backward() makes over the window's keyframes, utils/slam_mapper.py:273-322,394) ------------
  * gsr_backward_render: the per-pixel half (zeroes the partial-gradient scratch, then the backward tile renderer).

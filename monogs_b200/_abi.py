@@ -8,7 +8,10 @@ from __future__ import annotations
 import ctypes as C
 from pathlib import Path
 
-_LIB_PATH = Path(__file__).resolve().parent / "libgsr_b200.so"
+import os
+
+# GSR_B200_LIB selects an experimental build variant (monogs_b200/build.py --variant); default = the product library
+_LIB_PATH = Path(os.environ.get("GSR_B200_LIB") or (Path(__file__).resolve().parent / "libgsr_b200.so"))
 
 vp, i32, i64, f32, sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
 
@@ -28,6 +31,9 @@ SIGNATURES = {
                           vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, C.POINTER(i64), i32]),
     "gsr_backward": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, f32, f32,
                            vp, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
+    "gsr_l1_loss_forward": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, f32, vp, vp]),
+    "gsr_backward_l1": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, f32, f32,
+                              vp, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
     "gsr_backward_render": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, i64, vp, vp, vp, i32]),
     "gsr_backward_rows": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, f32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, i32,
                                 vp, vp, i32]),
@@ -41,6 +47,14 @@ SIGNATURES = {
     "gsr_debug_image_views": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "gsr_debug_sorted_keys": (i32, [vp, vp, vp, vp, i32, i64, i32, i32, vp]),
 }
+
+class L1LossSpec(C.Structure):
+    """gsr_l1_loss of include/gsr_b200.h."""
+    _fields_ = [("kind", i32)] + [(n, vp) for n in ("color", "depth", "opacity", "gt_rgb", "gt_depth", "mask",
+                                                     "grad_mask", "exposure_a", "exposure_b", "out", "upstream")]
+
+
+LOSS_MAPPING, LOSS_TRACKING = 1, 2
 
 STAGES = ("preprocess", "depth_sort", "scan", "emit", "tile_sort", "ranges", "render_fwd", "render_bwd",
           "preprocess_bwd")

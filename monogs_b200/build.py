@@ -19,7 +19,7 @@ OBJ = ROOT / "build"
 LIB = ROOT / "libgsr_b200.so"
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 SOURCES = ["preprocess.cu", "binning.cu", "radix_sort.cu", "render_fwd.cu", "render_bwd.cu",
-           "preprocess_bwd.cu", "knn.cu", "api.cu"]
+           "preprocess_bwd.cu", "knn.cu", "loss.cu", "api.cu"]
 FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
@@ -31,6 +31,26 @@ def _stamp() -> str:
         h.update(p.read_bytes())
     h.update(" ".join(FLAGS).encode())
     return h.hexdigest()
+
+
+def build_variant(name: str, defines) -> Path:
+    """Experimental variant monogs_b200/libgsr_b200_<name>.so with extra -D flags (selected with GSR_B200_LIB)."""
+    obj = ROOT / f"build_{name}"
+    obj.mkdir(exist_ok=True)
+    lib = ROOT / f"libgsr_b200_{name}.so"
+    objs = []
+    for src in SOURCES:
+        o = obj / (src + ".o")
+        r = subprocess.run([NVCC, *FLAGS, *[f"-D{d}" for d in defines], "-c", str(CSRC / src), "-o", str(o)],
+                           capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(r.stderr)
+        objs.append(str(o))
+    r = subprocess.run([NVCC, "-shared", "-o", str(lib), *objs, "-gencode", "arch=compute_100a,code=sm_100a"],
+                       capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(r.stderr)
+    return lib
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
@@ -67,4 +87,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--variant" in sys.argv:
+        i = sys.argv.index("--variant")
+        print(build_variant(sys.argv[i + 1], sys.argv[i + 2:]))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -270,16 +270,17 @@ int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs, int width, in
   return *num_rendered > capacity ? GSR_ECAPACITY : GSR_OK;
 }
 
-int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
-                 const float* background, const float* means3D, const float* shs, const float* colors_precomp,
-                 const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
-                 const float* viewmatrix, const float* projmatrix, const float* projmatrix_raw,
-                 const float* campos, float tan_fovx, float tan_fovy, const int* radii, const void* geom_ws,
-                 const void* image_ws, const uint32_t* point_list, int64_t num_rendered,
-                 const float* dL_dout_color, const float* dL_dout_depth, void* scratch, float* dL_dmeans2D,
-                 float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
-                 float* dL_dscales, float* dL_drotations, float* dL_dtau_per_gaussian, float* dL_dtau,
-                 int debug) {
+static int backward_impl(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
+                         const float* background, const float* means3D, const float* shs,
+                         const float* colors_precomp, const float* scales, float scale_modifier,
+                         const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                         const float* projmatrix, const float* projmatrix_raw, const float* campos, float tan_fovx,
+                         float tan_fovy, const int* radii, const void* geom_ws, const void* image_ws,
+                         const uint32_t* point_list, int64_t num_rendered, const float* dL_dout_color,
+                         const float* dL_dout_depth, const LossView& loss, void* scratch, float* dL_dmeans2D,
+                         float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                         float* dL_dsh, float* dL_dscales, float* dL_drotations, float* dL_dtau_per_gaussian,
+                         float* dL_dtau, int debug) {
   if (P < 0 || width <= 0 || height <= 0 || num_rendered < 0) return GSR_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   if (P == 0) {
@@ -301,7 +302,7 @@ int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs, int width, i
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
-                                    dL_dout_depth, bw.packed)));
+                                    dL_dout_depth, loss, bw.packed)));
     GSR_TRY(debug_sync(st, debug));
   }
   const float* shs_used = colors_precomp ? nullptr : shs;
@@ -312,6 +313,68 @@ int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs, int width, i
                                       dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
                                       dL_drotations, dL_dtau_per_gaussian, dL_dtau, 0, P, nullptr, 0)));
   return debug_sync(st, debug);
+}
+
+static LossView no_loss() {
+  LossView l{};
+  l.kind = GSR_LOSS_NONE;
+  return l;
+}
+
+int gsr_backward(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
+                 const float* background, const float* means3D, const float* shs, const float* colors_precomp,
+                 const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                 const float* viewmatrix, const float* projmatrix, const float* projmatrix_raw,
+                 const float* campos, float tan_fovx, float tan_fovy, const int* radii, const void* geom_ws,
+                 const void* image_ws, const uint32_t* point_list, int64_t num_rendered,
+                 const float* dL_dout_color, const float* dL_dout_depth, void* scratch, float* dL_dmeans2D,
+                 float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                 float* dL_dscales, float* dL_drotations, float* dL_dtau_per_gaussian, float* dL_dtau,
+                 int debug) {
+  return backward_impl(stream, P, sh_degree, sh_coeffs, width, height, background, means3D, shs, colors_precomp,
+                       scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw,
+                       campos, tan_fovx, tan_fovy, radii, geom_ws, image_ws, point_list, num_rendered,
+                       dL_dout_color, dL_dout_depth, no_loss(), scratch, dL_dmeans2D, dL_dcolors, dL_dopacity,
+                       dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, dL_dtau_per_gaussian, dL_dtau,
+                       debug);
+}
+
+int gsr_l1_loss_forward(void* stream, int kind, int width, int height, const float* color, const float* depth,
+                        const float* opacity, const float* gt_rgb, const float* gt_depth, const uint8_t* mask,
+                        const uint8_t* grad_mask, const float* exposure_a, const float* exposure_b,
+                        float lambda_rgb, void* scratch, float* out) {
+  if ((kind != GSR_LOSS_MAPPING && kind != GSR_LOSS_TRACKING) || width <= 0 || height <= 0) return GSR_EINVAL;
+  if (!color || !gt_rgb || !scratch || !out) return GSR_EINVAL;
+  if (gt_depth && !depth) return GSR_EINVAL;
+  if (kind == GSR_LOSS_TRACKING && !opacity) return GSR_EINVAL;
+  return check(launch_l1_loss((cudaStream_t)stream, kind, width, height, color, depth, opacity, gt_rgb, gt_depth,
+                              mask, grad_mask, exposure_a, exposure_b, lambda_rgb, (double*)scratch, out));
+}
+
+int gsr_backward_l1(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
+                    const float* background, const float* means3D, const float* shs, const float* colors_precomp,
+                    const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                    const float* viewmatrix, const float* projmatrix, const float* projmatrix_raw,
+                    const float* campos, float tan_fovx, float tan_fovy, const int* radii, const void* geom_ws,
+                    const void* image_ws, const uint32_t* point_list, int64_t num_rendered,
+                    const gsr_l1_loss* loss, void* scratch, float* dL_dmeans2D, float* dL_dcolors,
+                    float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                    float* dL_drotations, float* dL_dtau_per_gaussian, float* dL_dtau, int debug) {
+  if (!loss || (loss->kind != GSR_LOSS_MAPPING && loss->kind != GSR_LOSS_TRACKING)) return GSR_EINVAL;
+  if (!loss->color || !loss->gt_rgb || !loss->out || (loss->gt_depth && !loss->depth)) return GSR_EINVAL;
+  if (loss->kind == GSR_LOSS_TRACKING && !loss->opacity) return GSR_EINVAL;
+  LossView lv{};
+  lv.kind = loss->kind;
+  lv.color = loss->color; lv.depth = loss->depth; lv.opacity = loss->opacity;
+  lv.gt_rgb = loss->gt_rgb; lv.gt_depth = loss->gt_depth;
+  lv.mask = loss->mask; lv.grad_mask = loss->grad_mask;
+  lv.exposure_a = loss->exposure_a; lv.exposure_b = loss->exposure_b;
+  lv.out = loss->out; lv.upstream = loss->upstream;
+  return backward_impl(stream, P, sh_degree, sh_coeffs, width, height, background, means3D, shs, colors_precomp,
+                       scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw,
+                       campos, tan_fovx, tan_fovy, radii, geom_ws, image_ws, point_list, num_rendered, nullptr,
+                       nullptr, lv, scratch, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
+                       dL_dscales, dL_drotations, dL_dtau_per_gaussian, dL_dtau, debug);
 }
 
 int gsr_backward_render(void* stream, int P, int width, int height, const float* background, const void* geom_ws,
@@ -332,7 +395,7 @@ int gsr_backward_render(void* stream, int P, int width, int height, const float*
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
-                                    dL_dout_depth, bw.packed)));
+                                    dL_dout_depth, no_loss(), bw.packed)));
   }
   return debug_sync(st, debug);
 }

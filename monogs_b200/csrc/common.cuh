@@ -54,7 +54,10 @@ __host__ __device__ inline size_t num_tiles(int W, int H) {
 constexpr int SORT_RADIX_BITS = 8;   // widest digit of a pass
 constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_TILE_MIN = 256 * 8;             // smallest tile a sort pass uses (look-back words are sized for it)
-constexpr long long SORT_SMALL_N = 1ll << 21;      // up to here the 2048-key tile is used (more CTAs in flight)
+#ifndef GSR_SORT_SMALL_N_LOG2
+#define GSR_SORT_SMALL_N_LOG2 21
+#endif
+constexpr long long SORT_SMALL_N = 1ll << GSR_SORT_SMALL_N_LOG2;      // up to here the 2048-key tile is used (more CTAs in flight)
 constexpr int SORT_MAX_PASSES = 8;
 __host__ __device__ inline size_t sort_blocks(int64_t n) { return (size_t)((n + SORT_TILE_MIN - 1) / SORT_TILE_MIN); }
 
@@ -219,6 +222,17 @@ __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
 #define GSR_DEVINL __device__ __forceinline__
 #endif
+
+// Fused L1 loss (loss.cu): what the backward tile renderer needs to form dL/dpixel on the fly.
+struct LossView {
+  int kind;  // GSR_LOSS_NONE: use the dL_dpix images instead
+  const float* color; const float* depth; const float* opacity;   // rendered images of the forward
+  const float* gt_rgb; const float* gt_depth;                      // targets ([3,H,W], [1,H,W] or NULL)
+  const uint8_t* mask; const uint8_t* grad_mask;                   // [H,W] 0/1 or NULL
+  const float* exposure_a; const float* exposure_b;                // device scalars or NULL
+  const float* out;                                                // out[8] of launch_l1_loss (device)
+  const float* upstream;                                           // dL/dloss (device scalar) or NULL = 1
+};
 
 // Camera constants passed by value (kernel parameter -> constant bank).
 struct CameraParams {

@@ -48,7 +48,13 @@ cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& i
 // render_bwd.cu
 cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, const float* dL_dpix,
-                              const float* dL_dpix_depth, float* packed);
+                              const float* dL_dpix_depth, const LossView& loss, float* packed);
+
+// loss.cu
+cudaError_t launch_l1_loss(cudaStream_t st, int kind, int W, int H, const float* color, const float* depth,
+                           const float* opacity, const float* gt_rgb, const float* gt_depth, const uint8_t* mask,
+                           const uint8_t* grad_mask, const float* exposure_a, const float* exposure_b,
+                           float lambda_rgb, double* acc, float* out);
 
 // preprocess_bwd.cu
 cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const float* means3D, const int* radii,

@@ -24,7 +24,10 @@ namespace gsr {
 
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_LOOKBACK_BATCH = 8;
+#ifndef GSR_RS_LOOKBACK_BATCH
+#define GSR_RS_LOOKBACK_BATCH 8
+#endif
+constexpr int RS_LOOKBACK_BATCH = GSR_RS_LOOKBACK_BATCH;
 constexpr uint32_t FLAG_LOCAL = 1u << 30;
 constexpr uint32_t FLAG_INCL = 2u << 30;
 constexpr uint32_t FLAG_MASK = 3u << 30;

@@ -94,7 +94,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   int tiles_x, const float* __restrict__ bg, const float4* __restrict__ rec_a,
                   const float4* __restrict__ rec_b, const float4* __restrict__ rec_c,
                   const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
-                  const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth,
+                  const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth, LossView loss,
                   float* __restrict__ packed /*[P][GRAD_STRIDE]*/) {
   __shared__ __align__(16) RbStage stage[2];
   __shared__ uint32_t s_max[RB_THREADS / 32];
@@ -114,9 +114,29 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const float T_final = inside ? final_T[pix] : 0.0f;
   const uint32_t last_contributor = inside ? n_contrib[pix] : 0u;
   float dpr = 0.f, dpg = 0.f, dpb = 0.f, dpd = 0.f;
-  if (inside) {
+  if (inside && loss.kind == GSR_LOSS_NONE) {
     if (dL_dpix) { dpr = dL_dpix[pix]; dpg = dL_dpix[HW + pix]; dpb = dL_dpix[2 * HW + pix]; }
     if (dL_dpix_depth) dpd = dL_dpix_depth[pix];
+  } else if (inside) {
+    // fused L1 loss gradient (loss.cu): dL/dI_c = up * k_rgb * sign(e^a I_c + b - gt_c) on the masked pixels,
+    // dL/dD = up * k_d * sign(D - gtD) on the valid-depth pixels
+    const float up = loss.upstream ? *loss.upstream : 1.0f;
+    const float ea = loss.exposure_a ? expf(*loss.exposure_a) : 1.0f;
+    const float eb = loss.exposure_b ? *loss.exposure_b : 0.0f;
+    const bool om = loss.kind == GSR_LOSS_TRACKING ? (loss.opacity[pix] > 0.99f) : true;
+    bool m = loss.mask ? loss.mask[pix] != 0 : true;
+    if (loss.kind == GSR_LOSS_TRACKING) m = m && om && (loss.grad_mask ? loss.grad_mask[pix] != 0 : true);
+    auto sgn = [](float d) { return d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f); };
+    if (m) {
+      const float k = up * loss.out[3];
+      dpr = k * sgn(ea * loss.color[pix] + eb - loss.gt_rgb[pix]);
+      dpg = k * sgn(ea * loss.color[HW + pix] + eb - loss.gt_rgb[HW + pix]);
+      dpb = k * sgn(ea * loss.color[2 * HW + pix] + eb - loss.gt_rgb[2 * HW + pix]);
+    }
+    if (loss.gt_depth) {
+      const float gd = loss.gt_depth[pix];
+      if (gd > 0.f && om) dpd = up * loss.out[4] * sgn(loss.depth[pix] - gd);
+    }
   }
   const float bg_dot_dpixel = bg[0] * dpr + bg[1] * dpg + bg[2] * dpb;
 
@@ -244,11 +264,11 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 
 cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, const float* dL_dpix,
-                              const float* dL_dpix_depth, float* packed) {
+                              const float* dL_dpix_depth, const LossView& loss, float* packed) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y);
   count_launch(); render_bwd_kernel<<<grid, RB_THREADS, 0, st>>>(im.ranges, point_list, W, H, tiles_x, bg, g.rec_a, g.rec_b,
-                                                 g.rec_c, im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, packed);
+                                                 g.rec_c, im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, loss, packed);
   return cudaGetLastError();
 }
 

@@ -1,0 +1,10 @@
+#!/bin/bash
+# tools/variant_bench.sh v1 v2 ... -- bench stage times of experimental library variants (monogs_b200/libgsr_b200_<v>.so)
+mkdir -p gpurun_out
+for v in base "$@"; do
+  if [ $v = base ]; then unset GSR_B200_LIB; else export GSR_B200_LIB=$PWD/monogs_b200/libgsr_b200_$v.so; fi
+  python bench.py --steps 30 --warmup 5 --no-e2e --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json
+d=json.loads(sys.stdin.read())
+print('$v', round(d['ms_per_step'],4), json.dumps(d['stages_ms_per_step']))" | tee -a gpurun_out/variants.log
+done
