@@ -346,22 +346,26 @@ class E2EStep:
     backward, and the loss + pose gradient are read back to the host."""
 
     NAMES = ("means3D", "colors", "opacities", "scales", "rotations")
+    SLOTS = 3
 
     def __init__(self, wl: Workload, world, impl):
         self.wl, self.world, self.impl = wl, world, impl
         self.pinned = {k: wl.host[k].contiguous().pin_memory() for k in self.NAMES}
         self.pinned_img = wl.gt_image.contiguous().pin_memory()
         self.pinned_dep = wl.gt_depth.contiguous().pin_memory()
-        # double-buffered device staging: the H2D copy of step i+1's inputs runs on a copy stream while step i
-        # computes (every step still copies its own 61 MB from pinned host memory inside the timed region)
-        self.dev_buf = [{k: torch.empty_like(wl.host[k], device=wl.dev) for k in self.NAMES} for _ in range(2)]
-        self.dev_img = [torch.empty_like(wl.gt_image, device=wl.dev) for _ in range(2)]
-        self.dev_dep = [torch.empty_like(wl.gt_depth, device=wl.dev) for _ in range(2)]
+        # triple-buffered device staging: the H2D copies of the next two steps' inputs run on a copy stream while
+        # step i computes, so the copy engine never waits for the host (every step still copies its own 61 MB from
+        # pinned host memory inside the timed region)
+        S = self.SLOTS
+        self.dev_buf = [{k: torch.empty_like(wl.host[k], device=wl.dev) for k in self.NAMES} for _ in range(S)]
+        self.dev_img = [torch.empty_like(wl.gt_image, device=wl.dev) for _ in range(S)]
+        self.dev_dep = [torch.empty_like(wl.gt_depth, device=wl.dev) for _ in range(S)]
         self.copy_stream = torch.cuda.Stream(device=wl.dev)
-        self.ready = [torch.cuda.Event(), torch.cuda.Event()]
-        self.consumed = [torch.cuda.Event(), torch.cuda.Event()]
+        self.ready = [torch.cuda.Event() for _ in range(S)]
+        self.consumed = [torch.cuda.Event() for _ in range(S)]
         self.i = 0
         self._prefetch(0)
+        self._prefetch(1)
         self.host_out = torch.empty(7, dtype=torch.float32).pin_memory()
         self.h2d = sum(t.numel() * 4 for t in self.pinned.values()) + (self.pinned_img.numel() + self.pinned_dep.numel()) * 4
         self.d2h = 7 * 4
@@ -385,10 +389,10 @@ class E2EStep:
 
     def step(self):
         wl = self.wl
-        slot = self.i & 1
+        slot = self.i % self.SLOTS
         self.i += 1
         torch.cuda.current_stream().wait_event(self.ready[slot])
-        self._prefetch(slot ^ 1)                              # next step's inputs, overlapped with this step
+        self._prefetch((slot + 2) % self.SLOTS)               # inputs of step i+2, overlapped with steps i, i+1
         leaves = {k: self.dev_buf[slot][k].detach().requires_grad_(True) for k in self.NAMES}
         dev_img, dev_dep = self.dev_img[slot], self.dev_dep[slot]
         means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)

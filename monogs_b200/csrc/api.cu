@@ -2,6 +2,8 @@
 // Host-side orchestration only: argument checks, workspace carving, kernel
 // launches on the caller's stream.  See the header for which reference
 // interface each entry point replaces.
+#include <cstdlib>
+#include <cstring>
 #include <mutex>
 #include <vector>
 #include "common.cuh"
@@ -137,12 +139,34 @@ static SortPlan tile_sort_plan(int W, int H) { return make_sort_plan(higher_msb(
 
 // instance emit + tile sort + ranges + render. `cap` bounds the instances written; the actual count is read
 // from n_dev (device) when given, else it IS cap.
+// GSR_BINNING=radix forces the instance radix sort for every image size (A/B measurements, tests).
+static bool use_tile_scatter(int width, int height) {
+  static const bool force_radix = [] {
+    const char* e = getenv("GSR_BINNING");
+    return e && strcmp(e, "radix") == 0;
+  }();
+  return !force_radix && num_tiles(width, height) <= (size_t)TS_MAX_TILES;
+}
+
 static int enqueue_render(cudaStream_t st, int P, int width, int height, const float* background,
                           const GeomViews& g, const ImageViews& im, char* binning_ws, uint32_t* point_list,
                           long long cap, const unsigned long long* n_dev, float* out_color, float* out_depth,
                           float* out_opacity, int* n_touched, int debug) {
   const int tiles_x = (width + TILE_X - 1) / TILE_X;
-  if (cap > 0) {
+  const size_t n_tiles = num_tiles(width, height);
+  if (use_tile_scatter(width, height)) {
+    // sort-free binning (tile_scatter.cu): count matrix -> column scans -> in-order scatter
+    {
+      StageTimer tm(st, GSR_STAGE_EMIT);
+      GSR_TRY(check(launch_tile_count(st, P, g, tiles_x, (int)n_tiles)));
+    }
+    GSR_TRY(debug_sync(st, debug));
+    {
+      StageTimer tm(st, GSR_STAGE_TILE_SORT);
+      GSR_TRY(check(launch_tile_offsets_scatter(st, P, g, tiles_x, (int)n_tiles, cap, im.ranges, point_list)));
+    }
+    GSR_TRY(debug_sync(st, debug));
+  } else if (cap > 0) {
     BinningViews bv;
     carve_binning(binning_ws, cap, &bv);
     const SortPlan plan = tile_sort_plan(width, height);
@@ -514,9 +538,13 @@ int gsr_debug_image_views(const void* image_ws, int width, int height, const flo
 
 int gsr_debug_sorted_keys(void* stream, const void* geom_ws, const void* binning_ws, const uint32_t* point_list,
                           int P, int64_t num_rendered, int width, int height, uint64_t* keys_sorted) {
-  if (!geom_ws || !binning_ws || !keys_sorted || !point_list) return GSR_EINVAL;
+  if (!geom_ws || !keys_sorted || !point_list) return GSR_EINVAL;
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
+  if (use_tile_scatter(width, height))
+    return check(launch_rebuild_keys_from_starts((cudaStream_t)stream, num_rendered, (int)num_tiles(width, height), g,
+                                                 point_list, keys_sorted));
+  if (!binning_ws) return GSR_EINVAL;
   BinningViews bv;
   carve_binning((char*)binning_ws, num_rendered, &bv);
   const uint32_t* tk = (tile_sort_plan(width, height).n_passes & 1) ? bv.tkeys_b : bv.tkeys_a;

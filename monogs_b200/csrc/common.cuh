@@ -37,6 +37,9 @@ struct GeomViews {
   uint32_t* dkeys_b;         // [P]
   uint32_t* order_a;         // [P] Gaussian ids; after the 4-pass sort: ids in (depth, id) order
   uint32_t* order_b;         // [P]
+  uint32_t* ts_counts;       // [TS_BLOCKS][tiles] per-chunk tile counts -> exclusive prefixes (tile_scatter.cu)
+  uint32_t* ts_totals;       // [tiles] instances of every tile
+  uint32_t* ts_start;        // [tiles] first list position of every tile
   uint32_t* chunk_offsets;   // [ceil(P/256)+1] exclusive instance offsets of 256-Gaussian chunks, depth order
   // --- small region zeroed at the start of every forward ---
   uint32_t* hist;            // [4*256] depth digit histograms -> exclusive offsets
@@ -82,8 +85,19 @@ inline SortPlan make_sort_plan(int total_bits) {
   return pl;
 }
 
+constexpr int TS_MAX_TILES = 4096;   // above this the per-tile shared-memory state no longer fits: radix path
+constexpr int TS_GROUP_SMEM = 33536; // staged Gaussian group + staged piece of tile_scatter.cu
+constexpr int TS_TILE_SMEM = 24;     // per tile: cursor + piece base (u32) + 8 per-warp u16 counters
+// CTAs of the sort-free binning = rows of its count matrix: as many per SM as the scatter kernel's shared memory
+// allows (at most 3: its register budget), on the 148 SMs of a B200.
+__host__ __device__ inline int ts_blocks(size_t n_tiles) {
+  const size_t smem = (size_t)TS_GROUP_SMEM + n_tiles * TS_TILE_SMEM + 1024;
+  size_t occ = (size_t)232448 / smem;
+  occ = occ > 3 ? 3 : (occ < 1 ? 1 : occ);
+  return 148 * (int)occ;
+}
 __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, GeomViews* v) {
-  (void)W; (void)H;
+  const size_t ts_tiles = num_tiles(W, H) <= (size_t)TS_MAX_TILES ? num_tiles(W, H) : 0;
   size_t off = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
   char* a = take(sizeof(float4) * (size_t)P);
@@ -95,6 +109,9 @@ __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, Ge
   char* ka = take(4 * (size_t)P); char* kb = take(4 * (size_t)P);
   char* oa = take(4 * (size_t)P); char* ob = take(4 * (size_t)P);
   char* co = take(sizeof(uint32_t) * (size_t)(num_pre_blocks(P) + 1));
+  char* tc = take(sizeof(uint32_t) * (size_t)ts_blocks(ts_tiles) * ts_tiles);
+  char* tto = take(sizeof(uint32_t) * (ts_tiles + 1));
+  char* tst = take(sizeof(uint32_t) * (ts_tiles + 1));
   size_t zb = off;
   char* h = take(sizeof(uint32_t) * 4 * 256);
   char* tk = take(sizeof(uint32_t) * 4);
@@ -107,6 +124,7 @@ __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, Ge
     v->rect = (uint2*)rc; v->rect_sorted = (uint2*)rs;
     v->dkeys_a = (uint32_t*)ka; v->dkeys_b = (uint32_t*)kb; v->order_a = (uint32_t*)oa; v->order_b = (uint32_t*)ob;
     v->chunk_offsets = (uint32_t*)co;
+    v->ts_counts = (uint32_t*)tc; v->ts_totals = (uint32_t*)tto; v->ts_start = (uint32_t*)tst;
     v->hist = (uint32_t*)h; v->tickets = (uint32_t*)tk; v->lookback = (uint32_t*)lb;
     v->total = (unsigned long long*)tot; v->error_flag = (int*)(tot ? tot + 64 : nullptr);
     v->zero_begin = zb; v->zero_end = ze;

@@ -25,6 +25,13 @@ cudaError_t launch_tile_ranges(cudaStream_t st, long long cap, const unsigned lo
 cudaError_t launch_rebuild_keys(cudaStream_t st, long long L, const uint32_t* tkeys_sorted,
                                 const uint32_t* point_list, const float4* rec_a, uint64_t* keys);
 
+// tile_scatter.cu  (sort-free binning for images of <= TS_MAX_TILES tiles)
+cudaError_t launch_tile_count(cudaStream_t st, int P, const GeomViews& g, int tiles_x, int n_tiles);
+cudaError_t launch_tile_offsets_scatter(cudaStream_t st, int P, const GeomViews& g, int tiles_x, int n_tiles,
+                                        long long cap, uint2* ranges, uint32_t* point_list);
+cudaError_t launch_rebuild_keys_from_starts(cudaStream_t st, long long L, int n_tiles, const GeomViews& g,
+                                            const uint32_t* point_list, uint64_t* keys);
+
 // radix_sort.cu  (n_cap = element count or capacity; n_dev = optional device-resident count <= n_cap)
 cudaError_t sort_pairs_u64_prehist(cudaStream_t st, long long n_cap, const unsigned long long* n_dev,
                                    uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,

@@ -1,0 +1,423 @@
+// tile_scatter.cu -- instance binning WITHOUT an instance-level sort (replaces K4 + K5 + K6 of SURVEY 2.2:
+// duplicateWithKeys, cub::DeviceRadixSort::SortPairs, identifyTileRanges; rasterizer_impl.cu:70-138,303-321)
+// for images of up to TS_MAX_TILES tiles; larger images use the radix path of binning.cu.
+//
+// The Gaussians are already in (depth, id) order, so the reference's sorted instance list is: for every tile, the
+// Gaussians whose rectangle contains the tile, in that order.  With the depth-ordered instance sequence cut into nb
+// contiguous chunks of equal instance count, the final position of an instance of tile t in chunk b is
+//     start[t] + sum_{b' < b} count[b'][t] + (number of earlier instances of t inside chunk b)
+// which needs an nb x tiles count matrix instead of key/value passes over the R instances:
+//   tile_count_kernel    each CTA walks its chunk and histograms the tile ids in shared memory   (reads 8 B/Gaussian)
+//   tile_offsets_kernel  column scans of the matrix + tile totals                                (a few MB, L2)
+//   tile_scatter_kernel  each CTA scans the totals into tile starts (CTA 0 also writes the ranges), walks its chunk
+//                        again, in order, ranks the instances of every piece stably per tile (match.any + per-warp
+//                        tile counters, like one radix-sort CTA step but over the whole tile id) and writes the
+//                        Gaussian ids straight to their final slots                               (4 B/instance)
+// Instance keys are never written or read; traffic is ~4 B per instance instead of ~44 B.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace gsr {
+
+constexpr int TS_THREADS = 256;
+constexpr int TS_WARPS = TS_THREADS / 32;
+constexpr int TS_GPT = 4;                          // Gaussians per thread in a staged group
+constexpr int TS_GROUP = TS_THREADS * TS_GPT;      // 1024 Gaussians = 4 entries of chunk_offsets
+constexpr int TS_ITEMS = 16;                       // instances per thread per piece
+constexpr int TS_PIECE = TS_THREADS * TS_ITEMS;    // 4096 instances ranked at a time
+static_assert(TS_GROUP % 256 == 0, "groups are whole chunk_offsets chunks");
+
+__host__ __device__ inline int ts_num_groups(int P) { return (P + TS_GROUP - 1) / TS_GROUP; }
+GSR_DEVINL unsigned long long ts_group_offset(const uint32_t* __restrict__ chunk_offsets, int grp) {
+  return chunk_offsets[grp * (TS_GROUP / 256)];
+}
+
+// CTA b owns the instances [k_lo, k_hi) of the depth-ordered instance sequence (an even split of `total`, so one
+// group of screen-filling Gaussians cannot unbalance the grid); g0 = the group that contains k_lo.
+GSR_DEVINL void ts_block_range(const uint32_t* __restrict__ chunk_offsets, int n_groups, unsigned long long total,
+                               int b, int nb, unsigned long long& k_lo, unsigned long long& k_hi, int& g0) {
+  k_lo = total * (unsigned long long)b / nb;
+  k_hi = total * (unsigned long long)(b + 1) / nb;
+  int l = 0, h = n_groups - 1;  // last group whose first instance index is <= k_lo
+  while (l < h) {
+    const int m = (l + h + 1) >> 1;
+    if (ts_group_offset(chunk_offsets, m) <= k_lo) l = m; else h = m - 1;
+  }
+  g0 = l;
+}
+
+struct TsGroup {          // one group of depth-consecutive Gaussians staged in shared memory
+  uint32_t prefix[TS_GROUP + 1];  // exclusive instance prefix inside the group
+  uint2 rect[TS_GROUP];
+  uint32_t id[TS_GROUP];
+  uint32_t warp_sum[TS_WARPS];
+};
+
+GSR_DEVINL uint32_t ts_rect_count(uint2 r) { return ((r.x >> 16) - (r.x & 0xffffu)) * ((r.y >> 16) - (r.y & 0xffffu)); }
+
+// Loads group `grp` (rectangles in depth order) and builds the intra-group prefix. Returns its instance count.
+template <bool WITH_IDS>
+GSR_DEVINL uint32_t ts_load_group(TsGroup& sg, int grp, int P, const uint2* __restrict__ rect_sorted,
+                                  const uint32_t* __restrict__ order) {
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int s0 = grp * TS_GROUP + tid * TS_GPT;
+  uint2 r[TS_GPT];
+  uint32_t id[TS_GPT];
+  if (s0 + TS_GPT <= P) {
+    const uint4 a = *reinterpret_cast<const uint4*>(rect_sorted + s0);
+    const uint4 b = *reinterpret_cast<const uint4*>(rect_sorted + s0 + 2);
+    r[0] = make_uint2(a.x, a.y); r[1] = make_uint2(a.z, a.w); r[2] = make_uint2(b.x, b.y); r[3] = make_uint2(b.z, b.w);
+    if (WITH_IDS) {
+      const uint4 o = *reinterpret_cast<const uint4*>(order + s0);
+      id[0] = o.x; id[1] = o.y; id[2] = o.z; id[3] = o.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < TS_GPT; ++j) {
+      r[j] = make_uint2(0u, 0u); id[j] = 0u;
+      if (s0 + j < P) { r[j] = rect_sorted[s0 + j]; if (WITH_IDS) id[j] = order[s0 + j]; }
+    }
+  }
+  uint32_t n[TS_GPT], mine = 0;
+#pragma unroll
+  for (int j = 0; j < TS_GPT; ++j) { n[j] = ts_rect_count(r[j]); mine += n[j]; }
+  uint32_t inc = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  __syncthreads();  // previous group fully consumed
+  if (lane == 31) sg.warp_sum[w] = inc;
+#pragma unroll
+  for (int j = 0; j < TS_GPT; ++j) {
+    sg.rect[tid * TS_GPT + j] = r[j];
+    if (WITH_IDS) sg.id[tid * TS_GPT + j] = id[j];
+  }
+  __syncthreads();
+  uint32_t run = inc - mine;
+#pragma unroll
+  for (int ww = 0; ww < TS_WARPS; ++ww) run += (ww < w) ? sg.warp_sum[ww] : 0u;
+#pragma unroll
+  for (int j = 0; j < TS_GPT; ++j) { sg.prefix[tid * TS_GPT + j] = run; run += n[j]; }
+  if (tid == TS_THREADS - 1) sg.prefix[TS_GROUP] = run;
+  __syncthreads();
+  return sg.prefix[TS_GROUP];
+}
+
+// Walks a run of consecutive instances of the staged group: one binary search for the first instance, then
+// x/y/slot increments (row-major tile order inside a rectangle like rasterizer_impl.cu:98-109).
+struct TsWalker {
+  uint32_t slot, x, y, x0, x1, y1;
+  GSR_DEVINL void load_rect(const TsGroup& sg) {
+    const uint2 r = sg.rect[slot];
+    x0 = r.x & 0xffffu; x1 = r.x >> 16; y = r.y & 0xffffu; y1 = r.y >> 16; x = x0;
+  }
+  GSR_DEVINL void seek(const TsGroup& sg, uint32_t k) {  // k < instance count of the group
+    uint32_t l = 0;  // last slot with prefix[slot] <= k; prefix[0] = 0
+#pragma unroll
+    for (int step = TS_GROUP / 2; step > 0; step >>= 1)
+      if (sg.prefix[l + step] <= k) l += step;
+    slot = l;
+    load_rect(sg);
+    const uint32_t j = k - sg.prefix[l], wdt = x1 - x0, row = j / wdt;
+    y += row; x += j - row * wdt;
+  }
+  GSR_DEVINL uint32_t tile(int tiles_x) const { return y * (uint32_t)tiles_x + x; }
+  GSR_DEVINL void next(const TsGroup& sg, uint32_t k_next) {  // k_next = index of the instance stepped to
+    if (++x == x1) {
+      x = x0;
+      if (++y == y1) {  // rectangle exhausted: next Gaussian that touches a tile
+        ++slot;
+        load_rect(sg);  // slot < TS_GROUP: instance k_next exists
+        if (x1 == x0 || y1 == y) seek(sg, k_next);  // culled Gaussians in between: search instead of stepping
+      }
+    }
+  }
+};
+
+__global__ void __launch_bounds__(TS_THREADS)
+tile_count_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* __restrict__ chunk_offsets,
+                  const unsigned long long* __restrict__ total_dev, int tiles_x, int n_tiles,
+                  uint32_t* __restrict__ counts /*[gridDim.x][n_tiles]*/) {
+  extern __shared__ __align__(16) unsigned char ts_smem[];
+  TsGroup& sg = *reinterpret_cast<TsGroup*>(ts_smem);
+  uint32_t* hist = reinterpret_cast<uint32_t*>(ts_smem + sizeof(TsGroup));
+  const int tid = threadIdx.x;
+  for (int t = tid; t < n_tiles; t += TS_THREADS) hist[t] = 0u;
+  const int n_groups = ts_num_groups(P);
+  unsigned long long k_lo, k_hi;
+  int g0;
+  ts_block_range(chunk_offsets, n_groups, *total_dev, blockIdx.x, gridDim.x, k_lo, k_hi, g0);
+  for (int grp = g0; grp < n_groups && k_lo < k_hi; ++grp) {
+    const unsigned long long off = ts_group_offset(chunk_offsets, grp);
+    if (off >= k_hi) break;
+    const uint32_t n = ts_load_group<false>(sg, grp, P, rect_sorted, nullptr);
+    const uint32_t b = (uint32_t)(k_lo > off ? k_lo - off : 0ull);
+    const uint32_t e = (uint32_t)min((unsigned long long)n, k_hi - off);
+    if (e > b) {  // thread t walks the contiguous run [k, k_end)
+      const uint32_t per = (e - b + TS_THREADS - 1) / TS_THREADS;
+      uint32_t k = b + tid * per;
+      const uint32_t k_end = min(e, k + per);
+      if (k < k_end) {
+        TsWalker wk;
+        wk.seek(sg, k);
+        for (;;) {
+          atomicAdd(&hist[wk.tile(tiles_x)], 1u);
+          if (++k == k_end) break;
+          wk.next(sg, k);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int t = tid; t < n_tiles; t += TS_THREADS) counts[(size_t)blockIdx.x * n_tiles + t] = hist[t];
+}
+
+// One CTA per strip of 32 tiles: counts[b][t] -> exclusive prefix over b (in place), totals[t] = column sum.
+// Warp w owns a contiguous band of rows; lane = column, so every row access is one 128-byte line.
+__global__ void __launch_bounds__(TS_THREADS)
+tile_offsets_kernel(int nb, int n_tiles, uint32_t* __restrict__ counts, uint32_t* __restrict__ totals) {
+  __shared__ uint32_t part[TS_WARPS][32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int t = blockIdx.x * 32 + lane;
+  const int rows_per_warp = (nb + TS_WARPS - 1) / TS_WARPS;
+  const int r0 = w * rows_per_warp, r1 = min(nb, r0 + rows_per_warp);
+  uint32_t sum = 0u;
+  if (t < n_tiles) {
+#pragma unroll 8
+    for (int b = r0; b < r1; ++b) sum += counts[(size_t)b * n_tiles + t];
+  }
+  part[w][lane] = sum;
+  __syncthreads();
+  uint32_t run = 0u, all = 0u;
+#pragma unroll
+  for (int ww = 0; ww < TS_WARPS; ++ww) {
+    const uint32_t p = part[ww][lane];
+    run += ww < w ? p : 0u;
+    all += p;
+  }
+  if (t < n_tiles) {
+    for (int b0 = r0; b0 < r1; b0 += 8) {  // loads of a batch issued together, then the stores
+      uint32_t c[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) c[j] = b0 + j < r1 ? counts[(size_t)(b0 + j) * n_tiles + t] : 0u;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (b0 + j < r1) counts[(size_t)(b0 + j) * n_tiles + t] = run;
+        run += c[j];
+      }
+    }
+    if (w == 0) totals[t] = all;
+  }
+}
+
+constexpr int TS_STAGE_WORDS = TS_PIECE + TS_PIECE / 32;
+static_assert(sizeof(TsGroup) + TS_STAGE_WORDS * 4 <= TS_GROUP_SMEM, "ts_blocks() budgets TS_GROUP_SMEM bytes");
+static_assert(TS_GROUP <= 1024 && TS_MAX_TILES <= (1 << 22), "stage word = tile << 10 | slot");
+
+__global__ void __launch_bounds__(TS_THREADS, 3)
+tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* __restrict__ order,
+                    const uint32_t* __restrict__ chunk_offsets, const unsigned long long* __restrict__ total_dev,
+                    int tiles_x, int n_tiles, const uint32_t* __restrict__ counts /*exclusive over chunks*/,
+                    const uint32_t* __restrict__ totals, long long cap, uint32_t* __restrict__ start_out,
+                    uint2* __restrict__ ranges, uint32_t* __restrict__ point_list) {
+  extern __shared__ __align__(16) unsigned char ts_smem[];
+  TsGroup& sg = *reinterpret_cast<TsGroup*>(ts_smem);
+  uint32_t* cur = reinterpret_cast<uint32_t*>(ts_smem + sizeof(TsGroup));   // next free slot of every tile
+  uint32_t* pbase = cur + n_tiles;                                          // the same, at the start of the piece
+  uint32_t* stage = pbase + n_tiles;                                        // piece: tile << 10 | slot, padded
+  uint16_t* whist = reinterpret_cast<uint16_t*>(stage + TS_STAGE_WORDS);    // [TS_WARPS][n_tiles]
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+
+  // ---- tile starts = exclusive scan of the tile totals (every CTA; CTA 0 publishes starts and ranges) ----
+  for (int t = tid; t < n_tiles; t += TS_THREADS) pbase[t] = totals[t];
+  __syncthreads();
+  {
+    const int per = (n_tiles + TS_THREADS - 1) / TS_THREADS;
+    const int t0 = min(n_tiles, tid * per), t1 = min(n_tiles, t0 + per);
+    uint32_t mine = 0u;
+    for (int t = t0; t < t1; ++t) mine += pbase[t];
+    uint32_t inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
+    }
+    if (lane == 31) sg.warp_sum[w] = inc;
+    __syncthreads();
+    uint32_t run = inc - mine;
+#pragma unroll
+    for (int ww = 0; ww < TS_WARPS; ++ww) run += (ww < w) ? sg.warp_sum[ww] : 0u;
+    for (int t = t0; t < t1; ++t) {
+      const uint32_t c = pbase[t];
+      cur[t] = run;
+      run += c;
+    }
+    __syncthreads();
+  }
+  if (blockIdx.x == 0) {
+    for (int t = tid; t < n_tiles; t += TS_THREADS) {
+      const uint32_t st = cur[t], n = pbase[t];
+      start_out[t] = st;
+      // clipped to the list capacity: an undersized list (GSR_ECAPACITY) must not send the renderer out of bounds;
+      // (0,0) for empty tiles like the reference's memset (rasterizer_impl.cu:313)
+      const uint32_t lo = (uint32_t)min((long long)st, cap), hi = (uint32_t)min((long long)st + n, cap);
+      ranges[t] = hi > lo ? make_uint2(lo, hi) : make_uint2(0u, 0u);
+    }
+  }
+  for (int t = tid; t < n_tiles; t += TS_THREADS) cur[t] += counts[(size_t)blockIdx.x * n_tiles + t];
+
+  const int n_groups = ts_num_groups(P);
+  unsigned long long k_lo, k_hi;
+  int g0;
+  ts_block_range(chunk_offsets, n_groups, *total_dev, blockIdx.x, gridDim.x, k_lo, k_hi, g0);
+  uint16_t* my_hist = whist + (size_t)w * n_tiles;
+  const int n_words = TS_WARPS * n_tiles / 2 + 1;
+
+  for (int grp = g0; grp < n_groups && k_lo < k_hi; ++grp) {
+    const unsigned long long off = ts_group_offset(chunk_offsets, grp);
+    if (off >= k_hi) break;
+    const uint32_t n_all = ts_load_group<true>(sg, grp, P, rect_sorted, order);
+    const uint32_t first = (uint32_t)(k_lo > off ? k_lo - off : 0ull);
+    const uint32_t n = (uint32_t)min((unsigned long long)n_all, k_hi - off);
+    for (uint32_t piece = first; piece < n; piece += TS_PIECE) {
+      const uint32_t piece_n = min((uint32_t)TS_PIECE, n - piece);
+      for (int i = tid; i < n_words; i += TS_THREADS) reinterpret_cast<uint32_t*>(whist)[i] = 0u;
+      // warp w ranks the contiguous instances [wbase, wbase + 32 * rounds) of the piece
+      const int rounds = (int)((piece_n + TS_THREADS - 1) / TS_THREADS);
+      const uint32_t wbase = (uint32_t)(w * rounds * 32);
+
+      // ---- (tile, slot) of every instance: thread t walks the run [t * rounds, (t+1) * rounds) of the piece and
+      //      stages it in instance order (one pad word per 32 keeps both access patterns conflict-free) ----
+      {
+        uint32_t local = (uint32_t)(tid * rounds);
+        const uint32_t local_end = min(piece_n, local + (uint32_t)rounds);
+        if (local < local_end) {
+          TsWalker wk;
+          wk.seek(sg, piece + local);
+          for (;;) {
+            stage[local + (local >> 5)] = wk.tile(tiles_x) << 10 | wk.slot;
+            if (++local == local_end) break;
+            wk.next(sg, piece + local);
+          }
+        }
+      }
+      __syncthreads();
+      uint32_t tile[TS_ITEMS], sr[TS_ITEMS];  // sr = slot << 16 | rank
+#pragma unroll
+      for (int i = 0; i < TS_ITEMS; ++i) {
+        const uint32_t local = wbase + i * 32 + lane;
+        tile[i] = 0xFFFFFFFFu; sr[i] = 0u;
+        if (i < rounds && local < piece_n) {
+          const uint32_t v = stage[local + (local >> 5)];
+          tile[i] = v >> 10;
+          sr[i] = (v & 1023u) << 16;
+        }
+      }
+
+      // ---- stable rank per tile inside the warp's instances ----
+#pragma unroll
+      for (int i = 0; i < TS_ITEMS; ++i) {
+        if (i < rounds && wbase + i * 32 < piece_n) {  // warp-uniform
+          const uint32_t peers = __match_any_sync(0xffffffffu, tile[i]);
+          const uint32_t below = __popc(peers & ((1u << lane) - 1u));
+          uint32_t prev = 0;
+          if (tile[i] != 0xFFFFFFFFu && below == 0) {
+            prev = my_hist[tile[i]];
+            my_hist[tile[i]] = (uint16_t)(prev + __popc(peers));
+          }
+          prev = __shfl_sync(0xffffffffu, prev, __ffs(peers) - 1);
+          sr[i] |= prev + below;
+          __syncwarp();
+        }
+      }
+      __syncthreads();
+
+      // ---- per tile: exclusive prefix over the warps, advance the tile's cursor ----
+      for (int t = tid; t < n_tiles; t += TS_THREADS) {
+        uint32_t run = 0;
+#pragma unroll
+        for (int ww = 0; ww < TS_WARPS; ++ww) {
+          const uint32_t c = whist[(size_t)ww * n_tiles + t];
+          whist[(size_t)ww * n_tiles + t] = (uint16_t)run;
+          run += c;
+        }
+        const uint32_t c0 = cur[t];
+        pbase[t] = c0;
+        cur[t] = c0 + run;
+      }
+      __syncthreads();
+
+      // ---- final slots ----
+#pragma unroll
+      for (int i = 0; i < TS_ITEMS; ++i) {
+        if (tile[i] != 0xFFFFFFFFu) {
+          const long long pos = (long long)pbase[tile[i]] + my_hist[tile[i]] + (sr[i] & 0xffffu);
+          if (pos < cap) point_list[pos] = sg.id[sr[i] >> 16];
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// Test hook: the sorted tile id of every list position, from the tile starts (last tile with start <= i).
+__global__ void __launch_bounds__(256)
+rebuild_keys_from_starts_kernel(long long L, int n_tiles, const uint32_t* __restrict__ start,
+                                const uint32_t* __restrict__ point_list, const float4* __restrict__ rec_a,
+                                uint64_t* __restrict__ keys) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= L) return;
+  int l = 0, h = n_tiles - 1;
+  while (l < h) {
+    const int m = (l + h + 1) >> 1;
+    if ((long long)start[m] <= i) l = m; else h = m - 1;
+  }
+  keys[i] = ((uint64_t)(uint32_t)l << 32) | __float_as_uint(rec_a[point_list[i]].z);
+}
+
+static size_t ts_scatter_smem(int n_tiles) {
+  return sizeof(TsGroup) + TS_STAGE_WORDS * 4 + (size_t)n_tiles * TS_TILE_SMEM + 8;
+}
+static size_t ts_count_smem(int n_tiles) { return sizeof(TsGroup) + (size_t)n_tiles * 4; }
+
+cudaError_t launch_tile_count(cudaStream_t st, int P, const GeomViews& g, int tiles_x, int n_tiles) {
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(tile_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)ts_count_smem(TS_MAX_TILES));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(tile_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)ts_scatter_smem(TS_MAX_TILES));
+    if (e != cudaSuccess) return e;
+    attr = true;
+  }
+  count_launch();
+  tile_count_kernel<<<ts_blocks(n_tiles), TS_THREADS, ts_count_smem(n_tiles), st>>>(
+      P, g.rect_sorted, g.chunk_offsets, g.total, tiles_x, n_tiles, g.ts_counts);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_tile_offsets_scatter(cudaStream_t st, int P, const GeomViews& g, int tiles_x, int n_tiles,
+                                        long long cap, uint2* ranges, uint32_t* point_list) {
+  const int nb = ts_blocks(n_tiles);
+  count_launch();
+  tile_offsets_kernel<<<(n_tiles + 31) / 32, TS_THREADS, 0, st>>>(nb, n_tiles, g.ts_counts, g.ts_totals);
+  count_launch();
+  tile_scatter_kernel<<<nb, TS_THREADS, ts_scatter_smem(n_tiles), st>>>(
+      P, g.rect_sorted, g.order_a, g.chunk_offsets, g.total, tiles_x, n_tiles, g.ts_counts, g.ts_totals, cap,
+      g.ts_start, ranges, point_list);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_rebuild_keys_from_starts(cudaStream_t st, long long L, int n_tiles, const GeomViews& g,
+                                            const uint32_t* point_list, uint64_t* keys) {
+  if (L <= 0) return cudaSuccess;
+  count_launch();
+  rebuild_keys_from_starts_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>(L, n_tiles, g.ts_start, point_list,
+                                                                               g.rec_a, keys);
+  return cudaGetLastError();
+}
+
+}  // namespace gsr

@@ -23,6 +23,10 @@ ncuother)
   CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
   $CMD > gpurun_out/plain3.log 2>&1 && \
   ncu --set full --clock-control none --import-source on -k regex:"onesweep|preprocess_|emit_|tile_|chunk_" -s 14 -c 14 -f -o gpurun_out/prof_other $CMD > gpurun_out/ncu_other.log 2>&1 ;;
+ncuts)
+  CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
+  $CMD > gpurun_out/plain4.log 2>&1 && \
+  ncu --set full --clock-control none --import-source on -k regex:"tile_count|tile_scatter|tile_offsets" -s 3 -c 3 -f -o gpurun_out/prof_ts $CMD > gpurun_out/ncu_ts.log 2>&1 ;;
 esac
 done
 tail -n 3 gpurun_out/pytest_gpu.log gpurun_out/smoke.log gpurun_out/bench_ours.err gpurun_out/bench_ref.err 2>/dev/null
