@@ -15,6 +15,13 @@ using namespace gsr;
 namespace gsr {
 static std::atomic<unsigned long long> g_launches{0};
 unsigned long long count_launch(unsigned long long add) { return g_launches.fetch_add(add) + add; }
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("GSR_PDL");
+    return !(e && strcmp(e, "0") == 0);
+  }();
+  return on;
+}
 }  // namespace gsr
 
 namespace {

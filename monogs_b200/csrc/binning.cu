@@ -30,6 +30,8 @@ GSR_DEVINL uint32_t rect_count(uint2 r) {  // r.x = x0 | x1 << 16, r.y = y0 | y1
 __global__ void __launch_bounds__(256)
 gather_rects_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__ rect,
                     uint2* __restrict__ rect_sorted, uint32_t* __restrict__ chunk_sums) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ uint32_t s_w[8];
   const int s = blockIdx.x * 256 + threadIdx.x;
   uint32_t v = 0;
@@ -58,6 +60,8 @@ emit_instances_kernel(int P, const uint32_t* __restrict__ order, const uint2* __
                       const uint32_t* __restrict__ chunk_offsets, int tiles_x, long long cap, int n_passes,
                       uint32_t mask0, int shift1, uint32_t mask1, uint32_t* __restrict__ tkeys,
                       uint32_t* __restrict__ vals, uint32_t* __restrict__ hist) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ uint32_t s_warp[DUP_THREADS / 32];
   __shared__ uint32_t s_hist[2 * SORT_RADIX];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -118,6 +122,8 @@ emit_instances_kernel(int P, const uint32_t* __restrict__ order, const uint2* __
 __global__ void __launch_bounds__(256)
 tile_ranges_kernel(long long cap, const unsigned long long* __restrict__ n_dev,
                    const uint32_t* __restrict__ tkeys_sorted, uint2* __restrict__ ranges) {
+  pdl_launch_dependents();
+  pdl_wait();
   long long L = cap;
   if (n_dev) L = min((long long)*n_dev, cap);
   const long long i0 = ((long long)blockIdx.x * 256 + threadIdx.x) * 4;
@@ -148,13 +154,15 @@ tile_ranges_kernel(long long cap, const unsigned long long* __restrict__ n_dev,
 __global__ void __launch_bounds__(256)
 rebuild_keys_kernel(long long L, const uint32_t* __restrict__ tkeys_sorted, const uint32_t* __restrict__ point_list,
                     const float4* __restrict__ rec_a, uint64_t* __restrict__ keys) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= L) return;
   keys[i] = ((uint64_t)tkeys_sorted[i] << 32) | __float_as_uint(rec_a[point_list[i]].z);
 }
 
 cudaError_t launch_gather_rects(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g) {
-  count_launch(); gather_rects_kernel<<<num_pre_blocks(P), 256, 0, st>>>(P, order, g.rect, g.rect_sorted, g.chunk_offsets);
+  count_launch(); launch_k(gather_rects_kernel, num_pre_blocks(P), 256, 0, st, P, order, g.rect, g.rect_sorted, g.chunk_offsets);
   return cudaGetLastError();
 }
 
@@ -164,7 +172,7 @@ cudaError_t launch_emit_instances(cudaStream_t st, int P, const uint32_t* order,
   const uint32_t mask0 = (1u << plan.bits[0]) - 1u;
   const int shift1 = plan.n_passes > 1 ? plan.shift[1] : 0;
   const uint32_t mask1 = plan.n_passes > 1 ? (1u << plan.bits[1]) - 1u : 0u;
-  count_launch(); emit_instances_kernel<<<num_pre_blocks(P), DUP_THREADS, 0, st>>>(
+  count_launch(); launch_k(emit_instances_kernel, num_pre_blocks(P), DUP_THREADS, 0, st, 
       P, order, g.rect_sorted, g.chunk_offsets, tiles_x, cap, plan.n_passes, mask0, shift1, mask1, tkeys, vals, hist);
   return launch_digit_offsets(st, hist, plan.n_passes);
 }
@@ -173,14 +181,14 @@ cudaError_t launch_tile_ranges(cudaStream_t st, long long cap, const unsigned lo
                                const uint32_t* tkeys_sorted, uint2* ranges, size_t n_tiles) {
   cudaError_t e = cudaMemsetAsync(ranges, 0, sizeof(uint2) * n_tiles, st);
   if (e != cudaSuccess || cap <= 0) return e;
-  count_launch(); tile_ranges_kernel<<<(unsigned)((cap + 1023) / 1024), 256, 0, st>>>(cap, n_dev, tkeys_sorted, ranges);
+  count_launch(); launch_k(tile_ranges_kernel, (unsigned)((cap + 1023) / 1024), 256, 0, st, cap, n_dev, tkeys_sorted, ranges);
   return cudaGetLastError();
 }
 
 cudaError_t launch_rebuild_keys(cudaStream_t st, long long L, const uint32_t* tkeys_sorted,
                                 const uint32_t* point_list, const float4* rec_a, uint64_t* keys) {
   if (L <= 0) return cudaSuccess;
-  count_launch(); rebuild_keys_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>(L, tkeys_sorted, point_list, rec_a, keys);
+  count_launch(); launch_k(rebuild_keys_kernel, (unsigned)((L + 255) / 256), 256, 0, st, L, tkeys_sorted, point_list, rec_a, keys);
   return cudaGetLastError();
 }
 

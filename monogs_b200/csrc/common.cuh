@@ -239,6 +239,27 @@ __device__ __forceinline__ float gauss_power(float dx, float dy, float cx, float
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
 #define GSR_DEVINL __device__ __forceinline__
+
+// Programmatic dependent launch: every kernel of the library lets its successor in the stream start launching at
+// once (pdl_launch_dependents) and waits for its predecessor's results (pdl_wait) before it touches global memory,
+// so launch latency, CTA scheduling and the shared-memory prologue overlap the predecessor's tail.  Every kernel
+// must execute pdl_wait on every path: completion of a grid then implies completion of all earlier grids.
+GSR_DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+GSR_DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();  // api.cu: environment GSR_PDL=0 turns the launch attribute off (A/B measurements)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                            Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 #endif
 
 // Fused L1 loss (loss.cu): what the backward tile renderer needs to form dL/dpixel on the fly.

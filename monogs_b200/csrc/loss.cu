@@ -22,6 +22,8 @@ l1_loss_reduce_kernel(int kind, int N, const float* __restrict__ color, const fl
                       const float* __restrict__ gt_depth, const uint8_t* __restrict__ mask,
                       const uint8_t* __restrict__ grad_mask, const float* __restrict__ exposure_a,
                       const float* __restrict__ exposure_b, double* __restrict__ acc) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ double s_red[8][7];
   const float ea = exposure_a ? expf(*exposure_a) : 1.0f;
   const float eb = exposure_b ? *exposure_b : 0.0f;
@@ -68,6 +70,8 @@ l1_loss_reduce_kernel(int kind, int N, const float* __restrict__ color, const fl
 // [4]=k_depth, [5]=dL/da, [6]=dL/db, [7]=mean opacity
 __global__ void l1_loss_finish_kernel(int kind, int N, float lambda_rgb, const float* __restrict__ exposure_a,
                                       const double* __restrict__ acc, float* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
   if (threadIdx.x != 0) return;
   const double ea = exposure_a ? exp((double)*exposure_a) : 1.0;
   const double cnt_d = acc[3];
@@ -105,10 +109,10 @@ cudaError_t launch_l1_loss(cudaStream_t st, int kind, int W, int H, const float*
   if (e != cudaSuccess) return e;
   const int blocks = min(148 * 4, (N + 255) / 256);
   count_launch();
-  l1_loss_reduce_kernel<<<blocks, 256, 0, st>>>(kind, N, color, depth, opacity, gt_rgb, gt_depth, mask, grad_mask,
+  launch_k(l1_loss_reduce_kernel, blocks, 256, 0, st, kind, N, color, depth, opacity, gt_rgb, gt_depth, mask, grad_mask,
                                                 exposure_a, exposure_b, acc);
   count_launch();
-  l1_loss_finish_kernel<<<1, 32, 0, st>>>(kind, N, lambda_rgb, exposure_a, acc, out);
+  launch_k(l1_loss_finish_kernel, 1, 32, 0, st, kind, N, lambda_rgb, exposure_a, acc, out);
   return cudaGetLastError();
 }
 

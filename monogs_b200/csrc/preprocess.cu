@@ -181,6 +181,8 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       const float* __restrict__ campos, int W, int H, float tan_fovx, float tan_fovy,
                       float focal_x, float focal_y, int tiles_x, int tiles_y, int prefiltered,
                       int* __restrict__ radii, GeomViews g) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ __align__(16) float s_mean[PRE_THREADS * 3];
   __shared__ __align__(16) float s_scale[PRE_THREADS * 3];
   __shared__ float s_cam[36];
@@ -356,6 +358,8 @@ GSR_DEVINL uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp, uint
 // chunk sums -> exclusive chunk offsets (in place) + total = num_rendered (cub InclusiveSum, rasterizer_impl.cu:280).
 __global__ void __launch_bounds__(SCAN_THREADS)
 chunk_scan_kernel(int n_chunks, uint32_t* __restrict__ chunk_sums, unsigned long long* __restrict__ total) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ uint32_t s_warp[33];
   unsigned long long carry = 0;
   for (int base = 0; base < n_chunks; base += SCAN_THREADS) {
@@ -372,6 +376,8 @@ chunk_scan_kernel(int n_chunks, uint32_t* __restrict__ chunk_sums, unsigned long
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ viewmatrix,
                                     uint8_t* __restrict__ present) {
+  pdl_launch_dependents();
+  pdl_wait();
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P) return;
   float x = means3D[3 * (size_t)idx], y = means3D[3 * (size_t)idx + 1], z = means3D[3 * (size_t)idx + 2];
@@ -388,7 +394,7 @@ cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const fl
   const float focal_y = H / (2.0f * tan_fovy);
   const float focal_x = W / (2.0f * tan_fovx);
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
-  count_launch(); preprocess_fwd_kernel<<<num_pre_blocks(P), PRE_THREADS, 0, st>>>(
+  count_launch(); launch_k(preprocess_fwd_kernel, num_pre_blocks(P), PRE_THREADS, 0, st, 
       P, D, M, means3D, shs, colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
       viewmatrix, projmatrix, campos, W, H, tan_fovx, tan_fovy, focal_x, focal_y, tiles_x, tiles_y, prefiltered,
       radii, g);
@@ -400,13 +406,13 @@ cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, con
   const int nc = num_pre_blocks(P);
   cudaError_t e = launch_gather_rects(st, P, order, g);
   if (e != cudaSuccess) return e;
-  count_launch(); chunk_scan_kernel<<<1, SCAN_THREADS, 0, st>>>(nc, g.chunk_offsets, g.total);
+  count_launch(); launch_k(chunk_scan_kernel, 1, SCAN_THREADS, 0, st, nc, g.chunk_offsets, g.total);
   return cudaGetLastError();
 }
 
 cudaError_t launch_mark_visible(cudaStream_t st, int P, const float* means3D, const float* viewmatrix,
                                 uint8_t* present) {
-  count_launch(); mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means3D, viewmatrix, present);
+  count_launch(); launch_k(mark_visible_kernel, (P + 255) / 256, 256, 0, st, P, means3D, viewmatrix, present);
   return cudaGetLastError();
 }
 

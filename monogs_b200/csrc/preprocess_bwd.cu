@@ -108,6 +108,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       float* __restrict__ dL_dscales, float* __restrict__ dL_drots,
                       float* __restrict__ dL_dtau_pg, double* __restrict__ tau_partial, int p_begin,
                       float* __restrict__ rows /*[P,16] window rows or NULL*/, int accumulate) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_cam[40];
   __shared__ double s_red[PB_THREADS / 32][6];
   const int tid = threadIdx.x;
@@ -390,6 +392,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
 // Deterministic final reduction of the block partials: one block, fixed order.
 __global__ void __launch_bounds__(256) tau_final_kernel(int n_blocks, const double* __restrict__ partial,
                                                         float* __restrict__ dL_dtau) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ double s[8][6];
   const int tid = threadIdx.x;
   double acc[6] = {0, 0, 0, 0, 0, 0};
@@ -425,7 +429,7 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
   const int nb = num_pre_blocks(p_end - p_begin);  // p_begin is a multiple of 256 (checked by the caller)
   if (nb > 0) {
     count_launch();
-    preprocess_bwd_kernel<<<nb, PB_THREADS, 0, st>>>(p_end, D, M, means3D, radii, shs, clamped, scales, rotations,
+    launch_k(preprocess_bwd_kernel, nb, PB_THREADS, 0, st, p_end, D, M, means3D, radii, shs, clamped, scales, rotations,
                                                      scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
                                                      projmatrix_raw, campos, focal_x, focal_y, tan_fovx, tan_fovy,
                                                      bw.packed, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D,
@@ -434,7 +438,7 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
   }
   // the pose gradient is complete once the LAST range has run (ranges are issued in ascending order)
   if (dL_dtau && p_end == P) {
-    count_launch(); tau_final_kernel<<<1, 256, 0, st>>>(num_pre_blocks(P), bw.tau_partial, dL_dtau);
+    count_launch(); launch_k(tau_final_kernel, 1, 256, 0, st, num_pre_blocks(P), bw.tau_partial, dL_dtau);
   }
   return cudaGetLastError();
 }

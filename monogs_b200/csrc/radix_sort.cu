@@ -60,6 +60,8 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
                      const unsigned long long* __restrict__ n_dev, int shift, uint32_t dmask,
                      const uint32_t* __restrict__ digit_offsets /*[256] exclusive*/,
                      uint32_t* __restrict__ ticket, uint32_t* __restrict__ lookback /*[nblocks][256]*/) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int TILE = RS_THREADS * ITEMS;
   extern __shared__ __align__(16) unsigned char rs_smem_raw[];
   RsSmem<KeyT, ITEMS>& sm = *reinterpret_cast<RsSmem<KeyT, ITEMS>*>(rs_smem_raw);
@@ -196,6 +198,8 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 digit_hist_kernel(const KeyT* __restrict__ keys, long long n, SortPlan plan, uint32_t* __restrict__ hist) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ uint32_t s[SORT_MAX_PASSES * SORT_RADIX];
   for (int i = threadIdx.x; i < plan.n_passes * SORT_RADIX; i += 256) s[i] = 0;
   __syncthreads();
@@ -211,6 +215,8 @@ digit_hist_kernel(const KeyT* __restrict__ keys, long long n, SortPlan plan, uin
 
 // Exclusive prefix over the 256 bins of each pass' digit histogram (one warp per pass).
 __global__ void digit_offsets_kernel(uint32_t* hist, int n_passes) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (w >= n_passes) return;
   uint32_t run = 0;
@@ -228,7 +234,7 @@ __global__ void digit_offsets_kernel(uint32_t* hist, int n_passes) {
 }
 
 cudaError_t launch_digit_offsets(cudaStream_t st, uint32_t* hist, int n_passes) {
-  count_launch(); digit_offsets_kernel<<<1, 32 * n_passes, 0, st>>>(hist, n_passes);
+  count_launch(); launch_k(digit_offsets_kernel, 1, 32 * n_passes, 0, st, hist, n_passes);
   return cudaGetLastError();
 }
 
@@ -246,7 +252,7 @@ static cudaError_t launch_pass(cudaStream_t st, const KeyT* kin, KeyT* kout, con
   }
   const unsigned nblocks = (unsigned)((n_cap + RS_THREADS * ITEMS - 1) / (RS_THREADS * ITEMS));
   count_launch();
-  onesweep_pass_kernel<KeyT, ITEMS><<<nblocks, RS_THREADS, smem, st>>>(kin, kout, vin, vout, n_cap, n_dev, shift,
+  launch_k(onesweep_pass_kernel<KeyT, ITEMS>, nblocks, RS_THREADS, smem, st, kin, kout, vin, vout, n_cap, n_dev, shift,
                                                                       (1u << bits) - 1u, digit_offsets, ticket,
                                                                       lookback);
   return cudaGetLastError();
@@ -296,7 +302,7 @@ cudaError_t launch_digit_hist_u64(cudaStream_t st, const uint64_t* keys, long lo
                                   uint32_t* hist) {
   if (n <= 0) return cudaSuccess;
   int blocks = (int)min((long long)148 * 8, (n + 255) / 256);
-  count_launch(); digit_hist_kernel<uint64_t><<<blocks, 256, 0, st>>>(keys, n, plan, hist);
+  count_launch(); launch_k(digit_hist_kernel<uint64_t>, blocks, 256, 0, st, keys, n, plan, hist);
   return launch_digit_offsets(st, hist, plan.n_passes);
 }
 
@@ -304,7 +310,7 @@ cudaError_t launch_digit_hist_u32(cudaStream_t st, const uint32_t* keys, long lo
                                   uint32_t* hist) {
   if (n <= 0) return cudaSuccess;
   int blocks = (int)min((long long)148 * 8, (n + 255) / 256);
-  count_launch(); digit_hist_kernel<uint32_t><<<blocks, 256, 0, st>>>(keys, n, plan, hist);
+  count_launch(); launch_k(digit_hist_kernel<uint32_t>, blocks, 256, 0, st, keys, n, plan, hist);
   return launch_digit_offsets(st, hist, plan.n_passes);
 }
 

@@ -96,6 +96,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
                   const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth, LossView loss,
                   float* __restrict__ packed /*[P][GRAD_STRIDE]*/) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ __align__(16) RbStage stage[2];
   __shared__ uint32_t s_max[RB_THREADS / 32];
 
@@ -267,7 +269,7 @@ cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& i
                               const float* dL_dpix_depth, const LossView& loss, float* packed) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y);
-  count_launch(); render_bwd_kernel<<<grid, RB_THREADS, 0, st>>>(im.ranges, point_list, W, H, tiles_x, bg, g.rec_a, g.rec_b,
+  count_launch(); launch_k(render_bwd_kernel, grid, RB_THREADS, 0, st, im.ranges, point_list, W, H, tiles_x, bg, g.rec_a, g.rec_b,
                                                  g.rec_c, im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, loss, packed);
   return cudaGetLastError();
 }

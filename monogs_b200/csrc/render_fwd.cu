@@ -45,6 +45,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float4* __restrict__ rec_c, const float* __restrict__ bg, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_depth,
                   float* __restrict__ out_opacity, int* __restrict__ n_touched) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ __align__(16) RfStage stage[2];
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -164,7 +166,7 @@ cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& i
                               float* out_opacity, int* n_touched) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y);
-  count_launch(); render_fwd_kernel<<<grid, RF_THREADS, 0, st>>>(im.ranges, point_list, W, H, tiles_x, g.rec_a, g.rec_b, g.rec_c,
+  count_launch(); launch_k(render_fwd_kernel, grid, RF_THREADS, 0, st, im.ranges, point_list, W, H, tiles_x, g.rec_a, g.rec_b, g.rec_c,
                                                  bg, im.final_T, im.n_contrib, out_color, out_depth, out_opacity,
                                                  n_touched);
   return cudaGetLastError();

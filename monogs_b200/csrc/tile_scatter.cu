@@ -25,25 +25,35 @@ constexpr int TS_GPT = 4;                          // Gaussians per thread in a 
 constexpr int TS_GROUP = TS_THREADS * TS_GPT;      // 1024 Gaussians = 4 entries of chunk_offsets
 constexpr int TS_ITEMS = 16;                       // instances per thread per piece
 constexpr int TS_PIECE = TS_THREADS * TS_ITEMS;    // 4096 instances ranked at a time
-static_assert(TS_GROUP % 256 == 0, "groups are whole chunk_offsets chunks");
-
-__host__ __device__ inline int ts_num_groups(int P) { return (P + TS_GROUP - 1) / TS_GROUP; }
-GSR_DEVINL unsigned long long ts_group_offset(const uint32_t* __restrict__ chunk_offsets, int grp) {
-  return chunk_offsets[grp * (TS_GROUP / 256)];
-}
+#ifndef TS_MATCH_BATCH
+#define TS_MATCH_BATCH 4
+#endif
+static_assert(TS_GROUP % 256 == 0, "a staged window is whole chunk_offsets chunks (256 Gaussians each)");
 
 // CTA b owns the instances [k_lo, k_hi) of the depth-ordered instance sequence (an even split of `total`, so one
-// group of screen-filling Gaussians cannot unbalance the grid); g0 = the group that contains k_lo.
-GSR_DEVINL void ts_block_range(const uint32_t* __restrict__ chunk_offsets, int n_groups, unsigned long long total,
-                               int b, int nb, unsigned long long& k_lo, unsigned long long& k_hi, int& g0) {
+// chunk of screen-filling Gaussians cannot unbalance the grid); c0 = the 256-Gaussian chunk that contains k_lo.
+GSR_DEVINL void ts_block_range(const uint32_t* __restrict__ chunk_offsets, int n_chunks, unsigned long long total,
+                               int b, int nb, unsigned long long& k_lo, unsigned long long& k_hi, int& c0) {
   k_lo = total * (unsigned long long)b / nb;
   k_hi = total * (unsigned long long)(b + 1) / nb;
-  int l = 0, h = n_groups - 1;  // last group whose first instance index is <= k_lo
+  int l = 0, h = n_chunks - 1;  // last chunk whose first instance index is <= k_lo
   while (l < h) {
     const int m = (l + h + 1) >> 1;
-    if (ts_group_offset(chunk_offsets, m) <= k_lo) l = m; else h = m - 1;
+    if ((unsigned long long)chunk_offsets[m] <= k_lo) l = m; else h = m - 1;
   }
-  g0 = l;
+  c0 = l;
+}
+
+// Last chunk >= c whose first instance index is <= k (the chunk that contains instance k). Block-wide: every thread
+// tests one chunk per round, so the usual 0..4 chunk step costs one coalesced load and one barrier.
+GSR_DEVINL int ts_advance_chunk(const uint32_t* __restrict__ chunk_offsets, int n_chunks, int c,
+                                unsigned long long k) {
+  for (;;) {
+    const int idx = c + 1 + (int)threadIdx.x;
+    const int cnt = __syncthreads_count(idx < n_chunks && (unsigned long long)chunk_offsets[idx] <= k);
+    c += cnt;
+    if (cnt < TS_THREADS) return c;
+  }
 }
 
 struct TsGroup {          // one group of depth-consecutive Gaussians staged in shared memory
@@ -55,12 +65,13 @@ struct TsGroup {          // one group of depth-consecutive Gaussians staged in 
 
 GSR_DEVINL uint32_t ts_rect_count(uint2 r) { return ((r.x >> 16) - (r.x & 0xffffu)) * ((r.y >> 16) - (r.y & 0xffffu)); }
 
-// Loads group `grp` (rectangles in depth order) and builds the intra-group prefix. Returns its instance count.
+// Loads the window of TS_GROUP Gaussians that starts at chunk c (rectangles in depth order) and builds its instance
+// prefix. Returns the window's instance count.
 template <bool WITH_IDS>
-GSR_DEVINL uint32_t ts_load_group(TsGroup& sg, int grp, int P, const uint2* __restrict__ rect_sorted,
+GSR_DEVINL uint32_t ts_load_group(TsGroup& sg, int c, int P, const uint2* __restrict__ rect_sorted,
                                   const uint32_t* __restrict__ order) {
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int s0 = grp * TS_GROUP + tid * TS_GPT;
+  const int s0 = c * 256 + tid * TS_GPT;
   uint2 r[TS_GPT];
   uint32_t id[TS_GPT];
   if (s0 + TS_GPT <= P) {
@@ -140,22 +151,26 @@ __global__ void __launch_bounds__(TS_THREADS)
 tile_count_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* __restrict__ chunk_offsets,
                   const unsigned long long* __restrict__ total_dev, int tiles_x, int n_tiles,
                   uint32_t* __restrict__ counts /*[gridDim.x][n_tiles]*/) {
+  pdl_launch_dependents();
   extern __shared__ __align__(16) unsigned char ts_smem[];
   TsGroup& sg = *reinterpret_cast<TsGroup*>(ts_smem);
   uint32_t* hist = reinterpret_cast<uint32_t*>(ts_smem + sizeof(TsGroup));
   const int tid = threadIdx.x;
   for (int t = tid; t < n_tiles; t += TS_THREADS) hist[t] = 0u;
-  const int n_groups = ts_num_groups(P);
+  pdl_wait();
+  const int n_chunks = num_pre_blocks(P);
   unsigned long long k_lo, k_hi;
-  int g0;
-  ts_block_range(chunk_offsets, n_groups, *total_dev, blockIdx.x, gridDim.x, k_lo, k_hi, g0);
-  for (int grp = g0; grp < n_groups && k_lo < k_hi; ++grp) {
-    const unsigned long long off = ts_group_offset(chunk_offsets, grp);
-    if (off >= k_hi) break;
-    const uint32_t n = ts_load_group<false>(sg, grp, P, rect_sorted, nullptr);
-    const uint32_t b = (uint32_t)(k_lo > off ? k_lo - off : 0ull);
+  int c;
+  ts_block_range(chunk_offsets, n_chunks, *total_dev, blockIdx.x, gridDim.x, k_lo, k_hi, c);
+  for (unsigned long long kk = k_lo; kk < k_hi;) {
+    c = ts_advance_chunk(chunk_offsets, n_chunks, c, kk);
+    const unsigned long long off = chunk_offsets[c];
+    const uint32_t n = ts_load_group<false>(sg, c, P, rect_sorted, nullptr);
+    const uint32_t b = (uint32_t)(kk - off);
     const uint32_t e = (uint32_t)min((unsigned long long)n, k_hi - off);
-    if (e > b) {  // thread t walks the contiguous run [k, k_end)
+    if (e <= b) break;  // cannot happen (chunk c holds instance kk); never spin on inconsistent inputs
+    kk = off + e;
+    {  // thread t walks the contiguous run [k, k_end) of the window's instances [b, e)
       const uint32_t per = (e - b + TS_THREADS - 1) / TS_THREADS;
       uint32_t k = b + tid * per;
       const uint32_t k_end = min(e, k + per);
@@ -176,12 +191,15 @@ tile_count_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* 
 
 // One CTA per strip of 32 tiles: counts[b][t] -> exclusive prefix over b (in place), totals[t] = column sum.
 // Warp w owns a contiguous band of rows; lane = column, so every row access is one 128-byte line.
-__global__ void __launch_bounds__(TS_THREADS)
+constexpr int TS_OFF_WARPS = 32;
+__global__ void __launch_bounds__(TS_OFF_WARPS * 32)
 tile_offsets_kernel(int nb, int n_tiles, uint32_t* __restrict__ counts, uint32_t* __restrict__ totals) {
-  __shared__ uint32_t part[TS_WARPS][32];
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ uint32_t part[TS_OFF_WARPS][32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int t = blockIdx.x * 32 + lane;
-  const int rows_per_warp = (nb + TS_WARPS - 1) / TS_WARPS;
+  const int rows_per_warp = (nb + TS_OFF_WARPS - 1) / TS_OFF_WARPS;
   const int r0 = w * rows_per_warp, r1 = min(nb, r0 + rows_per_warp);
   uint32_t sum = 0u;
   if (t < n_tiles) {
@@ -192,7 +210,7 @@ tile_offsets_kernel(int nb, int n_tiles, uint32_t* __restrict__ counts, uint32_t
   __syncthreads();
   uint32_t run = 0u, all = 0u;
 #pragma unroll
-  for (int ww = 0; ww < TS_WARPS; ++ww) {
+  for (int ww = 0; ww < TS_OFF_WARPS; ++ww) {
     const uint32_t p = part[ww][lane];
     run += ww < w ? p : 0u;
     all += p;
@@ -222,6 +240,8 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
                     int tiles_x, int n_tiles, const uint32_t* __restrict__ counts /*exclusive over chunks*/,
                     const uint32_t* __restrict__ totals, long long cap, uint32_t* __restrict__ start_out,
                     uint2* __restrict__ ranges, uint32_t* __restrict__ point_list) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ __align__(16) unsigned char ts_smem[];
   TsGroup& sg = *reinterpret_cast<TsGroup*>(ts_smem);
   uint32_t* cur = reinterpret_cast<uint32_t*>(ts_smem + sizeof(TsGroup));   // next free slot of every tile
@@ -268,21 +288,28 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
   }
   for (int t = tid; t < n_tiles; t += TS_THREADS) cur[t] += counts[(size_t)blockIdx.x * n_tiles + t];
 
-  const int n_groups = ts_num_groups(P);
+  const int n_chunks = num_pre_blocks(P);
   unsigned long long k_lo, k_hi;
-  int g0;
-  ts_block_range(chunk_offsets, n_groups, *total_dev, blockIdx.x, gridDim.x, k_lo, k_hi, g0);
+  int c;
+  ts_block_range(chunk_offsets, n_chunks, *total_dev, blockIdx.x, gridDim.x, k_lo, k_hi, c);
   uint16_t* my_hist = whist + (size_t)w * n_tiles;
   const int n_words = TS_WARPS * n_tiles / 2 + 1;
 
-  for (int grp = g0; grp < n_groups && k_lo < k_hi; ++grp) {
-    const unsigned long long off = ts_group_offset(chunk_offsets, grp);
-    if (off >= k_hi) break;
-    const uint32_t n_all = ts_load_group<true>(sg, grp, P, rect_sorted, order);
-    const uint32_t first = (uint32_t)(k_lo > off ? k_lo - off : 0ull);
+  // Pieces of up to TS_PIECE consecutive instances; the staged window of Gaussians slides with them (it starts at
+  // the chunk that contains the piece's first instance), so pieces are full wherever TS_GROUP Gaussians have
+  // TS_PIECE instances.
+  int loaded = -1;
+  uint32_t n_all = 0;
+  for (unsigned long long kk = k_lo; kk < k_hi;) {
+    c = ts_advance_chunk(chunk_offsets, n_chunks, c, kk);
+    if (c != loaded) { n_all = ts_load_group<true>(sg, c, P, rect_sorted, order); loaded = c; }
+    const unsigned long long off = chunk_offsets[c];
+    const uint32_t piece = (uint32_t)(kk - off);
     const uint32_t n = (uint32_t)min((unsigned long long)n_all, k_hi - off);
-    for (uint32_t piece = first; piece < n; piece += TS_PIECE) {
+    {
+      if (n <= piece) break;  // cannot happen (chunk c holds instance kk); never spin on inconsistent inputs
       const uint32_t piece_n = min((uint32_t)TS_PIECE, n - piece);
+      kk += piece_n;
       for (int i = tid; i < n_words; i += TS_THREADS) reinterpret_cast<uint32_t*>(whist)[i] = 0u;
       // warp w ranks the contiguous instances [wbase, wbase + 32 * rounds) of the piece
       const int rounds = (int)((piece_n + TS_THREADS - 1) / TS_THREADS);
@@ -316,20 +343,31 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
         }
       }
 
-      // ---- stable rank per tile inside the warp's instances ----
+      // ---- stable rank per tile inside the warp's instances (match.any issued TS_MATCH_BATCH rounds ahead: the
+      //      counter updates of one round hide the match latency of the next) ----
 #pragma unroll
-      for (int i = 0; i < TS_ITEMS; ++i) {
-        if (i < rounds && wbase + i * 32 < piece_n) {  // warp-uniform
-          const uint32_t peers = __match_any_sync(0xffffffffu, tile[i]);
-          const uint32_t below = __popc(peers & ((1u << lane) - 1u));
-          uint32_t prev = 0;
-          if (tile[i] != 0xFFFFFFFFu && below == 0) {
-            prev = my_hist[tile[i]];
-            my_hist[tile[i]] = (uint16_t)(prev + __popc(peers));
+      for (int i0 = 0; i0 < TS_ITEMS; i0 += TS_MATCH_BATCH) {
+        uint32_t peers[TS_MATCH_BATCH];
+#pragma unroll
+        for (int j = 0; j < TS_MATCH_BATCH; ++j) {
+          const int i = i0 + j;
+          peers[j] = 0u;
+          if (i < rounds && wbase + i * 32 < piece_n) peers[j] = __match_any_sync(0xffffffffu, tile[i]);  // uniform
+        }
+#pragma unroll
+        for (int j = 0; j < TS_MATCH_BATCH; ++j) {
+          const int i = i0 + j;
+          if (i < rounds && wbase + i * 32 < piece_n) {  // warp-uniform
+            const uint32_t below = __popc(peers[j] & ((1u << lane) - 1u));
+            uint32_t prev = 0;
+            if (tile[i] != 0xFFFFFFFFu && below == 0) {
+              prev = my_hist[tile[i]];
+              my_hist[tile[i]] = (uint16_t)(prev + __popc(peers[j]));
+            }
+            prev = __shfl_sync(0xffffffffu, prev, __ffs(peers[j]) - 1);
+            sr[i] |= prev + below;
+            __syncwarp();
           }
-          prev = __shfl_sync(0xffffffffu, prev, __ffs(peers) - 1);
-          sr[i] |= prev + below;
-          __syncwarp();
         }
       }
       __syncthreads();
@@ -367,6 +405,8 @@ __global__ void __launch_bounds__(256)
 rebuild_keys_from_starts_kernel(long long L, int n_tiles, const uint32_t* __restrict__ start,
                                 const uint32_t* __restrict__ point_list, const float4* __restrict__ rec_a,
                                 uint64_t* __restrict__ keys) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= L) return;
   int l = 0, h = n_tiles - 1;
@@ -394,7 +434,7 @@ cudaError_t launch_tile_count(cudaStream_t st, int P, const GeomViews& g, int ti
     attr = true;
   }
   count_launch();
-  tile_count_kernel<<<ts_blocks(n_tiles), TS_THREADS, ts_count_smem(n_tiles), st>>>(
+  launch_k(tile_count_kernel, ts_blocks(n_tiles), TS_THREADS, ts_count_smem(n_tiles), st, 
       P, g.rect_sorted, g.chunk_offsets, g.total, tiles_x, n_tiles, g.ts_counts);
   return cudaGetLastError();
 }
@@ -403,9 +443,9 @@ cudaError_t launch_tile_offsets_scatter(cudaStream_t st, int P, const GeomViews&
                                         long long cap, uint2* ranges, uint32_t* point_list) {
   const int nb = ts_blocks(n_tiles);
   count_launch();
-  tile_offsets_kernel<<<(n_tiles + 31) / 32, TS_THREADS, 0, st>>>(nb, n_tiles, g.ts_counts, g.ts_totals);
+  launch_k(tile_offsets_kernel, (n_tiles + 31) / 32, TS_OFF_WARPS * 32, 0, st, nb, n_tiles, g.ts_counts, g.ts_totals);
   count_launch();
-  tile_scatter_kernel<<<nb, TS_THREADS, ts_scatter_smem(n_tiles), st>>>(
+  launch_k(tile_scatter_kernel, nb, TS_THREADS, ts_scatter_smem(n_tiles), st, 
       P, g.rect_sorted, g.order_a, g.chunk_offsets, g.total, tiles_x, n_tiles, g.ts_counts, g.ts_totals, cap,
       g.ts_start, ranges, point_list);
   return cudaGetLastError();
@@ -415,7 +455,7 @@ cudaError_t launch_rebuild_keys_from_starts(cudaStream_t st, long long L, int n_
                                             const uint32_t* point_list, uint64_t* keys) {
   if (L <= 0) return cudaSuccess;
   count_launch();
-  rebuild_keys_from_starts_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>(L, n_tiles, g.ts_start, point_list,
+  launch_k(rebuild_keys_from_starts_kernel, (unsigned)((L + 255) / 256), 256, 0, st, L, n_tiles, g.ts_start, point_list,
                                                                                g.rec_a, keys);
   return cudaGetLastError();
 }
