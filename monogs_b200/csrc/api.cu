@@ -329,7 +329,7 @@ static int backward_impl(void* stream, int P, int sh_degree, int sh_coeffs, int 
   carve_image((char*)image_ws, width, height, &im);
   BackwardViews bw;
   carve_backward((char*)scratch, P, &bw);
-  GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, sizeof(float) * GRAD_STRIDE * (size_t)P, st)));
+  GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, carve_backward(nullptr, P, nullptr), st)));
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
@@ -422,7 +422,7 @@ int gsr_backward_render(void* stream, int P, int width, int height, const float*
   carve_image((char*)image_ws, width, height, &im);
   BackwardViews bw;
   carve_backward((char*)scratch, P, &bw);
-  GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, sizeof(float) * GRAD_STRIDE * (size_t)P, st)));
+  GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, carve_backward(nullptr, P, nullptr), st)));
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,

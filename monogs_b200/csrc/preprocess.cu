@@ -172,7 +172,38 @@ GSR_DEVINL void stage_store3(float* s, float4 v) {
   if (threadIdx.x < PRE_THREADS * 3 / 4) reinterpret_cast<float4*>(s)[threadIdx.x] = v;
 }
 
-__global__ void __launch_bounds__(PRE_THREADS)
+// One 256-Gaussian chunk's global input loads of a thread, parked in registers: the NEXT chunk's loads are in flight
+// while the current chunk is computed.
+struct PreLoads {
+  float4 mean, scale, rot;
+  float opac;
+  float3 col;
+};
+GSR_DEVINL PreLoads pre_issue_loads(int chunk, int P, const float* __restrict__ means3D,
+                                    const float* __restrict__ colors_precomp, const float* __restrict__ opacities,
+                                    const float* __restrict__ scales, const float* __restrict__ rotations,
+                                    bool has_cov3D) {
+  PreLoads L;
+  const long long blk_base = (long long)chunk * PRE_THREADS;
+  const int idx = (int)(blk_base + threadIdx.x);
+  L.mean = stage_load3(means3D, blk_base * 3, (long long)P * 3);
+  L.scale = make_float4(0.f, 0.f, 0.f, 0.f);
+  L.rot = make_float4(1.f, 0.f, 0.f, 0.f);
+  if (!has_cov3D) {
+    L.scale = stage_load3(scales, blk_base * 3, (long long)P * 3);
+    if (idx < P) L.rot = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+  }
+  L.opac = idx < P ? __ldg(opacities + idx) : 0.f;
+  L.col = make_float3(0.f, 0.f, 0.f);
+  if (colors_precomp != nullptr && idx < P)
+    L.col = make_float3(__ldg(colors_precomp + (size_t)idx * 3), __ldg(colors_precomp + (size_t)idx * 3 + 1),
+                        __ldg(colors_precomp + (size_t)idx * 3 + 2));
+  return L;
+}
+
+constexpr int PRE_BLOCKS_PER_SM = 4;  // persistent grid: 148 SMs x 4 CTAs walk the chunks
+
+__global__ void __launch_bounds__(PRE_THREADS, PRE_BLOCKS_PER_SM)
 preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ shs,
                       const float* __restrict__ colors_precomp, const float* __restrict__ opacities,
                       const float* __restrict__ scales, float scale_modifier,
@@ -189,27 +220,25 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   __shared__ uint32_t s_hist[4 * 256];
 
   const int tid = threadIdx.x;
-  const long long blk_base = (long long)blockIdx.x * PRE_THREADS;
-  const int idx = (int)(blk_base + tid);
+  const int n_chunks = num_pre_blocks(P);
 
   if (tid < 16) s_cam[tid] = viewmatrix[tid];
   else if (tid < 32) s_cam[tid] = projmatrix[tid - 16];
   else if (tid < 35) s_cam[tid] = campos ? campos[tid - 32] : 0.0f;
   for (int i = tid; i < 4 * 256; i += PRE_THREADS) s_hist[i] = 0;
-  // all global input loads of this thread are issued back to back
-  const float4 ld_mean = stage_load3(means3D, blk_base * 3, (long long)P * 3);
-  float4 ld_scale = make_float4(0.f, 0.f, 0.f, 0.f), my_rot = make_float4(1.f, 0.f, 0.f, 0.f);
-  if (cov3D_precomp == nullptr) {
-    ld_scale = stage_load3(scales, blk_base * 3, (long long)P * 3);
-    if (idx < P) my_rot = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
-  }
-  const float my_opac = idx < P ? __ldg(opacities + idx) : 0.f;
-  float3 my_col = make_float3(0.f, 0.f, 0.f);
-  if (colors_precomp != nullptr && idx < P)
-    my_col = make_float3(__ldg(colors_precomp + (size_t)idx * 3), __ldg(colors_precomp + (size_t)idx * 3 + 1),
-                         __ldg(colors_precomp + (size_t)idx * 3 + 2));
-  stage_store3(s_mean, ld_mean);
-  stage_store3(s_scale, ld_scale);
+  PreLoads cur = pre_issue_loads(blockIdx.x, P, means3D, colors_precomp, opacities, scales, rotations,
+                                 cov3D_precomp != nullptr);
+
+  for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+  const int idx = chunk * PRE_THREADS + tid;
+  stage_store3(s_mean, cur.mean);
+  stage_store3(s_scale, cur.scale);
+  const float4 my_rot = cur.rot;
+  const float my_opac = cur.opac;
+  const float3 my_col = cur.col;
+  if (chunk + (int)gridDim.x < n_chunks)  // the next chunk's loads fly during this chunk's arithmetic
+    cur = pre_issue_loads(chunk + gridDim.x, P, means3D, colors_precomp, opacities, scales, rotations,
+                          cov3D_precomp != nullptr);
   __syncthreads();
 
   uint32_t my_tiles = 0;
@@ -319,7 +348,8 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       atomicAdd(&s_hist[768 + (hi >> 8)], c);
     }
   }
-  __syncthreads();
+  __syncthreads();  // s_mean / s_scale are rewritten by the next chunk; last chunk: s_hist complete
+  }  // chunk loop
   for (int i = tid; i < 4 * 256; i += PRE_THREADS) {
     uint32_t c = s_hist[i];
     if (c) atomicAdd(&g.hist[i], c);
@@ -394,7 +424,8 @@ cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const fl
   const float focal_y = H / (2.0f * tan_fovy);
   const float focal_x = W / (2.0f * tan_fovx);
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
-  count_launch(); launch_k(preprocess_fwd_kernel, num_pre_blocks(P), PRE_THREADS, 0, st, 
+  const int grid = num_pre_blocks(P) < 148 * PRE_BLOCKS_PER_SM ? num_pre_blocks(P) : 148 * PRE_BLOCKS_PER_SM;
+  count_launch(); launch_k(preprocess_fwd_kernel, grid, PRE_THREADS, 0, st, 
       P, D, M, means3D, shs, colors_precomp, opacities, scales, scale_modifier, rotations, cov3D_precomp,
       viewmatrix, projmatrix, campos, W, H, tan_fovx, tan_fovy, focal_x, focal_y, tiles_x, tiles_y, prefiltered,
       radii, g);

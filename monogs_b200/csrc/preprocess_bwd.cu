@@ -95,7 +95,42 @@ GSR_DEVINL V3 sh_backward(int deg, int M, const float* __restrict__ sh, const ui
   return dnorm(dir_orig, dL_ddir);
 }
 
-__global__ void __launch_bounds__(PB_THREADS, 3)
+#ifndef PB_BLOCKS_PER_SM
+#define PB_BLOCKS_PER_SM 2
+#endif
+// One Gaussian's global input loads, all issued up front, unconditionally (the kernel is latency-bound: a chain
+// radii -> packed -> inputs would serialise three DRAM round trips).  Prefetching the next chunk's loads was
+// measured: the extra 23 registers spill and cost more than the overlap gains.
+struct PbLoads {
+  int radius;
+  float4 pk0, pk1, pk2, rot;
+  float m[3], s[3];
+};
+GSR_DEVINL PbLoads pb_issue_loads(int idx, int P, const int* __restrict__ radii, const float* __restrict__ packed,
+                                  const float* __restrict__ means3D, const float* __restrict__ scales,
+                                  const float* __restrict__ rotations, bool has_cov3D) {
+  PbLoads L;
+  L.radius = 0;
+  L.pk0 = make_float4(0.f, 0.f, 0.f, 0.f); L.pk1 = L.pk0; L.pk2 = L.pk0; L.rot = L.pk0;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { L.m[k] = 0.f; L.s[k] = 0.f; }
+  if (idx < P) {
+    L.radius = __ldg(radii + idx);
+    L.pk0 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE));
+    L.pk1 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 4));
+    L.pk2 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 8));
+#pragma unroll
+    for (int k = 0; k < 3; ++k) L.m[k] = __ldg(means3D + 3 * (size_t)idx + k);
+    if (!has_cov3D) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) L.s[k] = __ldg(scales + 3 * (size_t)idx + k);
+      L.rot = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+    }
+  }
+  return L;
+}
+
+__global__ void __launch_bounds__(PB_THREADS, PB_BLOCKS_PER_SM)
 preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
                       const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
                       const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
@@ -123,7 +158,12 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   const float* v = s_cam;
   const float* p = s_cam + 16;
 
-  const int idx = p_begin + blockIdx.x * PB_THREADS + tid;  // P = end of this launch's Gaussian range
+  // persistent grid: every CTA walks chunks of PB_THREADS Gaussians of the range [p_begin, P) and keeps ONE fp64
+  // pose-gradient accumulator per thread (fixed chunk assignment: the sums are deterministic)
+  double tacc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  const int n_chunks = (P - p_begin + PB_THREADS - 1) / PB_THREADS;
+  for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+  const int idx = p_begin + chunk * PB_THREADS + tid;  // P = end of this launch's Gaussian range
   float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   float g2x = 0.f, g2y = 0.f, gop = 0.f, gcr = 0.f, gcg = 0.f, gcb = 0.f;
   V3 dmean = v3(0, 0, 0);
@@ -131,24 +171,10 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   float dscale[3] = {0.f, 0.f, 0.f};
   float drot[4] = {0.f, 0.f, 0.f, 0.f};
   const bool in_range = idx < P;
-  // every global load of this thread is issued up front, unconditionally (the kernel is latency-bound: a chain
-  // radii -> packed -> inputs would serialise three DRAM round trips)
-  int my_radius = 0;
-  float4 pk0 = make_float4(0.f, 0.f, 0.f, 0.f), pk1 = pk0, pk2 = pk0, ld_rot = pk0;
-  float ld_m[3] = {0.f, 0.f, 0.f}, ld_s[3] = {0.f, 0.f, 0.f};
-  if (in_range) {
-    my_radius = __ldg(radii + idx);
-    pk0 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE));
-    pk1 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 4));
-    pk2 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 8));
-#pragma unroll
-    for (int k = 0; k < 3; ++k) ld_m[k] = __ldg(means3D + 3 * (size_t)idx + k);
-    if (!cov3D_precomp) {
-#pragma unroll
-      for (int k = 0; k < 3; ++k) ld_s[k] = __ldg(scales + 3 * (size_t)idx + k);
-      ld_rot = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
-    }
-  }
+  const PbLoads L = pb_issue_loads(idx, P, radii, packed, means3D, scales, rotations, cov3D_precomp != nullptr);
+  const int my_radius = L.radius;
+  const float4 pk0 = L.pk0, pk1 = L.pk1, pk2 = L.pk2, ld_rot = L.rot;
+  const float ld_m[3] = {L.m[0], L.m[1], L.m[2]}, ld_s[3] = {L.s[0], L.s[1], L.s[2]};
   const bool visible = in_range && my_radius > 0;
 
   if (visible) {
@@ -367,12 +393,15 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       r4[0] = o0; r4[1] = o1; r4[2] = o2; r4[3] = o3;
     }
   }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) tacc[k] += (double)tau[k];
+  }  // chunk loop
 
   // ---- block reduction of dL/dtau in fp64 ----
   double td[6];
 #pragma unroll
   for (int k = 0; k < 6; ++k) {
-    td[k] = (double)tau[k];
+    td[k] = tacc[k];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) td[k] += __shfl_xor_sync(0xffffffffu, td[k], o);
   }
@@ -426,7 +455,10 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
                                   int p_begin, int p_end, float* rows, int accumulate) {
   const float focal_y = H / (2.0f * tan_fovy);
   const float focal_x = W / (2.0f * tan_fovx);
-  const int nb = num_pre_blocks(p_end - p_begin);  // p_begin is a multiple of 256 (checked by the caller)
+  // p_begin is a multiple of 256 (checked by the caller); persistent grid of 148 SMs x PB_BLOCKS_PER_SM CTAs. Partial slot of CTA b
+  // = p_begin / 256 + b: distinct over the ranges of one backward; slots no CTA writes stay zero (memset with packed)
+  int nb = num_pre_blocks(p_end - p_begin);
+  if (nb > 148 * PB_BLOCKS_PER_SM) nb = 148 * PB_BLOCKS_PER_SM;
   if (nb > 0) {
     count_launch();
     launch_k(preprocess_bwd_kernel, nb, PB_THREADS, 0, st, p_end, D, M, means3D, radii, shs, clamped, scales, rotations,

@@ -389,11 +389,13 @@ def test_window_rows_backward_equals_plain_backward(built):
     n = lambda t: t.detach().cpu().numpy()
     sl = window.column_slices()
     vis = (radii > 0)
+    # two separate backward passes: the float atomics of the tile renderer land in a different order each time,
+    # so the two results agree to accumulation noise (the gradient bar of the north star is 1e-4)
     for name, i in (("means3D", 3), ("colors", 1), ("opacities", 2), ("scales", 6), ("rotations", 7)):
-        assert rel_inf(n(rows[:, sl[name]]), n(plain[i])) <= 1e-5, name
-    assert rel_inf(n(m2d), n(plain[0])) <= 1e-5
+        assert rel_inf(n(rows[:, sl[name]]), n(plain[i])) <= 5e-5, name
+    assert rel_inf(n(m2d), n(plain[0])) <= 5e-5
     assert torch.equal(rows[:, 15], vis.float())
-    assert rel_inf(n(rows[:, 14]), n(plain[0][:, :2].norm(dim=1) * vis)) <= 1e-5
+    assert rel_inf(n(rows[:, 14]), n(plain[0][:, :2].norm(dim=1) * vis)) <= 5e-5
     assert rel_inf(n(tau), n(plain[8]).astype(np.float64).sum(0)) <= 1e-4
     # second keyframe added on top: rows == 2 x single (same keyframe twice)
     once = rows.clone()

@@ -23,6 +23,10 @@ ncuother)
   CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
   $CMD > gpurun_out/plain3.log 2>&1 && \
   ncu --set full --clock-control none --import-source on -k regex:"onesweep|preprocess_|emit_|tile_|chunk_" -s 14 -c 14 -f -o gpurun_out/prof_other $CMD > gpurun_out/ncu_other.log 2>&1 ;;
+ncupre)
+  CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
+  $CMD > gpurun_out/plain5.log 2>&1 && \
+  ncu --set full --clock-control none --import-source on -k regex:"preprocess_|gather_rects|chunk_scan" -s 4 -c 4 -f -o gpurun_out/prof_pre $CMD > gpurun_out/ncu_pre.log 2>&1 ;;
 ncuts)
   CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
   $CMD > gpurun_out/plain4.log 2>&1 && \
