@@ -500,13 +500,20 @@ def stage_bytes(u):
     Render stages use the instances actually consumed (early termination skips the rest of a tile's list)."""
     P, V, R, N = u["P"], u["V"], u["R"], u["N"]
     Rc = u["R_consumed"] if u.get("R_consumed") is not None else R
+    T = (N + 255) // 256  # tiles (exact for the bench's 16-divisible image sizes)
+    if T <= 4096:
+        # sort-free binning (tile_scatter.cu): count matrix of nb CTAs x T tiles instead of instance keys
+        nb = 148 * max(1, min(4, 232448 // (16512 + 8448 + 24 * T + 1024)))
+        emit, tile_sort, ranges = 8 * P + 4 * nb * T, 12 * nb * T + 12 * P + 4 * R + 16 * T, 0
+    else:
+        emit, tile_sort, ranges = 12 * R, 24 * R, 8 * R
     return {
         "preprocess": 44 * P + 8 * P + 52 * V,
         "depth_sort": 16 * P,
         "scan": 8 * P,
-        "emit": 12 * R,
-        "tile_sort": 24 * R,
-        "ranges": 8 * R,
+        "emit": emit,
+        "tile_sort": tile_sort,
+        "ranges": ranges,
         "render_fwd": 44 * Rc + 28 * N + 4 * P,
         "render_bwd": 84 * Rc + 24 * N,
         "preprocess_bwd": 164 * V + 48 * P,
@@ -682,6 +689,13 @@ def main():
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                             "frac": achieved / peak, "traffic": ncu_traffic(dom), "peak_source": peak_src,
                             "algorithmic_bytes_per_launch": sb[dom], "ms_per_launch": per_launch_ms[dom]}
+        # the same kernels against SURVEY 8d's per-instance terms with the FULL instance count R (the formula
+        # assumes every instance of a tile list is read; early termination makes the kernels skip most of them)
+        full = dict(units, R_consumed=None)
+        sbf = stage_bytes(full)
+        line["roofline"]["survey_formula_full_R"] = {
+            s: {"bytes": sbf[s], "frac": round(sbf[s] / (per_launch_ms[s] * 1e-3) / 1e9 / peak, 4)}
+            for s in ("render_fwd", "render_bwd") if per_launch_ms[s] > 0}
         line["stages_ms_per_step"] = {s: round(per_launch_ms[s], 5) for s in STAGES}
         line["stages_frac_of_hbm_peak"] = {s: round(sb[s] / (per_launch_ms[s] * 1e-3) / 1e9 / peak, 4)
                                            if per_launch_ms[s] > 0 else None for s in STAGES}

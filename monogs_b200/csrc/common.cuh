@@ -86,14 +86,20 @@ inline SortPlan make_sort_plan(int total_bits) {
 }
 
 constexpr int TS_MAX_TILES = 4096;   // above this the per-tile shared-memory state no longer fits: radix path
-constexpr int TS_GROUP_SMEM = 33536; // staged Gaussian group + staged piece of tile_scatter.cu
+#ifndef TS_ITEMS_PER_THREAD
+#define TS_ITEMS_PER_THREAD 8          // instances per thread and piece of the scatter kernel
+#endif
+#ifndef TS_MAX_OCC
+#define TS_MAX_OCC 4                   // CTAs per SM the scatter kernel's registers allow
+#endif
+constexpr int TS_GROUP_SMEM = 16512 + (256 * TS_ITEMS_PER_THREAD / 32 * 33) * 4;  // staged Gaussians + staged piece
 constexpr int TS_TILE_SMEM = 24;     // per tile: cursor + piece base (u32) + 8 per-warp u16 counters
 // CTAs of the sort-free binning = rows of its count matrix: as many per SM as the scatter kernel's shared memory
-// allows (at most 3: its register budget), on the 148 SMs of a B200.
+// allows (at most TS_MAX_OCC: its register budget), on the 148 SMs of a B200.
 __host__ __device__ inline int ts_blocks(size_t n_tiles) {
   const size_t smem = (size_t)TS_GROUP_SMEM + n_tiles * TS_TILE_SMEM + 1024;
   size_t occ = (size_t)232448 / smem;
-  occ = occ > 3 ? 3 : (occ < 1 ? 1 : occ);
+  occ = occ > TS_MAX_OCC ? TS_MAX_OCC : (occ < 1 ? 1 : occ);
   return 148 * (int)occ;
 }
 __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, GeomViews* v) {

@@ -386,18 +386,38 @@ GSR_DEVINL uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp, uint
 }
 
 // chunk sums -> exclusive chunk offsets (in place) + total = num_rendered (cub InclusiveSum, rasterizer_impl.cu:280).
+// One block; 4 consecutive chunks per thread and round (one 16-byte load), so 1M Gaussians are a single round.
 __global__ void __launch_bounds__(SCAN_THREADS)
 chunk_scan_kernel(int n_chunks, uint32_t* __restrict__ chunk_sums, unsigned long long* __restrict__ total) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ uint32_t s_warp[33];
   unsigned long long carry = 0;
-  for (int base = 0; base < n_chunks; base += SCAN_THREADS) {
-    const int i = base + threadIdx.x;
-    const uint32_t v = i < n_chunks ? chunk_sums[i] : 0u;
+  for (int base = 0; base < n_chunks; base += SCAN_THREADS * 4) {
+    const int i0 = base + threadIdx.x * 4;
+    uint32_t v[4] = {0u, 0u, 0u, 0u};
+    if (i0 + 4 <= n_chunks) {
+      const uint4 x = *reinterpret_cast<const uint4*>(chunk_sums + i0);
+      v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) if (i0 + j < n_chunks) v[j] = chunk_sums[i0 + j];
+    }
     uint32_t tot;
-    const uint32_t ex = block_exclusive_scan_1024(v, s_warp, tot);
-    if (i < n_chunks) chunk_sums[i] = (uint32_t)(carry + ex);
+    const uint32_t ex = block_exclusive_scan_1024(v[0] + v[1] + v[2] + v[3], s_warp, tot);
+    unsigned long long run = carry + ex;
+    if (i0 + 4 <= n_chunks) {
+      uint4 o;
+      o.x = (uint32_t)run; o.y = (uint32_t)(run + v[0]); o.z = (uint32_t)(run + v[0] + v[1]);
+      o.w = (uint32_t)(run + v[0] + v[1] + v[2]);
+      *reinterpret_cast<uint4*>(chunk_sums + i0) = o;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (i0 + j < n_chunks) chunk_sums[i0 + j] = (uint32_t)run;
+        run += v[j];
+      }
+    }
     carry += tot;
     __syncthreads();
   }

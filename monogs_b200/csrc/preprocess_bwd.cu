@@ -470,7 +470,8 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
   }
   // the pose gradient is complete once the LAST range has run (ranges are issued in ascending order)
   if (dL_dtau && p_end == P) {
-    count_launch(); launch_k(tau_final_kernel, 1, 256, 0, st, num_pre_blocks(P), bw.tau_partial, dL_dtau);
+    // slots above the last range's are never written (ranges ascend), the others are written or still zero
+    count_launch(); launch_k(tau_final_kernel, 1, 256, 0, st, p_begin / PB_THREADS + nb, bw.tau_partial, dL_dtau);
   }
   return cudaGetLastError();
 }

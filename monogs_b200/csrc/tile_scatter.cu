@@ -23,8 +23,8 @@ constexpr int TS_THREADS = 256;
 constexpr int TS_WARPS = TS_THREADS / 32;
 constexpr int TS_GPT = 4;                          // Gaussians per thread in a staged group
 constexpr int TS_GROUP = TS_THREADS * TS_GPT;      // 1024 Gaussians = 4 entries of chunk_offsets
-constexpr int TS_ITEMS = 16;                       // instances per thread per piece
-constexpr int TS_PIECE = TS_THREADS * TS_ITEMS;    // 4096 instances ranked at a time
+constexpr int TS_ITEMS = TS_ITEMS_PER_THREAD;      // instances per thread per piece
+constexpr int TS_PIECE = TS_THREADS * TS_ITEMS;    // 2048 instances ranked at a time
 #ifndef TS_MATCH_BATCH
 #define TS_MATCH_BATCH 4
 #endif
@@ -234,7 +234,7 @@ constexpr int TS_STAGE_WORDS = TS_PIECE + TS_PIECE / 32;
 static_assert(sizeof(TsGroup) + TS_STAGE_WORDS * 4 <= TS_GROUP_SMEM, "ts_blocks() budgets TS_GROUP_SMEM bytes");
 static_assert(TS_GROUP <= 1024 && TS_MAX_TILES <= (1 << 22), "stage word = tile << 10 | slot");
 
-__global__ void __launch_bounds__(TS_THREADS, 3)
+__global__ void __launch_bounds__(TS_THREADS, TS_MAX_OCC)
 tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* __restrict__ order,
                     const uint32_t* __restrict__ chunk_offsets, const unsigned long long* __restrict__ total_dev,
                     int tiles_x, int n_tiles, const uint32_t* __restrict__ counts /*exclusive over chunks*/,

@@ -1,0 +1,23 @@
+"""tools/ncu_full_summary.py REP [HEADER...] -- the metrics DESIGN.md / bench.py quote, per captured launch, from
+`ncu -i REP --page raw --csv` of an `ncu --set full` capture."""
+import csv, subprocess, sys
+WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "launch__registers_per_thread", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
+        "launch__grid_size", "smsp__inst_executed.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__throughput.avg.pct_of_peak_sustained_elapsed", "sm__cycles_active.avg"]
+def main(rep, header):
+    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    idx = {h: i for i, h in enumerate(hdr)}
+    for h in header: print("# " + h)
+    for r in rows[2:]:
+        print("----")
+        print(f"{'Kernel Name':72s} {r[idx['Kernel Name']][:80]}")
+        for m in WANT:
+            if m in idx: print(f"{m:72s} {r[idx[m]]} {units[idx[m]]}")
+if __name__ == "__main__":
+    main(sys.argv[1], sys.argv[2:])
