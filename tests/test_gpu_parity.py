@@ -169,6 +169,8 @@ REF_CASES = [
     (50_000, "tum", 2, True, False),
     (60_000, "tum", 3, False, True),
     (300_000, "replica", 4, False, False),
+    (200_000, "hd", 5, False, False),        # 8160 tiles > 4096: the instance radix-sort binning path (C5 shape)
+    (3_000, "tum_half", 6, False, False),    # fewer Gaussians than binning CTAs
 ]
 
 
@@ -434,3 +436,39 @@ def test_mapping_window_cuda_backend_single_gpu(built):
     for name in want:
         assert rel_inf(n(res.grads[name]), n(want[name])) <= 1e-4, name
     assert torch.equal(res.vis_count, vis_count) and torch.equal(res.max_radii, max_r)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# (5) the two binning implementations produce the same lists: GSR_BINNING=radix (read once per process, so a
+#     child process) against the default sort-free path at a size both support
+# ----------------------------------------------------------------------------------------------------------------
+_BINNING_CHILD = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+import test_gpu_parity as T
+from monogs_b200 import synth
+cam = synth.make_camera("tum", rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))
+sc = synth.make_scene(120_000, cam, seed=11, device="cuda")
+bg = torch.tensor([0.1, 0.2, 0.3], device="cuda")
+z3, z1 = torch.zeros(3, cam.H, cam.W, device="cuda"), torch.zeros(1, cam.H, cam.W, device="cuda")
+o = T._run_ours(cam, sc, bg, z3, z1)
+_, n_contrib, ranges = T._image_state(o["img"], cam.W, cam.H)
+np.savez(sys.argv[2], R=o["R"], plist=o["plist"].cpu().numpy()[:o["R"]], keys=o["keys"].cpu().numpy(), ranges=ranges,
+         n_contrib=n_contrib, color=o["color"].cpu().numpy(), n_touched=o["n_touched"].cpu().numpy())
+"""
+
+
+def test_radix_and_sort_free_binning_agree(built, tmp_path):
+    import os, subprocess, sys
+    outs = {}
+    for mode in ("radix", "scatter"):
+        env = dict(os.environ, GSR_BINNING=mode)
+        f = tmp_path / f"{mode}.npz"
+        r = subprocess.run([sys.executable, "-c", _BINNING_CHILD, str(ROOT), str(f)], env=env, capture_output=True,
+                           text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs[mode] = np.load(f)
+    a, b = outs["radix"], outs["scatter"]
+    assert int(a["R"]) == int(b["R"]) > 0
+    for k in ("plist", "keys", "ranges", "n_contrib", "n_touched", "color"):
+        assert np.array_equal(a[k], b[k]), k
