@@ -28,6 +28,10 @@ constexpr int RS_WARPS = RS_THREADS / 32;
 #define GSR_RS_LOOKBACK_BATCH 8
 #endif
 constexpr int RS_LOOKBACK_BATCH = GSR_RS_LOOKBACK_BATCH;
+#ifndef GSR_RS_MATCH_BATCH
+#define GSR_RS_MATCH_BATCH 8
+#endif
+constexpr int RS_MATCH_BATCH = GSR_RS_MATCH_BATCH;
 constexpr uint32_t FLAG_LOCAL = 1u << 30;
 constexpr uint32_t FLAG_INCL = 2u << 30;
 constexpr uint32_t FLAG_MASK = 3u << 30;
@@ -94,21 +98,30 @@ onesweep_pass_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     val[i] = (t < tile_n) ? vals_in[tile_base + t] : 0u;
   }
 
-  // ---- rank inside the warp (padding keys take the largest digit and sort last) ----
+  // ---- rank inside the warp (padding keys take the largest digit and sort last); the match.any of a batch of
+  //      items are issued back to back so that their latencies overlap, then the counters are updated in order ----
+  constexpr int MB = ITEMS < RS_MATCH_BATCH ? ITEMS : RS_MATCH_BATCH;
 #pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const int t = wbase + i * 32 + lane;
-    const uint32_t d = (t < tile_n) ? (uint32_t)((key[i] >> shift) & dmask) : dmask;
-    const uint32_t peers = __match_any_sync(0xffffffffu, d);
-    const uint32_t below = __popc(peers & ((1u << lane) - 1u));
-    uint32_t prev = 0;
-    if (below == 0) {
-      prev = sm.warp_hist[w][d];
-      sm.warp_hist[w][d] = prev + __popc(peers);
+  for (int i0 = 0; i0 < ITEMS; i0 += MB) {
+    uint32_t dg[MB], peers[MB];
+#pragma unroll
+    for (int j = 0; j < MB; ++j) {
+      const int t = wbase + (i0 + j) * 32 + lane;
+      dg[j] = (t < tile_n) ? (uint32_t)((key[i0 + j] >> shift) & dmask) : dmask;
+      peers[j] = __match_any_sync(0xffffffffu, dg[j]);
     }
-    prev = __shfl_sync(0xffffffffu, prev, __ffs(peers) - 1);
-    rank[i] = prev + below;
-    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < MB; ++j) {
+      const uint32_t below = __popc(peers[j] & ((1u << lane) - 1u));
+      uint32_t prev = 0;
+      if (below == 0) {
+        prev = sm.warp_hist[w][dg[j]];
+        sm.warp_hist[w][dg[j]] = prev + __popc(peers[j]);
+      }
+      prev = __shfl_sync(0xffffffffu, prev, __ffs(peers[j]) - 1);
+      rank[i0 + j] = prev + below;
+      __syncwarp();
+    }
   }
   __syncthreads();
 
