@@ -261,6 +261,10 @@ int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, cons
 int gsr_debug_image_views(const void* image_ws, int width, int height,
                           const float** final_T, const uint32_t** n_contrib,
                           const uint32_t** ranges /*uint2[tiles]*/);
+/* Test hook: 0 = automatic choice of the binning implementation (sort-free for images of <= 4096 tiles, instance
+ * radix sort above), 1 = radix sort at every size. Both produce the identical point_list / ranges. A forward and
+ * the gsr_debug_sorted_keys call that inspects it must run under the same mode. */
+int gsr_debug_set_binning(int mode);
 /* Rebuilds the reference's sorted 64-bit keys (tile << 32 | depth bits, rasterizer_impl.cu:102-104) of the
  * LAST gsr_forward_render call that used these workspaces into keys_sorted[num_rendered] (device). */
 int gsr_debug_sorted_keys(void* stream, const void* geom_ws, const void* binning_ws,

@@ -147,12 +147,16 @@ static SortPlan tile_sort_plan(int W, int H) { return make_sort_plan(higher_msb(
 // instance emit + tile sort + ranges + render. `cap` bounds the instances written; the actual count is read
 // from n_dev (device) when given, else it IS cap.
 // GSR_BINNING=radix forces the instance radix sort for every image size (A/B measurements, tests).
+// gsr_debug_set_binning overrides it at run time (tests compare the two implementations in one process).
+static std::atomic<int> g_binning_mode{-1};  // -1: not decided yet, 0: automatic, 1: radix everywhere
 static bool use_tile_scatter(int width, int height) {
-  static const bool force_radix = [] {
+  int mode = g_binning_mode.load();
+  if (mode < 0) {
     const char* e = getenv("GSR_BINNING");
-    return e && strcmp(e, "radix") == 0;
-  }();
-  return !force_radix && num_tiles(width, height) <= (size_t)TS_MAX_TILES;
+    mode = (e && strcmp(e, "radix") == 0) ? 1 : 0;
+    g_binning_mode.store(mode);
+  }
+  return mode == 0 && num_tiles(width, height) <= (size_t)TS_MAX_TILES;
 }
 
 static int enqueue_render(cudaStream_t st, int P, int width, int height, const float* background,
@@ -540,6 +544,12 @@ int gsr_debug_image_views(const void* image_ws, int width, int height, const flo
   if (final_T) *final_T = im.final_T;
   if (n_contrib) *n_contrib = im.n_contrib;
   if (ranges) *ranges = (const uint32_t*)im.ranges;
+  return GSR_OK;
+}
+
+int gsr_debug_set_binning(int mode) {
+  if (mode != 0 && mode != 1) return GSR_EINVAL;
+  g_binning_mode.store(mode);
   return GSR_OK;
 }
 
