@@ -615,8 +615,8 @@ def main():
     e2e = None
     if not a.no_e2e:
         es = E2EStep(wl, world, impl)
-        k_e2e = max(3, min(a.steps, 20))
-        for _ in range(3):
+        k_e2e = max(3, min(2 * a.steps, 60))  # longer than the device leg: host-side jitter averages out
+        for _ in range(5):
             es.step()
         barrier(world)
         t0 = torch.cuda.Event(enable_timing=True)
@@ -639,7 +639,7 @@ def main():
     if not a.no_e2e and impl == "ours":
         # the same iteration through the ADDITIONAL fused entry point (monogs_b200.fused_loss.render_l1_loss)
         ef = E2EStep(wl, world, "ours-fused")
-        for _ in range(3):
+        for _ in range(5):
             ef.step()
         barrier(world)
         t0 = torch.cuda.Event(enable_timing=True)
