@@ -219,6 +219,16 @@ int gsr_mark_visible(void* stream, int P, const float* means3D,
                      const float* viewmatrix, const float* projmatrix,
                      uint8_t* present);
 
+/* Per-call camera matrices of the reference's render() wrapper in ONE launch, no host synchronisation
+ * (gaussian_splatting/gaussian_renderer/__init__.py:63-84, utils/camera_utils.py:171-178,224-231: a 4x4
+ * assembly, a general 4x4 inverse and a bmm per call there):
+ *   viewmatrix[16]  = getWorld2View(R, T)^T          (row-major; element [4*c + r] = W2C[r][c])
+ *   projmatrix[16]  = viewmatrix x proj_T            (proj_T = projection matrix already transposed)
+ *   campos[3]       = row 3 of viewmatrix^-1 = -R^-1 T (general 3x3 inverse, R need not be orthonormal)
+ * R and T are read with element strides (r_stride_row, r_stride_col, t_stride) so that views of a 4x4 pose work. */
+int gsr_camera_setup(void* stream, const float* R, int r_stride_row, int r_stride_col, const float* T,
+                     int t_stride, const float* proj_T, float* viewmatrix, float* projmatrix, float* campos);
+
 /* mean_dist2[P] = mean squared distance to the 3 nearest other points. */
 int gsr_knn_dist2(void* stream, int P, const float* points, float* mean_dist2,
                   void* knn_ws);

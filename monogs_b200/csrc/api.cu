@@ -471,6 +471,13 @@ int gsr_mark_visible(void* stream, int P, const float* means3D, const float* vie
   return check(launch_mark_visible((cudaStream_t)stream, P, means3D, viewmatrix, present));
 }
 
+int gsr_camera_setup(void* stream, const float* R, int r_stride_row, int r_stride_col, const float* T,
+                     int t_stride, const float* proj_T, float* viewmatrix, float* projmatrix, float* campos) {
+  if (!R || !T || !proj_T || !viewmatrix || !projmatrix || !campos) return GSR_EINVAL;
+  return check(launch_camera_setup((cudaStream_t)stream, R, r_stride_row, r_stride_col, T, t_stride, proj_T,
+                                   viewmatrix, projmatrix, campos));
+}
+
 int gsr_knn_dist2(void* stream, int P, const float* points, float* mean_dist2, void* knn_ws) {
   if (P < 0) return GSR_EINVAL;
   if (P == 0) return GSR_OK;

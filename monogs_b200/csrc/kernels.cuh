@@ -14,6 +14,9 @@ cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const fl
 cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g);
 cudaError_t launch_mark_visible(cudaStream_t st, int P, const float* means3D, const float* viewmatrix,
                                 uint8_t* present);
+cudaError_t launch_camera_setup(cudaStream_t st, const float* R, int rs, int cs, const float* T, int ts,
+                                const float* proj_T,
+                                float* viewmatrix, float* projmatrix, float* campos);
 
 // binning.cu
 cudaError_t launch_gather_rects(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g);

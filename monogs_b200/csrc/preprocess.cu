@@ -434,6 +434,39 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
   present[idx] = !(affine_row(viewmatrix, 2, x, y, z) <= 0.2f);
 }
 
+// Camera matrices of one render() call (gsr_camera_setup): 16 threads, thread t = element (row i, column j).
+__global__ void camera_setup_kernel(const float* __restrict__ R, int rs, int cs, const float* __restrict__ T, int ts,
+                                    const float* __restrict__ proj_T, float* __restrict__ viewmatrix,
+                                    float* __restrict__ projmatrix, float* __restrict__ campos) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float v[16];
+  const int t = threadIdx.x, i = t >> 2, j = t & 3;
+  // viewmatrix = W2C^T with W2C = [R T; 0 0 0 1]: v[i][j] = W2C[j][i]
+  float e;
+  if (i < 3) e = j < 3 ? R[j * rs + i * cs] : 0.0f;
+  else e = j < 3 ? T[j * ts] : 1.0f;
+  v[t] = e;
+  viewmatrix[t] = e;
+  __syncthreads();
+  // projmatrix = viewmatrix x proj_T, k = 0..3 in order, one rounding per step
+  float acc = __fmul_rn(v[i * 4], proj_T[j]);
+#pragma unroll
+  for (int k = 1; k < 4; ++k) acc = __fmaf_rn(v[i * 4 + k], proj_T[k * 4 + j], acc);
+  projmatrix[t] = acc;
+  if (t < 3) {
+    // campos = -R^-1 T by the adjugate (R^-1 = adj(R) / det R)
+    const float a = R[0], b = R[cs], c = R[2 * cs], d = R[rs], f = R[rs + cs], g = R[rs + 2 * cs], h = R[2 * rs],
+                k2 = R[2 * rs + cs], m = R[2 * rs + 2 * cs];
+    const float det = a * (f * m - g * k2) - b * (d * m - g * h) + c * (d * k2 - f * h);
+    float r0, r1, r2;  // row t of adj(R)
+    if (t == 0) { r0 = f * m - g * k2; r1 = c * k2 - b * m; r2 = b * g - c * f; }
+    else if (t == 1) { r0 = g * h - d * m; r1 = a * m - c * h; r2 = c * d - a * g; }
+    else { r0 = d * k2 - f * h; r1 = b * h - a * k2; r2 = a * f - b * d; }
+    campos[t] = -(r0 * T[0] + r1 * T[ts] + r2 * T[2 * ts]) / det;
+  }
+}
+
 // ---------------------------------------------------------------------------
 cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const float* means3D, const float* shs,
                                   const float* colors_precomp, const float* opacities, const float* scales,
@@ -458,6 +491,12 @@ cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, con
   cudaError_t e = launch_gather_rects(st, P, order, g);
   if (e != cudaSuccess) return e;
   count_launch(); launch_k(chunk_scan_kernel, 1, SCAN_THREADS, 0, st, nc, g.chunk_offsets, g.total);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_camera_setup(cudaStream_t st, const float* R, int rs, int cs, const float* T, int ts,
+                                const float* proj_T, float* viewmatrix, float* projmatrix, float* campos) {
+  count_launch(); launch_k(camera_setup_kernel, 1, 16, 0, st, R, rs, cs, T, ts, proj_T, viewmatrix, projmatrix, campos);
   return cudaGetLastError();
 }
 
