@@ -271,6 +271,9 @@ int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, cons
 int gsr_debug_image_views(const void* image_ws, int width, int height,
                           const float** final_T, const uint32_t** n_contrib,
                           const uint32_t** ranges /*uint2[tiles]*/);
+/* 1 when a forward at this image size uses the instance radix sort and therefore needs the binning workspace
+ * (gsr_binning_bytes); 0 when the sort-free binning is used: binning_ws may then be NULL. */
+int gsr_binning_needed(int width, int height);
 /* Test hook: 0 = automatic choice of the binning implementation (sort-free for images of <= 4096 tiles, instance
  * radix sort above), 1 = radix sort at every size. Both produce the identical point_list / ranges. A forward and
  * the gsr_debug_sorted_keys call that inspects it must run under the same mode. */

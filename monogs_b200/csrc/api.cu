@@ -263,7 +263,7 @@ int gsr_forward_render(void* stream, int P, int width, int height, const float* 
   if (P == 0) return GSR_OK;  // reference returns its zero-filled outputs (rasterize_points.cu:85)
   if (!background || !radii || !geom_ws || !image_ws || !out_color || !out_depth || !out_opacity || !n_touched)
     return GSR_EINVAL;
-  if (num_rendered > 0 && (!binning_ws || !point_list)) return GSR_EINVAL;
+  if (num_rendered > 0 && (!point_list || (!binning_ws && !use_tile_scatter(width, height)))) return GSR_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
@@ -287,7 +287,7 @@ int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs, int width, in
   GSR_TRY(check_forward_args(P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
                              rotations, cov3D_precomp, viewmatrix, projmatrix, campos, radii, geom_ws));
   if (!background || !image_ws || !out_color || !out_depth || !out_opacity || !n_touched) return GSR_EINVAL;
-  if (capacity > 0 && (!binning_ws || !point_list)) return GSR_EINVAL;
+  if (capacity > 0 && (!point_list || (!binning_ws && !use_tile_scatter(width, height)))) return GSR_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
@@ -552,6 +552,11 @@ int gsr_debug_image_views(const void* image_ws, int width, int height, const flo
   if (n_contrib) *n_contrib = im.n_contrib;
   if (ranges) *ranges = (const uint32_t*)im.ranges;
   return GSR_OK;
+}
+
+int gsr_binning_needed(int width, int height) {
+  if (width <= 0 || height <= 0) return 0;
+  return use_tile_scatter(width, height) ? 0 : 1;
 }
 
 int gsr_debug_set_binning(int mode) {

@@ -34,7 +34,26 @@ def _f32(t, name):
 
 
 def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    """The caller's current CUDA stream (raw handle; the C call is ~10x cheaper than building a Stream object)."""
+    return C.c_void_p(torch._C._cuda_getCurrentRawStream(torch.cuda.current_device()))
+
+
+class _on_device:
+    """`with _on_device(dev)` that costs nothing when `dev` already is the current device (the usual case:
+    one process per GPU); the generic context manager is ~15 us of Python per use."""
+    __slots__ = ("ctx",)
+
+    def __init__(self, dev):
+        self.ctx = None if dev.index is None or dev.index == torch.cuda.current_device() else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+        return False
 
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
@@ -56,7 +75,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         zi = torch.zeros(0, dtype=torch.int32, device=dev)
         return 0, z(NUM_CHANNELS, H, W), zi, e, e.clone(), e.clone(), z(1, H, W), z(1, H, W), zi.clone()
 
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         means3D_c = _f32(means3D, "means3D")
         colors_c, opacity_c = _f32(colors, "colors"), _f32(opacity, "opacity")
         scales_c, rot_c, cov_c = _f32(scales, "scales"), _f32(rotations, "rotations"), _f32(cov3D_precomp, "cov3D_precomp")
@@ -81,14 +100,16 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         out_args = (out_color.data_ptr(), out_depth.data_ptr(), out_opacity.data_ptr(), n_touched.data_ptr())
         key = (P, W, H, dev.index)
         cap = _capacity.get(key)
+        # the instance-sort workspace exists only where the radix binning runs (images of > 4096 tiles)
+        bin_bytes = lib.gsr_binning_bytes if lib.gsr_binning_needed(W, H) else (lambda n: 0)
         done = False
         if cap is not None and not debug:
             # single call, no GPU bubble: the instance-level kernels are enqueued for a capacity remembered from
             # the last call of this shape; the host wait for num_rendered overlaps them
             point_list = torch.empty(lib.gsr_point_list_bytes(cap), dtype=torch.uint8, device=dev)
-            binning = torch.empty(lib.gsr_binning_bytes(cap), dtype=torch.uint8, device=dev)
+            binning = torch.empty(bin_bytes(cap), dtype=torch.uint8, device=dev)
             rc = lib.gsr_forward(*plan_args, _ptr(bg_c), *in_args, radii.data_ptr(), geom.data_ptr(), img.data_ptr(),
-                                 binning.data_ptr(), point_list.data_ptr(), cap, *out_args, C.byref(R), 0)
+                                 _ptr(binning), point_list.data_ptr(), cap, *out_args, C.byref(R), 0)
             if rc != _abi.GSR_ECAPACITY:
                 _abi.check(rc, "gsr_forward")
                 done = True
@@ -101,7 +122,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         R = int(R.value)
         if not done:
             point_list = torch.empty(lib.gsr_point_list_bytes(R), dtype=torch.uint8, device=dev)
-            binning = torch.empty(lib.gsr_binning_bytes(R) if R > 0 else 0, dtype=torch.uint8, device=dev)
+            binning = torch.empty(bin_bytes(R) if R > 0 else 0, dtype=torch.uint8, device=dev)
             rc = lib.gsr_forward_render(st, P, W, H, _ptr(bg_c), radii.data_ptr(), geom.data_ptr(), img.data_ptr(),
                                         _ptr(binning), point_list.data_ptr(), R, *out_args, int(bool(debug)))
             _abi.check(rc, "gsr_forward_render")
@@ -142,7 +163,7 @@ def _backward_impl(background, means3D, radii, colors, scales, rotations, scale_
     tau = torch.zeros(6, **fopt)
     if P == 0:
         return out, tau_pg, tau
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         scratch = torch.empty(lib.gsr_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
         gc, gd = _f32(dL_dout_color, "dL_dout_color"), _f32(dL_dout_depth, "dL_dout_depth")
         args = [_f32(background, "bg"), _f32(means3D, "means3D"), _f32(sh, "sh"), _f32(colors, "colors"),
@@ -189,8 +210,8 @@ def debug_sorted_keys(geom, binning, point_list, P, R, W, H):
     lib = _abi.load()
     keys = torch.empty(max(int(R), 0), dtype=torch.int64, device=geom.device)
     if R > 0:
-        with torch.cuda.device(geom.device):
-            rc = lib.gsr_debug_sorted_keys(_stream(), geom.data_ptr(), binning.data_ptr(), point_list.data_ptr(), int(P),
+        with _on_device(geom.device):
+            rc = lib.gsr_debug_sorted_keys(_stream(), geom.data_ptr(), _ptr(binning), point_list.data_ptr(), int(P),
                                            int(R), int(W), int(H), keys.data_ptr())
             _abi.check(rc, "gsr_debug_sorted_keys")
     return keys
@@ -202,7 +223,7 @@ def mark_visible(means3D, viewmatrix, projmatrix):
     P = int(means3D.size(0))
     present = torch.zeros(P, dtype=torch.bool, device=means3D.device)
     if P != 0:
-        with torch.cuda.device(means3D.device):
+        with _on_device(means3D.device):
             rc = lib.gsr_mark_visible(_stream(), P, _f32(means3D, "means3D").data_ptr(),
                                       _f32(viewmatrix, "viewmatrix").data_ptr(),
                                       _f32(projmatrix, "projmatrix").data_ptr(), present.data_ptr())
@@ -229,7 +250,7 @@ def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotati
     if P == 0:
         return tau, m2d
     chunks = chunks or [(0, P)]
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         scratch = torch.empty(lib.gsr_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
         gc, gd = _f32(dL_dout_color, "dL_dout_color"), _f32(dL_dout_depth, "dL_dout_depth")
         bg_c, m3, sc, ro = _f32(background, "bg"), _f32(means3D, "means3D"), _f32(scales, "scales"), _f32(rotations, "rotations")

@@ -60,7 +60,7 @@ class _RenderL1(torch.autograd.Function):
         ea, eb = _scalar(exposure_a), _scalar(exposure_b)
         out = torch.empty(8, dtype=torch.float32, device=dev)
         acc = torch.empty(8, dtype=torch.float64, device=dev)
-        with torch.cuda.device(dev):
+        with _C._on_device(dev):
             rc = lib.gsr_l1_loss_forward(_C._stream(), KINDS[kind], W, H, color.data_ptr(), depth.data_ptr(),
                                          opacity.data_ptr(), _C._ptr(gt_rgb_c), _C._ptr(gt_depth_c),
                                          _C._ptr(mask_c), _C._ptr(gmask_c), _C._ptr(ea), _C._ptr(eb),
@@ -105,7 +105,7 @@ class _RenderL1(torch.autograd.Function):
                                    _C._ptr(gt_rgb_c), _C._ptr(gt_depth_c), _C._ptr(mask_c), _C._ptr(gmask_c),
                                    _C._ptr(ea), _C._ptr(eb), out.data_ptr(), up.data_ptr())
             f = lambda t, n: _C._f32(t, n)
-            with torch.cuda.device(dev):
+            with _C._on_device(dev):
                 scratch = torch.empty(lib.gsr_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
                 keep = [f(s.bg, "bg"), f(means3D, "means3D"), f(sh, "sh"), f(colors_precomp, "colors"),
                         f(scales, "scales"), f(rotations, "rotations"), f(cov3Ds_precomp, "cov3D"),

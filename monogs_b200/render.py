@@ -88,7 +88,7 @@ def camera_matrices(R: torch.Tensor, T: torch.Tensor, proj_T: torch.Tensor):
     p = proj_T.detach()
     if not p.is_contiguous():
         p = p.contiguous()
-    with torch.cuda.device(R.device):
+    with _C._on_device(R.device):
         rc = lib.gsr_camera_setup(_C._stream(), R.data_ptr(), int(R.stride(0)), int(R.stride(1)), T.data_ptr(),
                                   int(T.stride(0)), p.data_ptr(), buf.data_ptr(), buf.data_ptr() + 64,
                                   buf.data_ptr() + 128)
