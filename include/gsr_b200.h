@@ -229,6 +229,17 @@ int gsr_mark_visible(void* stream, int P, const float* means3D,
 int gsr_camera_setup(void* stream, const float* R, int r_stride_row, int r_stride_col, const float* T,
                      int t_stride, const float* proj_T, float* viewmatrix, float* projmatrix, float* campos);
 
+/* Mapper statistics of ONE keyframe, fused (utils/slam_mapper.py:452-460, gaussian_model.py:888-892): for every
+ * Gaussian with radii > 0: max_radii_2d = max(max_radii_2d, radii); xyz_gradient_accum += ||dL_dmeans2D[:, :2]||;
+ * denom += 1. max_radii_2d may be NULL; dL_dmeans2D NULL skips the gradient statistics. All arrays on the device. */
+int gsr_densify_stats(void* stream, int P, const int* radii, const float* dL_dmeans2D /*[P,3]*/,
+                      float* max_radii_2d /*[P]*/, float* xyz_gradient_accum /*[P]*/, float* denom /*[P]*/);
+/* Window observation count and prune mask (utils/slam_mapper.py:399-440): nr_obs[i] = #{k < K : n_touched[k][i] > 0};
+ * to_prune[i] = nr_obs[i] <= coviz && kf_idx[i] >= min_kf. n_touched = HOST array of K (<= 16) device pointers (the
+ * n_touched outputs of the window's renders); kf_idx device i32[P]; either output may be NULL. */
+int gsr_visibility_prune(void* stream, int P, int K, const int* const* n_touched, const int* kf_idx, int min_kf,
+                         int coviz, int* nr_obs, uint8_t* to_prune);
+
 /* mean_dist2[P] = mean squared distance to the 3 nearest other points. */
 int gsr_knn_dist2(void* stream, int P, const float* points, float* mean_dist2,
                   void* knn_ws);

@@ -48,6 +48,8 @@ SIGNATURES = {
     "gsr_debug_sorted_keys": (i32, [vp, vp, vp, vp, i32, i64, i32, i32, vp]),
     "gsr_debug_set_binning": (i32, [i32]),
     "gsr_binning_needed": (i32, [i32, i32]),
+    "gsr_densify_stats": (i32, [vp, i32, vp, vp, vp, vp, vp]),
+    "gsr_visibility_prune": (i32, [vp, i32, i32, vp, vp, i32, i32, vp, vp]),
     "gsr_camera_setup": (i32, [vp, vp, i32, i32, vp, i32, vp, vp, vp, vp]),
 }
 

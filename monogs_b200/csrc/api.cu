@@ -478,6 +478,26 @@ int gsr_camera_setup(void* stream, const float* R, int r_stride_row, int r_strid
                                    viewmatrix, projmatrix, campos));
 }
 
+int gsr_densify_stats(void* stream, int P, const int* radii, const float* dL_dmeans2D, float* max_radii_2d,
+                      float* xyz_gradient_accum, float* denom) {
+  if (P < 0) return GSR_EINVAL;
+  if (P == 0) return GSR_OK;
+  if (!radii || (dL_dmeans2D && (!xyz_gradient_accum || !denom))) return GSR_EINVAL;
+  return check(launch_densify_stats((cudaStream_t)stream, P, radii, dL_dmeans2D, max_radii_2d, xyz_gradient_accum,
+                                    denom));
+}
+
+int gsr_visibility_prune(void* stream, int P, int K, const int* const* n_touched, const int* kf_idx, int min_kf,
+                         int coviz, int* nr_obs, uint8_t* to_prune) {
+  if (P < 0 || K < 0 || K > VIS_MAX_KEYFRAMES) return GSR_EINVAL;
+  if (P == 0) return GSR_OK;
+  if ((K > 0 && !n_touched) || (to_prune && !kf_idx)) return GSR_EINVAL;
+  for (int k = 0; k < K; ++k)
+    if (!n_touched[k]) return GSR_EINVAL;
+  return check(launch_visibility_prune((cudaStream_t)stream, P, K, n_touched, kf_idx, min_kf, coviz, nr_obs,
+                                       to_prune));
+}
+
 int gsr_knn_dist2(void* stream, int P, const float* points, float* mean_dist2, void* knn_ws) {
   if (P < 0) return GSR_EINVAL;
   if (P == 0) return GSR_OK;

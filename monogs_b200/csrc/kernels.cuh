@@ -77,6 +77,13 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
                                   float* dL_dscales, float* dL_drots, float* dL_dtau_pg, float* dL_dtau,
                                   int p_begin, int p_end, float* rows, int accumulate);
 
+// stats.cu
+constexpr int VIS_MAX_KEYFRAMES = 16;  // keyframes per window the visibility kernel takes in one launch
+cudaError_t launch_densify_stats(cudaStream_t st, int P, const int* radii, const float* grad2d, float* max_radii_2d,
+                                 float* grad_accum, float* denom);
+cudaError_t launch_visibility_prune(cudaStream_t st, int P, int K, const int* const* touched, const int* kf_idx,
+                                    int min_kf, int coviz, int* nr_obs, uint8_t* to_prune);
+
 // knn.cu
 size_t knn_workspace_bytes(int P);
 cudaError_t launch_knn(cudaStream_t st, int P, const float* points, float* mean_dist2, void* ws);
