@@ -246,6 +246,29 @@ __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
 #define GSR_DEVINL __device__ __forceinline__
 
+// Lanes of the warp that hold the same value in the low NBITS bits (all 32 lanes must call). One ballot per bit:
+// constant cost, where match.any takes time proportional to the number of DISTINCT values in the warp -- high for
+// the nearly all-distinct tile ids ranked by tile_scatter.cu (-8 us there; GSR_MATCH_ANY=1 selects the match.any
+// instruction). The 8-bit digits of the onesweep passes keep match.any: ballots were 2x slower in that kernel.
+#ifndef GSR_MATCH_ANY
+#define GSR_MATCH_ANY 0
+#endif
+template <int NBITS>
+GSR_DEVINL uint32_t warp_peers(uint32_t v) {
+#if GSR_MATCH_ANY
+  return __match_any_sync(0xffffffffu, v);
+#else
+  uint32_t peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < NBITS; ++b) {
+    const bool bit = (v >> b) & 1u;
+    const uint32_t vote = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? vote : ~vote;
+  }
+  return peers;
+#endif
+}
+
 // Programmatic dependent launch: every kernel of the library lets its successor in the stream start launching at
 // once (pdl_launch_dependents) and waits for its predecessor's results (pdl_wait) before it touches global memory,
 // so launch latency, CTA scheduling and the shared-memory prologue overlap the predecessor's tail.  Every kernel

@@ -232,7 +232,7 @@ tile_offsets_kernel(int nb, int n_tiles, uint32_t* __restrict__ counts, uint32_t
 
 constexpr int TS_STAGE_WORDS = TS_PIECE + TS_PIECE / 32;
 static_assert(sizeof(TsGroup) + TS_STAGE_WORDS * 4 <= TS_GROUP_SMEM, "ts_blocks() budgets TS_GROUP_SMEM bytes");
-static_assert(TS_GROUP <= 1024 && TS_MAX_TILES <= (1 << 22), "stage word = tile << 10 | slot");
+static_assert(TS_GROUP <= 1024 && TS_MAX_TILES <= (1 << 12), "stage word = tile << 10 | slot; 13-bit peer masks");
 
 __global__ void __launch_bounds__(TS_THREADS, TS_MAX_OCC)
 tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* __restrict__ order,
@@ -352,7 +352,8 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
         for (int j = 0; j < TS_MATCH_BATCH; ++j) {
           const int i = i0 + j;
           peers[j] = 0u;
-          if (i < rounds && wbase + i * 32 < piece_n) peers[j] = __match_any_sync(0xffffffffu, tile[i]);  // uniform
+          // 13 bits: tile ids < TS_MAX_TILES = 2^12, bit 12 of the invalid marker 0xFFFFFFFF separates idle lanes
+          if (i < rounds && wbase + i * 32 < piece_n) peers[j] = warp_peers<13>(tile[i]);  // warp-uniform branch
         }
 #pragma unroll
         for (int j = 0; j < TS_MATCH_BATCH; ++j) {
