@@ -149,7 +149,8 @@ def main():
         "small": [(10_000, "tum_half", 0, False, False), (100_000, "tum", 1, False, False),
                   (50_000, "tum", 2, True, False), (60_000, "tum", 3, False, True)],
         "headline": [(1_000_000, "tum", 0, False, False)],
-        "big": [(500_000, "replica", 0, False, False), (4_000_000, "hd", 0, False, False)],
+        "big": [(500_000, "replica", 0, False, False), (4_000_000, "hd", 0, False, False),
+                (4_000_000, "tum", 1, False, False), (2_000_000, "replica", 2, True, True)],
     }
     for name in a.cases.split(","):
         for (P, kind, seed, aniso, lay) in cases[name]:
