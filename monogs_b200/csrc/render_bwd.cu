@@ -19,8 +19,28 @@
 
 namespace gsr {
 
-constexpr int RB_THREADS = 256;
-constexpr int RB_BATCH = 256;
+#ifdef GSR_CTA_TRACE
+// Debug build only (tools/time_kernels.py --trace): per-CTA start/end globaltimer and SM id.
+__device__ unsigned long long g_trace_render_bwd[3 * 32768];
+GSR_DEVINL unsigned long long trace_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+GSR_DEVINL unsigned trace_smid() { unsigned s; asm volatile("mov.u32 %0, %smid;" : "=r"(s)); return s; }
+#endif
+
+// CTA = RB_WARPS of the tile's 8 warp rectangles (see render_fwd.cu); the back-to-front walk then starts at the
+// largest n_contrib of the CTA's OWN pixels.
+#ifndef GSR_RENDER_WARPS
+#define GSR_RENDER_WARPS 8
+#endif
+#ifndef GSR_RENDER_BATCH
+#define GSR_RENDER_BATCH 256
+#endif
+constexpr int RB_WARPS = GSR_RENDER_WARPS;
+constexpr int RB_SUB = 8 / RB_WARPS;
+constexpr int RB_THREADS = 32 * RB_WARPS;
+constexpr int RB_BATCH = GSR_RENDER_BATCH;
+constexpr int RB_PER_THREAD = RB_BATCH / RB_THREADS;
+static_assert(RB_WARPS == 8 || RB_WARPS == 4 || RB_WARPS == 2, "RB_WARPS");
+static_assert(RB_BATCH % RB_THREADS == 0 && RB_BATCH % 32 == 0, "RB_BATCH");
 
 struct RbStage {
   float4 a[RB_BATCH];
@@ -97,14 +117,22 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth, LossView loss,
                   float* __restrict__ packed /*[P][GRAD_STRIDE]*/) {
   pdl_launch_dependents();
+#ifdef GSR_CTA_TRACE
+  const unsigned long long t_enter = trace_now();
+#endif
   pdl_wait();
+#ifdef GSR_CTA_TRACE
+  const unsigned long long t_start = trace_now();
+#endif
   __shared__ __align__(16) RbStage stage[2];
   __shared__ uint32_t s_max[RB_THREADS / 32];
 
-  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int tile = blockIdx.y * tiles_x + blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, wl = tid >> 5;
+  const int tile_y = blockIdx.y / RB_SUB;
+  const int w = (blockIdx.y % RB_SUB) * RB_WARPS + wl;   // warp rectangle within the tile
+  const int tile = tile_y * tiles_x + blockIdx.x;
   const int wx0 = blockIdx.x * TILE_X + (w & 1) * 8;
-  const int wy0 = blockIdx.y * TILE_Y + (w >> 1) * 4;
+  const int wy0 = tile_y * TILE_Y + (w >> 1) * 4;
   const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
   const bool inside = pxi < W && pyi < H;
   const float pixx = (float)pxi, pixy = (float)pyi;
@@ -146,7 +174,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   uint32_t wm = last_contributor;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) wm = max(wm, __shfl_xor_sync(0xffffffffu, wm, o));
-  if (lane == 0) s_max[w] = wm;
+  if (lane == 0) s_max[wl] = wm;
   __syncthreads();
   uint32_t tile_last = 0;
 #pragma unroll
@@ -161,33 +189,49 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int slot = owner_slot(lane);
 
   // batch k covers list positions pos = total-1 - (k*RB_BATCH + t), t = 0..255 (descending)
-  uint32_t id_next = 0;
+  uint32_t id_next[RB_PER_THREAD];
+#pragma unroll
+  for (int k = 0; k < RB_PER_THREAD; ++k) id_next[k] = 0;
   if (n_batches > 0) {
-    if (tid < total) {
-      const uint32_t id = point_list[range.x + (total - 1 - tid)];
-      stage[0].id[tid] = id;
-      rb_cp_async16(&stage[0].a[tid], rec_a + id);
-      rb_cp_async16(&stage[0].b[tid], rec_b + id);
-      rb_cp_async16(&stage[0].c[tid], rec_c + id);
+#pragma unroll
+    for (int k = 0; k < RB_PER_THREAD; ++k) {
+      const int t = tid + k * RB_THREADS;
+      if (t < total) {
+        const uint32_t id = point_list[range.x + (total - 1 - t)];
+        stage[0].id[t] = id;
+        rb_cp_async16(&stage[0].a[t], rec_a + id);
+        rb_cp_async16(&stage[0].b[t], rec_b + id);
+        rb_cp_async16(&stage[0].c[t], rec_c + id);
+      }
     }
     rb_commit();
-    if (RB_BATCH + tid < total) id_next = point_list[range.x + (total - 1 - RB_BATCH - tid)];
+#pragma unroll
+    for (int k = 0; k < RB_PER_THREAD; ++k) {
+      const int t = tid + k * RB_THREADS;
+      if (RB_BATCH + t < total) id_next[k] = point_list[range.x + (total - 1 - RB_BATCH - t)];
+    }
   }
 
   for (int b = 0; b < n_batches; ++b) {
     const int cur = b & 1;
     if (b + 1 < n_batches) {
-      const int e = (b + 1) * RB_BATCH + tid;
-      if (e < total) {
-        RbStage& nx = stage[cur ^ 1];
-        nx.id[tid] = id_next;
-        rb_cp_async16(&nx.a[tid], rec_a + id_next);
-        rb_cp_async16(&nx.b[tid], rec_b + id_next);
-        rb_cp_async16(&nx.c[tid], rec_c + id_next);
+      RbStage& nx = stage[cur ^ 1];
+#pragma unroll
+      for (int k = 0; k < RB_PER_THREAD; ++k) {
+        const int t = tid + k * RB_THREADS;
+        if ((b + 1) * RB_BATCH + t < total) {
+          nx.id[t] = id_next[k];
+          rb_cp_async16(&nx.a[t], rec_a + id_next[k]);
+          rb_cp_async16(&nx.b[t], rec_b + id_next[k]);
+          rb_cp_async16(&nx.c[t], rec_c + id_next[k]);
+        }
       }
       rb_commit();
-      const int e2 = (b + 2) * RB_BATCH + tid;
-      if (e2 < total) id_next = point_list[range.x + (total - 1 - e2)];
+#pragma unroll
+      for (int k = 0; k < RB_PER_THREAD; ++k) {
+        const int e2 = (b + 2) * RB_BATCH + tid + k * RB_THREADS;
+        if (e2 < total) id_next[k] = point_list[range.x + (total - 1 - e2)];
+      }
       rb_wait<1>();
     } else {
       rb_wait<0>();
@@ -268,16 +312,32 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     __syncthreads();
   }
   rb_wait<0>();
+#ifdef GSR_CTA_TRACE
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned b = blockIdx.y * gridDim.x + blockIdx.x;
+    if (b < 32768) {
+      g_trace_render_bwd[3 * b] = t_start; g_trace_render_bwd[3 * b + 1] = trace_now();
+      g_trace_render_bwd[3 * b + 2] = ((unsigned long long)(t_start - t_enter) << 32) | trace_smid();
+    }
+  }
+#endif
 }
 
 cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, const float* dL_dpix,
                               const float* dL_dpix_depth, const LossView& loss, float* packed) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
-  dim3 grid(tiles_x, tiles_y);
+  dim3 grid(tiles_x, tiles_y * RB_SUB);
   count_launch(); launch_k(render_bwd_kernel, grid, RB_THREADS, 0, st, im.ranges, point_list, W, H, tiles_x, bg, g.rec_a, g.rec_b,
                                                  g.rec_c, im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, loss, packed);
   return cudaGetLastError();
 }
 
 }  // namespace gsr
+
+#ifdef GSR_CTA_TRACE
+extern "C" int gsr_debug_cta_trace_render_bwd(unsigned long long* host_out, int n_ctas) {
+  return (int)cudaMemcpyFromSymbol(host_out, gsr::g_trace_render_bwd, sizeof(unsigned long long) * 3 * (size_t)n_ctas);
+}
+#endif

@@ -21,8 +21,29 @@
 
 namespace gsr {
 
-constexpr int RF_THREADS = 256;
-constexpr int RF_BATCH = 256;
+#ifdef GSR_CTA_TRACE
+// Debug build only (tools/time_kernels.py --trace): per-CTA start/end globaltimer and SM id.
+__device__ unsigned long long g_trace_render_fwd[3 * 32768];
+GSR_DEVINL unsigned long long trace_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+GSR_DEVINL unsigned trace_smid() { unsigned s; asm volatile("mov.u32 %0, %smid;" : "=r"(s)); return s; }
+#endif
+
+// A CTA renders RF_WARPS of the 8 warp rectangles of a tile (8: the whole 16x16 tile, 4: a 16x8 half, 2: a 16x4
+// quarter); the sub-tile index is folded into blockIdx.y.  Smaller CTAs re-stage the tile's list (cheap: ~15
+// instructions per record and thread) but shorten the tail of the launch and stop at their own pixels' saturation.
+#ifndef GSR_RENDER_WARPS
+#define GSR_RENDER_WARPS 8
+#endif
+#ifndef GSR_RENDER_BATCH
+#define GSR_RENDER_BATCH 256
+#endif
+constexpr int RF_WARPS = GSR_RENDER_WARPS;
+constexpr int RF_SUB = 8 / RF_WARPS;          // CTAs per tile
+constexpr int RF_THREADS = 32 * RF_WARPS;
+constexpr int RF_BATCH = GSR_RENDER_BATCH;
+constexpr int RF_PER_THREAD = RF_BATCH / RF_THREADS;
+static_assert(RF_WARPS == 8 || RF_WARPS == 4 || RF_WARPS == 2, "RF_WARPS");
+static_assert(RF_BATCH % RF_THREADS == 0 && RF_BATCH % 32 == 0, "RF_BATCH");
 
 struct RfStage {
   float4 a[RF_BATCH];
@@ -46,14 +67,22 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_depth,
                   float* __restrict__ out_opacity, int* __restrict__ n_touched) {
   pdl_launch_dependents();
+#ifdef GSR_CTA_TRACE
+  const unsigned long long t_enter = trace_now();
+#endif
   pdl_wait();
+#ifdef GSR_CTA_TRACE
+  const unsigned long long t_start = trace_now();
+#endif
   __shared__ __align__(16) RfStage stage[2];
 
-  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int tile = blockIdx.y * tiles_x + blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int tile_y = blockIdx.y / RF_SUB;
+  const int w = (blockIdx.y % RF_SUB) * RF_WARPS + (tid >> 5);   // warp rectangle within the tile
+  const int tile = tile_y * tiles_x + blockIdx.x;
   // warp sub-rectangle: 2 columns x 4 rows of 8x4-pixel rectangles
   const int wx0 = blockIdx.x * TILE_X + (w & 1) * 8;
-  const int wy0 = blockIdx.y * TILE_Y + (w >> 1) * 4;
+  const int wy0 = tile_y * TILE_Y + (w >> 1) * 4;
   const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
   const bool inside = pxi < W && pyi < H;
   const float pixx = (float)pxi, pixy = (float)pyi;
@@ -68,34 +97,50 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   bool done = !inside;
 
   // prologue: gather batch 0, prefetch the ids of batch 1
-  uint32_t id_next = 0;
+  uint32_t id_next[RF_PER_THREAD];
+#pragma unroll
+  for (int k = 0; k < RF_PER_THREAD; ++k) id_next[k] = 0;
   if (n_batches > 0) {
-    if (tid < total) {
-      const uint32_t id = point_list[range.x + tid];
-      stage[0].id[tid] = id;
-      cp_async16(&stage[0].a[tid], rec_a + id);
-      cp_async16(&stage[0].b[tid], rec_b + id);
-      cp_async16(&stage[0].c[tid], rec_c + id);
+#pragma unroll
+    for (int k = 0; k < RF_PER_THREAD; ++k) {
+      const int t = tid + k * RF_THREADS;
+      if (t < total) {
+        const uint32_t id = point_list[range.x + t];
+        stage[0].id[t] = id;
+        cp_async16(&stage[0].a[t], rec_a + id);
+        cp_async16(&stage[0].b[t], rec_b + id);
+        cp_async16(&stage[0].c[t], rec_c + id);
+      }
     }
     cp_async_commit();
-    if (RF_BATCH + tid < total) id_next = point_list[range.x + RF_BATCH + tid];
+#pragma unroll
+    for (int k = 0; k < RF_PER_THREAD; ++k) {
+      const int t = tid + k * RF_THREADS;
+      if (RF_BATCH + t < total) id_next[k] = point_list[range.x + RF_BATCH + t];
+    }
   }
 
   for (int b = 0; b < n_batches; ++b) {
     const int cur = b & 1;
     // issue the gather of batch b+1 into the other buffer (free since the barrier ending batch b-1)
     if (b + 1 < n_batches) {
-      const int e = (b + 1) * RF_BATCH + tid;
-      if (e < total) {
-        RfStage& nx = stage[cur ^ 1];
-        nx.id[tid] = id_next;
-        cp_async16(&nx.a[tid], rec_a + id_next);
-        cp_async16(&nx.b[tid], rec_b + id_next);
-        cp_async16(&nx.c[tid], rec_c + id_next);
+      RfStage& nx = stage[cur ^ 1];
+#pragma unroll
+      for (int k = 0; k < RF_PER_THREAD; ++k) {
+        const int t = tid + k * RF_THREADS;
+        if ((b + 1) * RF_BATCH + t < total) {
+          nx.id[t] = id_next[k];
+          cp_async16(&nx.a[t], rec_a + id_next[k]);
+          cp_async16(&nx.b[t], rec_b + id_next[k]);
+          cp_async16(&nx.c[t], rec_c + id_next[k]);
+        }
       }
       cp_async_commit();
-      const int e2 = (b + 2) * RF_BATCH + tid;
-      if (e2 < total) id_next = point_list[range.x + e2];
+#pragma unroll
+      for (int k = 0; k < RF_PER_THREAD; ++k) {
+        const int e2 = (b + 2) * RF_BATCH + tid + k * RF_THREADS;
+        if (e2 < total) id_next[k] = point_list[range.x + e2];
+      }
       cp_async_wait<1>();
     } else {
       cp_async_wait<0>();
@@ -159,13 +204,23 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     out_depth[pix] = D;
     out_opacity[pix] = fsub(1.0f, T);
   }
+#ifdef GSR_CTA_TRACE
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned b = blockIdx.y * gridDim.x + blockIdx.x;
+    if (b < 32768) {
+      g_trace_render_fwd[3 * b] = t_start; g_trace_render_fwd[3 * b + 1] = trace_now();
+      g_trace_render_fwd[3 * b + 2] = ((unsigned long long)(t_start - t_enter) << 32) | trace_smid();
+    }
+  }
+#endif
 }
 
 cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, float* out_color, float* out_depth,
                               float* out_opacity, int* n_touched) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
-  dim3 grid(tiles_x, tiles_y);
+  dim3 grid(tiles_x, tiles_y * RF_SUB);
   count_launch(); launch_k(render_fwd_kernel, grid, RF_THREADS, 0, st, im.ranges, point_list, W, H, tiles_x, g.rec_a, g.rec_b, g.rec_c,
                                                  bg, im.final_T, im.n_contrib, out_color, out_depth, out_opacity,
                                                  n_touched);
@@ -173,3 +228,9 @@ cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& i
 }
 
 }  // namespace gsr
+
+#ifdef GSR_CTA_TRACE
+extern "C" int gsr_debug_cta_trace_render_fwd(unsigned long long* host_out, int n_ctas) {
+  return (int)cudaMemcpyFromSymbol(host_out, gsr::g_trace_render_fwd, sizeof(unsigned long long) * 3 * (size_t)n_ctas);
+}
+#endif

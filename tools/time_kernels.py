@@ -53,3 +53,27 @@ def bwd():
         tau.data_ptr(), 0)
     assert rc == 0, rc
 print("backward_us", round(timeit(bwd, a.iters), 1))
+
+# --- per-CTA timeline of the render kernels (library variant built with -DGSR_CTA_TRACE) --------------------
+if hasattr(lib, "gsr_debug_cta_trace_render_bwd") or "--trace" in sys.argv:
+    import numpy as np
+    raw = C.CDLL(str(_abi._LIB_PATH))
+    sub = int(__import__("os").environ.get("TRACE_SUB", "1"))
+    n_cta = ((W + 15) // 16) * ((H + 15) // 16) * sub
+    for name, fn in (("render_fwd", render), ("render_bwd", bwd)):
+        torch.cuda.synchronize(); fn(); torch.cuda.synchronize()
+        buf = np.zeros(3 * n_cta, dtype=np.uint64)
+        rc = getattr(raw, "gsr_debug_cta_trace_" + name)(buf.ctypes.data_as(C.c_void_p), n_cta); assert rc == 0, rc
+        t0, t1, x = buf[0::3].astype(np.int64), buf[1::3].astype(np.int64), buf[2::3]
+        smid = (x & np.uint64(0xffffffff)).astype(np.int64); waited = (x >> np.uint64(32)).astype(np.int64)
+        base = t0.min(); span = t1.max() - base; dur = t1 - t0
+        print(f"[{name}] ctas {n_cta} span_us {span/1e3:.1f} cta_dur_us mean {dur.mean()/1e3:.2f} p50 {np.median(dur)/1e3:.2f} "
+              f"p90 {np.percentile(dur,90)/1e3:.2f} max {dur.max()/1e3:.2f} pdl_wait_us mean {waited.mean()/1e3:.2f} max {waited.max()/1e3:.2f}")
+        # concurrency over time in 20 slices
+        edges = np.linspace(0, span, 21)
+        conc = [(np.minimum(t1 - base, e1) - np.maximum(t0 - base, e0)).clip(0).sum() / max(e1 - e0, 1) for e0, e1 in zip(edges[:-1], edges[1:])]
+        print(f"[{name}] resident CTAs per 5% slice:", " ".join(f"{c:.0f}" for c in conc))
+        busy = np.zeros(smid.max() + 1)
+        np.add.at(busy, smid, dur)
+        print(f"[{name}] per-SM sum of CTA time / span: min {busy.min()/span:.2f} mean {busy.mean()/span:.2f} max {busy.max()/span:.2f}; "
+              f"last start at {100*(t0.max()-base)/span:.0f}% of span; first end at {100*(t1.min()-base)/span:.0f}%")
