@@ -254,11 +254,13 @@ class OursDeviceStep:
         assert rc == 0, rc
         works = []
         for (p0, p1) in self.chunks:
-            rc = lib.gsr_backward_rows(st, P, p0, p1, W, H, sc["means3D"].data_ptr(), sc["scales"].data_ptr(), 1.0,
-                                       sc["rotations"].data_ptr(), wl.view.data_ptr(), wl.proj.data_ptr(),
-                                       wl.proj_raw.data_ptr(), wl.cam.tanfovx, wl.cam.tanfovy, self.radii.data_ptr(),
-                                       self.geom.data_ptr(), self.scratch.data_ptr(), self.rows.data_ptr(), 0,
-                                       self.means2D.data_ptr(), self.tau.data_ptr(), 0)
+            mk = self.exchange.marks or (None, None)
+            rc = lib.gsr_backward_rows_marked(st, P, p0, p1, W, H, sc["means3D"].data_ptr(),
+                                              sc["scales"].data_ptr(), 1.0, sc["rotations"].data_ptr(),
+                                              wl.view.data_ptr(), wl.proj.data_ptr(), wl.proj_raw.data_ptr(),
+                                              wl.cam.tanfovx, wl.cam.tanfovy, self.radii.data_ptr(),
+                                              self.geom.data_ptr(), self.scratch.data_ptr(), self.rows.data_ptr(), 0,
+                                              self.means2D.data_ptr(), self.tau.data_ptr(), mk[0], mk[1], 0)
             assert rc == 0, rc
             w = self.exchange.reduce(self.rows, p0, p1)
             if w is not None:
@@ -674,6 +676,8 @@ def main():
     }
     if e2e_fused:
         line["e2e_fused_loss"] = e2e_fused
+    if world > 1 and getattr(stepper, "exchange", None) is not None:
+        line["exchange"] = dict(getattr(stepper.exchange, "report", {}), mode=stepper.exchange.mode)
     if impl == "reference":
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": value, "unit": "it/s", "cores": 0, "kind": "reference",

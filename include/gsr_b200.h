@@ -214,6 +214,35 @@ int gsr_backward_rows(void* stream, int P, int p_begin, int p_end, int width, in
                       const void* geom_ws, void* scratch, float* rows, int accumulate,
                       float* dL_dmeans2D, float* dL_dtau, int debug);
 
+/* ---- sparse in-switch exchange of the window rows (csrc/rows_exchange.cu; no reference counterpart) ---------
+ * One symmetric buffer per rank (same size and layout on every rank, mapped for peer access AND bound to an
+ * NVLS multicast object by the caller, e.g. torch.distributed._symmetric_memory), zero-filled once:
+ *   [ rows f32[P][16] | touched bitmaps u32[world][words_per_rank] | visibility counts u8[world][vis_bytes_per_rank]
+ *     | barrier flags ]                       (offsets: gsr_rows_exchange_layout; size: gsr_rows_exchange_bytes)
+ * gsr_backward_rows_marked = gsr_backward_rows that also writes (ORs / adds when accumulate != 0) this rank's
+ *   marks into slot [rank] of its own buffer: touched_words = local + offsets[1] + 4*rank*words_per_rank (bit i of
+ *   word i/32 = row i is non-zero here), vis_u8 = local + offsets[2] + rank*vis_bytes_per_rank (keyframes of this
+ *   rank that see Gaussian i). Both NULL = plain gsr_backward_rows.
+ * gsr_rows_exchange: ONE kernel, enqueued on every rank with the same P / world / n_ctas / epoch: rows that are
+ *   non-zero on some rank are summed in the NVSwitch (multimem.ld_reduce) and multicast back (multimem.st); all
+ *   other rows are left alone (zero gradients everywhere). vis_count[P] (local, optional) = sum over the ranks of
+ *   the visibility counts; column 15 of the rows is not meaningful afterwards. peer_bufs = DEVICE array of
+ *   world pointers to every rank's buffer in this process's address space (peer_bufs[rank] == local_buf);
+ *   multicast_buf = the multicast address of the same buffer. epoch must advance by 2 per call, starting at 1,
+ *   identically on all ranks. *status (device int, optional) is set to 1 if a peer did not arrive within 20 s
+ *   (the kernel then returns instead of hanging). n_ctas <= 256, at most one CTA per SM (they spin on peers). */
+size_t gsr_rows_exchange_bytes(int P, int world);
+int gsr_rows_exchange_layout(int P, int world, size_t* offsets /*[4]: rows, bitmaps, visibility, flags*/,
+                             int* words_per_rank, int* vis_bytes_per_rank);
+int gsr_backward_rows_marked(void* stream, int P, int p_begin, int p_end, int width, int height,
+                             const float* means3D, const float* scales, float scale_modifier,
+                             const float* rotations, const float* viewmatrix, const float* projmatrix,
+                             const float* projmatrix_raw, float tan_fovx, float tan_fovy, const int* radii,
+                             const void* geom_ws, void* scratch, float* rows, int accumulate, float* dL_dmeans2D,
+                             float* dL_dtau, uint32_t* touched_words, uint8_t* vis_u8, int debug);
+int gsr_rows_exchange(void* stream, int P, int rank, int world, int n_ctas, void* local_buf, void* multicast_buf,
+                      const uint64_t* peer_bufs, uint32_t epoch, float* vis_count, int* status);
+
 /* present[P] (uint8 0/1) = p_view.z > 0.2  (auxiliary.h:139-164). */
 int gsr_mark_visible(void* stream, int P, const float* means3D,
                      const float* viewmatrix, const float* projmatrix,

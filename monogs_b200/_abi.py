@@ -37,6 +37,11 @@ SIGNATURES = {
     "gsr_backward_render": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, i64, vp, vp, vp, i32]),
     "gsr_backward_rows": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, f32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, i32,
                                 vp, vp, i32]),
+    "gsr_backward_rows_marked": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, f32, vp, vp, vp, vp, f32, f32, vp, vp, vp,
+                                       vp, i32, vp, vp, vp, vp, i32]),
+    "gsr_rows_exchange_bytes": (C.c_size_t, [i32, i32]),
+    "gsr_rows_exchange_layout": (i32, [i32, i32, C.POINTER(C.c_size_t), C.POINTER(i32), C.POINTER(i32)]),
+    "gsr_rows_exchange": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, C.c_uint32, vp, vp]),
     "gsr_mark_visible": (i32, [vp, i32, vp, vp, vp, vp]),
     "gsr_knn_dist2": (i32, [vp, i32, vp, vp, vp]),
     "gsr_profile_enable": (i32, [i32]),

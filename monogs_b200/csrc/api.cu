@@ -440,6 +440,42 @@ int gsr_backward_rows(void* stream, int P, int p_begin, int p_end, int width, in
                       const float* projmatrix, const float* projmatrix_raw, float tan_fovx, float tan_fovy,
                       const int* radii, const void* geom_ws, void* scratch, float* rows, int accumulate,
                       float* dL_dmeans2D, float* dL_dtau, int debug) {
+  return gsr_backward_rows_marked(stream, P, p_begin, p_end, width, height, means3D, scales, scale_modifier,
+                                  rotations, viewmatrix, projmatrix, projmatrix_raw, tan_fovx, tan_fovy, radii,
+                                  geom_ws, scratch, rows, accumulate, dL_dmeans2D, dL_dtau, nullptr, nullptr, debug);
+}
+
+size_t gsr_rows_exchange_bytes(int P, int world) {
+  if (P < 0 || world < 1 || world > XCHG_MAX_WORLD) return 0;
+  return xchg_layout(P, world).total;
+}
+
+int gsr_rows_exchange_layout(int P, int world, size_t* offsets, int* words_per_rank, int* vis_bytes_per_rank) {
+  if (P < 0 || world < 1 || world > XCHG_MAX_WORLD || !offsets) return GSR_EINVAL;
+  const XchgLayout L = xchg_layout(P, world);
+  offsets[0] = L.rows; offsets[1] = L.bitmap; offsets[2] = L.vis; offsets[3] = L.flags;
+  if (words_per_rank) *words_per_rank = L.words_pad;
+  if (vis_bytes_per_rank) *vis_bytes_per_rank = L.p_pad;
+  return GSR_OK;
+}
+
+int gsr_rows_exchange(void* stream, int P, int rank, int world, int n_ctas, void* local_buf, void* multicast_buf,
+                      const uint64_t* peer_bufs, uint32_t epoch, float* vis_count, int* status) {
+  if (P < 0 || world < 1 || world > XCHG_MAX_WORLD || rank < 0 || rank >= world) return GSR_EINVAL;
+  if (n_ctas < 1 || n_ctas > XCHG_MAX_CTAS || !local_buf || !multicast_buf || !peer_bufs) return GSR_EINVAL;
+  if (P == 0) return GSR_OK;
+  return check(launch_rows_exchange((cudaStream_t)stream, P, rank, world, n_ctas, local_buf, multicast_buf,
+                                    reinterpret_cast<const unsigned long long*>(peer_bufs), epoch, vis_count,
+                                    status));
+}
+
+int gsr_backward_rows_marked(void* stream, int P, int p_begin, int p_end, int width, int height,
+                             const float* means3D, const float* scales, float scale_modifier,
+                             const float* rotations, const float* viewmatrix, const float* projmatrix,
+                             const float* projmatrix_raw, float tan_fovx, float tan_fovy, const int* radii,
+                             const void* geom_ws, void* scratch, float* rows, int accumulate, float* dL_dmeans2D,
+                             float* dL_dtau, uint32_t* touched_words, uint8_t* vis_u8, int debug) {
+  if ((touched_words == nullptr) != (vis_u8 == nullptr)) return GSR_EINVAL;
   if (P < 0 || width <= 0 || height <= 0 || p_begin < 0 || p_end < p_begin || p_end > P) return GSR_EINVAL;
   if (p_begin % 256 != 0) return GSR_EINVAL;  // ranges start on a 256-Gaussian boundary (tau block partials)
   cudaStream_t st = (cudaStream_t)stream;
@@ -458,7 +494,8 @@ int gsr_backward_rows(void* stream, int P, int p_begin, int p_end, int width, in
   GSR_TRY(check(launch_preprocess_bwd(st, P, 0, 0, means3D, radii, nullptr, g.clamped, scales, rotations,
                                       scale_modifier, nullptr, viewmatrix, projmatrix, projmatrix_raw, nullptr, width,
                                       height, tan_fovx, tan_fovy, bw, dL_dmeans2D, nullptr, nullptr, nullptr, nullptr,
-                                      nullptr, nullptr, nullptr, nullptr, dL_dtau, p_begin, p_end, rows, accumulate)));
+                                      nullptr, nullptr, nullptr, nullptr, dL_dtau, p_begin, p_end, rows, accumulate,
+                                      touched_words, vis_u8)));
   return debug_sync(st, debug);
 }
 

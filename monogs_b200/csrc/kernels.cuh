@@ -75,7 +75,22 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
                                   const BackwardViews& bw, float* dL_dmeans2D, float* dL_dcolors,
                                   float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
                                   float* dL_dscales, float* dL_drots, float* dL_dtau_pg, float* dL_dtau,
-                                  int p_begin, int p_end, float* rows, int accumulate);
+                                  int p_begin, int p_end, float* rows, int accumulate,
+                                  uint32_t* touched_words = nullptr, uint8_t* vis_u8 = nullptr);
+
+// rows_exchange.cu  (sparse in-switch exchange of the mapping-window rows)
+struct XchgLayout {
+  size_t rows, bitmap, vis, flags, total;  // byte offsets into the symmetric buffer, and its size
+  int n_gran;                              // 128-Gaussian granules = ceil(P / 128)
+  int words_pad;                           // bitmap words per rank (4 per granule)
+  int p_pad;                               // visibility bytes per rank (128 per granule)
+};
+constexpr int XCHG_MAX_CTAS = 256;
+constexpr int XCHG_MAX_WORLD = 32;
+XchgLayout xchg_layout(int P, int world);
+cudaError_t launch_rows_exchange(cudaStream_t st, int P, int rank, int world, int n_ctas, void* local_buf,
+                                 void* multicast_buf, const unsigned long long* peer_bufs, uint32_t epoch,
+                                 float* vis_count, int* status);
 
 // stats.cu
 constexpr int VIS_MAX_KEYFRAMES = 16;  // keyframes per window the visibility kernel takes in one launch

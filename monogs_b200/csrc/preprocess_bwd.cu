@@ -142,7 +142,9 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
                       float* __restrict__ dL_dscales, float* __restrict__ dL_drots,
                       float* __restrict__ dL_dtau_pg, double* __restrict__ tau_partial, int p_begin,
-                      float* __restrict__ rows /*[P,16] window rows or NULL*/, int accumulate) {
+                      float* __restrict__ rows /*[P,16] window rows or NULL*/, int accumulate,
+                      uint32_t* __restrict__ touched_words /*sparse exchange marks or NULL*/,
+                      uint8_t* __restrict__ vis_u8) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float s_cam[40];
@@ -393,6 +395,19 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       r4[0] = o0; r4[1] = o1; r4[2] = o2; r4[3] = o3;
     }
   }
+  if (touched_words) {
+    // marks for the sparse window exchange (rows_exchange.cu): bit i of word idx/32 = this rank holds a non-zero
+    // gradient row for Gaussian idx (every output above is linear in the ten packed partials, so an all-zero record
+    // gives an all-zero row); vis_u8 = number of this rank's keyframes that see the Gaussian.
+    const bool t = visible && (pk0.x != 0.f || pk0.y != 0.f || pk0.z != 0.f || pk0.w != 0.f || pk1.x != 0.f ||
+                               pk1.y != 0.f || pk1.z != 0.f || pk1.w != 0.f || pk2.x != 0.f || pk2.y != 0.f);
+    const unsigned bal = __ballot_sync(0xffffffffu, t);
+    if ((tid & 31) == 0 && in_range) {
+      uint32_t* wp = touched_words + (idx >> 5);
+      *wp = accumulate ? (*wp | bal) : bal;
+    }
+    if (in_range) vis_u8[idx] = (uint8_t)((accumulate ? vis_u8[idx] : 0) + (visible ? 1 : 0));
+  }
 #pragma unroll
   for (int k = 0; k < 6; ++k) tacc[k] += (double)tau[k];
   }  // chunk loop
@@ -452,7 +467,8 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
                                   const BackwardViews& bw, float* dL_dmeans2D, float* dL_dcolors,
                                   float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
                                   float* dL_dscales, float* dL_drots, float* dL_dtau_pg, float* dL_dtau,
-                                  int p_begin, int p_end, float* rows, int accumulate) {
+                                  int p_begin, int p_end, float* rows, int accumulate, uint32_t* touched_words,
+                                  uint8_t* vis_u8) {
   const float focal_y = H / (2.0f * tan_fovy);
   const float focal_x = W / (2.0f * tan_fovx);
   // p_begin is a multiple of 256 (checked by the caller); persistent grid of 148 SMs x PB_BLOCKS_PER_SM CTAs. Partial slot of CTA b
@@ -466,7 +482,7 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
                                                      projmatrix_raw, campos, focal_x, focal_y, tan_fovx, tan_fovy,
                                                      bw.packed, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D,
                                                      dL_dcov3D, dL_dsh, dL_dscales, dL_drots, dL_dtau_pg,
-                                                     bw.tau_partial, p_begin, rows, accumulate);
+                                                     bw.tau_partial, p_begin, rows, accumulate, touched_words, vis_u8);
   }
   // the pose gradient is complete once the LAST range has run (ranges are issued in ascending order)
   if (dL_dtau && p_end == P) {

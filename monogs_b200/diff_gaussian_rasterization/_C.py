@@ -234,11 +234,12 @@ def mark_visible(means3D, viewmatrix, projmatrix):
 def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotations, scale_modifier, viewmatrix,
                                       projmatrix, projmatrix_raw, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth,
                                       geomBuffer, R, point_list, imageBuffer, rows, accumulate, chunks=None,
-                                      chunk_done=None, want_means2D=False, debug=False):
+                                      chunk_done=None, want_means2D=False, debug=False, marks=None):
     """Backward of one keyframe of the sharded mapping window (gsr_backward_render + gsr_backward_rows): the
     Gaussian gradients are written / added into `rows` f32[P,16] (layout: include/gsr_b200.h) range by range;
     `chunk_done(p0, p1)` is called right after each range has been enqueued (the caller starts its allreduce of
-    rows[p0:p1] there). Returns (dL_dtau[6], dL_dmeans2D[P,3] or None)."""
+    rows[p0:p1] there). `marks` = (touched_words_ptr, vis_u8_ptr): this rank's slot of the sparse window exchange
+    (gsr_backward_rows_marked, monogs_b200.window.RowExchange.marks). Returns (dL_dtau[6], dL_dmeans2D[P,3] or None)."""
     lib = _abi.load()
     P = int(means3D.size(0))
     dev = means3D.device
@@ -261,11 +262,14 @@ def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotati
                                      _ptr(point_list), int(R), _ptr(gc), _ptr(gd), scratch.data_ptr(), int(bool(debug)))
         _abi.check(rc, "gsr_backward_render")
         for (p0, p1) in chunks:
-            rc = lib.gsr_backward_rows(st, P, int(p0), int(p1), W, H, _ptr(m3), _ptr(sc), float(scale_modifier),
-                                       _ptr(ro), _ptr(vm), _ptr(pm), _ptr(pr), float(tan_fovx), float(tan_fovy),
-                                       radii_c.data_ptr(), geomBuffer.data_ptr(), scratch.data_ptr(), rows.data_ptr(),
-                                       int(bool(accumulate)), _ptr(m2d), tau.data_ptr(), int(bool(debug)))
-            _abi.check(rc, "gsr_backward_rows")
+            rc = lib.gsr_backward_rows_marked(st, P, int(p0), int(p1), W, H, _ptr(m3), _ptr(sc),
+                                              float(scale_modifier), _ptr(ro), _ptr(vm), _ptr(pm), _ptr(pr),
+                                              float(tan_fovx), float(tan_fovy), radii_c.data_ptr(),
+                                              geomBuffer.data_ptr(), scratch.data_ptr(), rows.data_ptr(),
+                                              int(bool(accumulate)), _ptr(m2d), tau.data_ptr(),
+                                              marks[0] if marks else None, marks[1] if marks else None,
+                                              int(bool(debug)))
+            _abi.check(rc, "gsr_backward_rows_marked")
             if chunk_done is not None:
                 chunk_done(p0, p1)
     return tau, m2d

@@ -17,6 +17,7 @@ host logic is testable on CPU with world_size 2 / gloo; the product default is t
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass, field
 from typing import Callable, Dict, List, Optional, Sequence
 
@@ -89,67 +90,187 @@ RenderFn = Callable[..., KeyframeResult]
 class RowExchange:
     """The one exchange step: sum of the [P,16] window rows over the ranks.
 
-    On NVSwitch boxes the rows live in symmetric memory and are reduced IN THE SWITCH (NVLS multimem
-    ld_reduce / st through torch.distributed._symmetric_memory): measured on 8 x B200 at 64 MB: 0.172 ms vs
-    0.278 ms for ncclAllReduce (gpurun_out/nccl_probe2_n8.json, profiles/r01_nccl_probe_n8.json). Elsewhere
-    (gloo on CPU, no multicast support) it is a plain all_reduce. Splitting the rows into ranges to overlap the
-    allreduce with the per-Gaussian backward was measured and rejected: 4 pieces cost 0.47 ms (latency-bound
-    collectives) against 0.064 ms of overlappable compute -- so the default is ONE range."""
+    On NVSwitch boxes the rows live in symmetric memory (torch.distributed._symmetric_memory supplies the peer
+    mappings and the NVLS multicast address; nothing else) and three exchanges are available:
+      * "sparse"     OUR kernel (csrc/rows_exchange.cu, gsr_rows_exchange): only rows that are non-zero on some rank
+                     are summed in the switch (multimem.ld_reduce) and multicast back, found through per-rank bitmaps
+                     the per-Gaussian backward writes (gsr_backward_rows_marked); visibility counts travel as bytes;
+      * "multimem"   torch's dense in-switch allreduce of the whole buffer (0.172 ms for 64 MB at 8 GPUs);
+      * "all_reduce" ncclAllReduce (0.278 ms; the only mode on CPU / gloo and without multicast support).
+    The first real exchange times all available modes ON THE REAL ROWS (rows and marks are restored between trials),
+    checks the sparse result against the dense one, and keeps the fastest; the decision is made identical on every
+    rank with a MAX-allreduce of the timings. Splitting the rows into ranges to overlap the allreduce with the
+    per-Gaussian backward was measured and rejected (4 pieces 0.47 ms, latency-bound)."""
 
     def __init__(self, group=None):
         self.group = group
         self.mode = "all_reduce"
+        self.candidates = ["all_reduce"]
+        self.decided = True
+        self.report = {}
+        self.marks = None          # (touched_words_ptr, vis_u8_ptr) of this rank's slot, or None
+        self.vis = None            # f32[P] visibility sum of the sparse mode
         self._name = None
+        self._buf = None
+        self._P = 0
 
+    # -- allocation ------------------------------------------------------------------------------------------
     def allocate(self, P: int, device) -> torch.Tensor:
         device = torch.device(device)
         world = dist.get_world_size(self.group) if dist.is_initialized() else 1
-        if device.type == "cuda" and world > 1:
+        self._P = P
+        if device.type == "cuda" and world > 1 and os.environ.get("GSR_XCHG", "auto") != "nccl":
             try:
-                import torch.distributed._symmetric_memory as symm_mem
-                grp = self.group if self.group is not None else dist.group.WORLD
-                t = symm_mem.empty(P * N_COLS, dtype=torch.float32, device=device)
-                hdl = symm_mem.rendezvous(t, grp.group_name)
-                if getattr(hdl, "multicast_ptr", 0) and hasattr(torch.ops.symm_mem, "multimem_all_reduce_"):
-                    self._name = grp.group_name
-                    flat = t.view(P, N_COLS)
-                    self.mode = self._pick(flat)
+                flat = self._allocate_symmetric(P, device, world)
+                if flat is not None:
                     return flat
-            except Exception:  # no symmetric memory / multicast on this system: NCCL ring/tree instead
-                pass
+            except Exception as e:  # no symmetric memory / multicast on this system: NCCL ring/tree instead
+                self.report["symmetric_memory_error"] = repr(e)[:200]
         return torch.empty(P, N_COLS, dtype=torch.float32, device=device)
 
-    def _pick(self, flat: torch.Tensor) -> str:
-        """Time both exchanges once on the real buffer and keep the faster (the in-switch reduction wins at 8 GPUs,
-        ncclAllReduce at 2); the decision is made identical on every rank with a MAX-allreduce of the timings."""
-        flat.zero_()
-        times = []
-        for mode in ("multimem", "all_reduce"):
-            self.mode = mode
-            for _ in range(2):
-                w = self.reduce(flat, 0, flat.shape[0])
-                if w is not None:
-                    w.wait()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            torch.cuda.synchronize(flat.device)
-            a.record()
-            for _ in range(3):
-                w = self.reduce(flat, 0, flat.shape[0])
-                if w is not None:
-                    w.wait()
-            b.record()
-            torch.cuda.synchronize(flat.device)
-            times.append(a.elapsed_time(b))
-        t = torch.tensor(times, dtype=torch.float64, device=flat.device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
-        return "multimem" if float(t[0]) < float(t[1]) else "all_reduce"
+    def _allocate_symmetric(self, P, device, world):
+        import ctypes as C
+        import torch.distributed._symmetric_memory as symm_mem
+        from . import _abi
+        lib = _abi.load()
+        grp = self.group if self.group is not None else dist.group.WORLD
+        total = int(lib.gsr_rows_exchange_bytes(P, world))
+        if total == 0:
+            return None
+        t = symm_mem.empty(total // 4, dtype=torch.float32, device=device)
+        hdl = symm_mem.rendezvous(t, grp.group_name)
+        if not getattr(hdl, "multicast_ptr", 0):
+            return None
+        t.zero_()
+        torch.cuda.synchronize(device)
+        hdl.barrier()
+        torch.cuda.synchronize(device)
+        offs = (C.c_size_t * 4)()
+        wpr, vpr = C.c_int(0), C.c_int(0)
+        _abi.check(lib.gsr_rows_exchange_layout(P, world, offs, C.byref(wpr), C.byref(vpr)), "gsr_rows_exchange_layout")
+        rank = dist.get_rank(self.group)
+        self._lib, self._hdl, self._buf, self._name = lib, hdl, t, grp.group_name
+        self._rank, self._world = rank, world
+        self._offs, self._wpr, self._vpr = [int(o) for o in offs], int(wpr.value), int(vpr.value)
+        base_off = int(getattr(hdl, "offset", 0) or 0)
+        self._local_ptr = t.data_ptr()
+        self._mc_ptr = int(hdl.multicast_ptr) + base_off
+        # device array of the peers' buffer addresses (+ this allocation's offset inside the symmetric block)
+        self._peers = torch.tensor([int(p) + base_off for p in hdl.buffer_ptrs], dtype=torch.int64, device=device)
+        self.marks = (self._local_ptr + self._offs[1] + 4 * rank * self._wpr,
+                      self._local_ptr + self._offs[2] + rank * self._vpr)
+        self.vis = torch.zeros(P, dtype=torch.float32, device=device)
+        self._status = torch.zeros(1, dtype=torch.int32, device=device)
+        self._epoch = 1
+        sms = torch.cuda.get_device_properties(device).multi_processor_count
+        self._ctas = max(1, min(int(os.environ.get("GSR_XCHG_CTAS", "148")), sms, 256))
+        forced = os.environ.get("GSR_XCHG", "auto")
+        self.candidates = []
+        if forced in ("auto", "sparse"):
+            self.candidates.append("sparse")
+        if forced in ("auto", "multimem") and hasattr(torch.ops.symm_mem, "multimem_all_reduce_"):
+            self.candidates.append("multimem")
+        if forced in ("auto", "all_reduce") or not self.candidates:
+            self.candidates.append("all_reduce")
+        self.mode, self.decided = self.candidates[0], len(self.candidates) == 1
+        return t[:P * N_COLS].view(P, N_COLS)
 
-    def reduce(self, flat: torch.Tensor, p0: int, p1: int):
-        """Start the sum of rows [p0, p1); returns a handle with .wait() or None when already stream-ordered."""
-        if self.mode == "multimem":
+    def zero_marks(self):
+        """A rank without keyframes contributes no rows: clear its bitmap / visibility slot."""
+        if self._buf is not None:
+            b = self._buf.view(torch.uint8)
+            o1 = self._offs[1] + 4 * self._rank * self._wpr
+            o2 = self._offs[2] + self._rank * self._vpr
+            b[o1:o1 + 4 * self._wpr].zero_()
+            b[o2:o2 + self._vpr].zero_()
+
+    def vis_count(self, flat: torch.Tensor) -> torch.Tensor:
+        """Number of keyframes (over all ranks) in which each Gaussian is visible, after the exchange."""
+        return self.vis if self.mode == "sparse" else flat[:, N_COLS - 1]
+
+    # -- the exchange ----------------------------------------------------------------------------------------
+    def _run(self, mode, flat, p0, p1):
+        if mode == "sparse":
+            if p1 < self._P:
+                return None  # ranges: the sparse kernel runs once, when the last range is in place
+            rc = self._lib.gsr_rows_exchange(torch.cuda.current_stream(flat.device).cuda_stream, self._P, self._rank,
+                                             self._world, self._ctas, self._local_ptr, self._mc_ptr,
+                                             self._peers.data_ptr(), self._epoch, self.vis.data_ptr(),
+                                             self._status.data_ptr())
+            self._epoch = (self._epoch + 2) & 0xFFFFFFFF
+            if rc != 0:
+                raise RuntimeError(f"gsr_rows_exchange failed: {rc}")
+            return None
+        if mode == "multimem":
             torch.ops.symm_mem.multimem_all_reduce_(flat.view(-1)[p0 * N_COLS:p1 * N_COLS], "sum", self._name)
             return None
         return dist.all_reduce(flat[p0:p1], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+
+    def _decide(self, flat: torch.Tensor):
+        """First real exchange: time every candidate on the real rows, verify the sparse result, keep the fastest."""
+        P, dev = self._P, flat.device
+        b = self._buf.view(torch.uint8)
+        regions = [(0, 4 * P * N_COLS), (self._offs[1] + 4 * self._rank * self._wpr, 4 * self._wpr),
+                   (self._offs[2] + self._rank * self._vpr, self._vpr)]
+        saved = [b[o:o + n].clone() for o, n in regions]
+
+        def restore():
+            for (o, n), s in zip(regions, saved):
+                b[o:o + n].copy_(s)
+
+        times, results = {}, {}
+        for mode in self.candidates:
+            ts = []
+            for rep in range(4):
+                restore()
+                a, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                w = self._run(mode, flat, 0, P)
+                if w is not None:
+                    w.wait()
+                e.record()
+                torch.cuda.synchronize(dev)
+                if rep > 0:
+                    ts.append(a.elapsed_time(e))
+            times[mode] = sorted(ts)[len(ts) // 2]
+            results[mode] = (flat.clone(), self.vis.clone())
+        ok = 1.0
+        dense = next((m for m in ("multimem", "all_reduce") if m in results), None)
+        if "sparse" in results and dense is not None:
+            rs, vs = results["sparse"]
+            rd, _ = results[dense]
+            scale = float(rd[:, :N_COLS - 1].abs().max().clamp_min(1e-30))
+            err = float((rs[:, :N_COLS - 1] - rd[:, :N_COLS - 1]).abs().max()) / scale
+            verr = float((vs - rd[:, N_COLS - 1]).abs().max())
+            self.report.update(sparse_vs_dense_rel_err=err, sparse_vis_err=verr)
+            if not (err <= 1e-5 and verr == 0.0) or int(self._status.item()) != 0:
+                ok = 0.0
+        order = list(self.candidates)
+        t = torch.tensor([times[m] for m in order] + [-ok], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        tl = [float(x) for x in t.tolist()]
+        agreed = dict(zip(order, tl[:-1]))
+        if -tl[-1] < 0.5:  # some rank saw a wrong sparse result: never use it
+            agreed.pop("sparse", None)
+            self.report["sparse_rejected"] = True
+        self.mode = min(agreed, key=agreed.get)
+        self.decided = True
+        import numpy as np
+        o = self._offs[1] // 4 + self._rank * self._wpr
+        words = self._buf.view(torch.int32)[o:o + self._wpr].cpu().numpy()
+        self.report.update(times_ms=agreed, mode=self.mode, rows=P,
+                           touched_rows_local=int(np.unpackbits(words.view(np.uint8)).sum()))
+        restore()
+
+    def reduce(self, flat: torch.Tensor, p0: int, p1: int):
+        """Start the sum of rows [p0, p1); returns a handle with .wait() or None when already stream-ordered."""
+        if not self.decided:
+            if (p0, p1) != (0, self._P):   # ranges are not supported by the sparse kernel's trial: drop it
+                self.candidates = [m for m in self.candidates if m != "sparse"] or ["all_reduce"]
+                self.mode, self.decided = self.candidates[0], len(self.candidates) == 1
+            if not self.decided:
+                self._decide(flat)
+        return self._run(self.mode, flat, p0, p1)
 
 
 class MappingWindow:
@@ -197,11 +318,16 @@ class MappingWindow:
         radii.zero_()
         if not mine:  # more GPUs than keyframes: contribute zeros, but take part in every collective
             flat.zero_()
+            self.exchange.zero_marks()
             for c in chunks:
                 chunk_done(*c)
         for i, k in enumerate(mine):
             last = i == len(mine) - 1
-            r = self.render_fn(k, params, flat, i > 0, chunks, chunk_done if last else None)
+            if self.exchange.marks is not None and getattr(self.render_fn, "accepts_marks", False):
+                r = self.render_fn(k, params, flat, i > 0, chunks, chunk_done if last else None,
+                                   marks=self.exchange.marks)
+            else:
+                r = self.render_fn(k, params, flat, i > 0, chunks, chunk_done if last else None)
             torch.maximum(radii, r.radii.to(torch.int32), out=radii)
             local.append(r)
         if world > 1:
@@ -211,7 +337,8 @@ class MappingWindow:
         sl = column_slices()
         grads = {name: flat[:, sl[name]] for name, _ in PARAM_COLUMNS}
         return WindowStepResult(grads=grads, grad2d_norm=flat[:, sl["grad2d_norm"]].squeeze(1),
-                                vis_count=flat[:, sl["vis_count"]].squeeze(1), max_radii=radii, local=local)
+                                vis_count=self.exchange.vis_count(flat) if world > 1 else
+                                flat[:, sl["vis_count"]].squeeze(1), max_radii=radii, local=local)
 
 
 def mapping_loss_grad(color, depth, gt_image, gt_depth):
@@ -240,7 +367,7 @@ def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
     cached = {}
     lg = loss_grad or mapping_loss_grad
 
-    def render(k, params, flat, accumulate, chunks, chunk_done) -> KeyframeResult:
+    def render(k, params, flat, accumulate, chunks, chunk_done, marks=None) -> KeyframeResult:
         cam = cameras[k]
         dev = flat.device
         if k not in cached:
@@ -255,7 +382,8 @@ def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
         tau, _ = _C.rasterize_gaussians_backward_rows(
             bg, params["means3D"], radii, params["scales"], params["rotations"], 1.0, view, proj, proj_raw,
             cam.tanfovx, cam.tanfovy, dcol.contiguous(), ddep.contiguous(), geom, R, plist, img, flat, accumulate,
-            chunks=chunks, chunk_done=chunk_done)
+            chunks=chunks, chunk_done=chunk_done, marks=marks)
         return KeyframeResult(index=k, radii=radii, n_touched=n_touched, grad_tau=tau, loss=loss)
 
+    render.accepts_marks = True
     return render

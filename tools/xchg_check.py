@@ -1,0 +1,91 @@
+"""Window-row exchange check on >= 2 GPUs (run under torchrun, NCCL):
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
+      tools/xchg_check.py [--gaussians 200000] [--keyframes 5] [--out gpurun_out/xchg_check.json]
+
+Runs the sharded mapping window (monogs_b200.window.MappingWindow + the sm_100a rasterizer) once per exchange
+mode -- our sparse in-switch kernel (gsr_rows_exchange), torch's dense multimem allreduce, ncclAllReduce -- on the
+same scene and compares gradients, densification statistics, visibility counts and radii of the sparse mode with
+the NCCL result; then times the three exchanges on the rows of one keyframe of the headline-sized map.
+Rank 0 prints one JSON line (and writes --out)."""
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+
+def run_mode(mode, cams, targets, bg, sc, n_kf):
+    from monogs_b200 import window
+    os.environ["GSR_XCHG"] = mode
+    w = window.MappingWindow(window.make_cuda_render_fn(cams, targets, bg))
+    res = None
+    for _ in range(3):  # the first step decides / warms up; later steps must give the same sums
+        res = w.step(sc, n_kf)
+    torch.cuda.synchronize()
+    out = {k: v.clone() for k, v in res.grads.items()}
+    out["grad2d_norm"] = res.grad2d_norm.clone()
+    out["vis_count"] = res.vis_count.clone()
+    out["max_radii"] = res.max_radii.clone().float()
+    return out, w.exchange
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gaussians", type=int, default=200000)
+    ap.add_argument("--keyframes", type=int, default=5)
+    ap.add_argument("--kind", default="tum")
+    ap.add_argument("--out", default="")
+    a = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dev = torch.device("cuda", torch.cuda.current_device())
+    dist.init_process_group("nccl", device_id=dev)
+    from monogs_b200 import synth
+
+    cams = synth.arc_cameras(a.kind, a.keyframes)
+    sc = {k: v.to(dev) for k, v in synth.make_scene(a.gaussians, synth.make_camera(a.kind), seed=1).items()}
+    targets = [tuple(t.to(dev) for t in synth.make_targets(c, seed=i)) for i, c in enumerate(cams)]
+    bg = torch.tensor([0.1, 0.2, 0.3], device=dev)
+
+    report = {"world": world, "gaussians": a.gaussians, "keyframes": a.keyframes, "modes": {}}
+    ref, _ = run_mode("all_reduce", cams, targets, bg, sc, a.keyframes)
+    worst = 0.0
+    for mode in ("sparse", "multimem"):
+        try:
+            got, ex = run_mode(mode, cams, targets, bg, sc, a.keyframes)
+        except Exception as e:  # noqa: BLE001
+            report["modes"][mode] = {"error": repr(e)[:300]}
+            continue
+        errs = {}
+        for k, r in ref.items():
+            scale = float(r.abs().max().clamp_min(1e-30))
+            errs[k] = float((got[k].reshape(r.shape) - r).abs().max()) / scale
+        st = int(ex._status.item()) if getattr(ex, "_status", None) is not None else None
+        report["modes"][mode] = {"used_mode": ex.mode, "rel_err": errs, "status": st}
+        if ex.mode == mode:
+            worst = max(worst, max(errs.values()))
+    t = torch.tensor([worst], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    report["worst_rel_err_all_ranks"] = float(t)
+    report["pass"] = bool(float(t) <= 1e-5)
+    if rank == 0:
+        line = json.dumps(report)
+        print(line, flush=True)
+        if a.out:
+            Path(a.out).parent.mkdir(parents=True, exist_ok=True)
+            Path(a.out).write_text(line + "\n")
+    dist.barrier()
+    dist.destroy_process_group()
+    if not report["pass"]:
+        sys.exit(1)
+
+
+if __name__ == "__main__":
+    main()
