@@ -243,6 +243,33 @@ int gsr_backward_rows_marked(void* stream, int P, int p_begin, int p_end, int wi
 int gsr_rows_exchange(void* stream, int P, int rank, int world, int n_ctas, void* local_buf, void* multicast_buf,
                       const uint64_t* peer_bufs, uint32_t epoch, float* vis_count, int* status);
 
+/* ---- Gaussian insertion from an RGB-D keyframe: the device side of
+ * GaussianModel.create_viewpoint_pcd (gaussian_splatting/scene/gaussian_model.py:121-319), the caller of distCUDA2.
+ * Images are the reference's row-major [H,W] / [3,H,W] tensors; "flat index" i = x*H + y is the reference's
+ * (W,H)-ordered flattening (:180-186), which fixes the order of the selected pixels.
+ *  gsr_select_kth_f32  out[0] = the element of ascending rank k of v[i] = b ? |a[i]-b[i]| : a[i]   (k = (n-1)/2 is
+ *                      torch.median's lower median, :177,:218); 4 radix-select launches, no sort. ws >= 8192 bytes.
+ *  gsr_insert_select   densification mask (:191-226: depth >= 1e-3, and unless init: opacity < 0.5 or (depth in front
+ *                      of the rendered depth and |error| > 50 * *median_err)) + stable compaction:
+ *                      selected[0..*count) = flat indices in ascending order. ws = gsr_insert_ws_bytes(W, H).
+ *  gsr_insert_points   for j < K: i = selected[pick ? pick[j] : j] (pick = the host's randperm subsample, int64,
+ *                      :247-259): features[j] = rgb (clamp(exp(a) rgb + b, 0, 1) when exposure_a/b given, :135-139),
+ *                      ids[j] = segmentation (optional), xyz[j] = c2w * (K_inv * (x+.5, y+.5, 1) * depth)  (:262-279).
+ *                      K_inv: row-major 3x3, c2w: row-major 4x4 (device).
+ *  gsr_insert_finish   scales[j][0..scale_cols) = log(sqrt(max(dist2[j], 1e-7) * min(0.05, 0.01 * *median_depth)))
+ *                      (:169-177,:294-306), rotations[j] = (1,0,0,0), opacities[j] = logit(0.5) = 0  (:308-318). */
+size_t gsr_insert_ws_bytes(int width, int height);
+int gsr_select_kth_f32(void* stream, int64_t n, const float* a, const float* b, int64_t k, float* out, void* ws);
+int gsr_insert_select(void* stream, int width, int height, const float* gt_depth, const float* render_depth,
+                      const float* render_opacity, int init, const float* median_err, int32_t* selected,
+                      uint32_t* count, void* ws);
+int gsr_insert_points(void* stream, int K, const int32_t* selected, const int64_t* pick, int width, int height,
+                      const float* rgb, const float* exposure_a, const float* exposure_b, const float* gt_depth,
+                      const int32_t* segmentation, const float* K_inv, const float* c2w, float* xyz,
+                      float* features, int32_t* ids);
+int gsr_insert_finish(void* stream, int K, const float* dist2, const float* median_depth, int scale_cols,
+                      float* scales, float* rotations, float* opacities);
+
 /* present[P] (uint8 0/1) = p_view.z > 0.2  (auxiliary.h:139-164). */
 int gsr_mark_visible(void* stream, int P, const float* means3D,
                      const float* viewmatrix, const float* projmatrix,

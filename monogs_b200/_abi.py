@@ -42,6 +42,11 @@ SIGNATURES = {
     "gsr_rows_exchange_bytes": (C.c_size_t, [i32, i32]),
     "gsr_rows_exchange_layout": (i32, [i32, i32, C.POINTER(C.c_size_t), C.POINTER(i32), C.POINTER(i32)]),
     "gsr_rows_exchange": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, C.c_uint32, vp, vp]),
+    "gsr_insert_ws_bytes": (sz, [i32, i32]),
+    "gsr_select_kth_f32": (i32, [vp, i64, vp, vp, i64, vp, vp]),
+    "gsr_insert_select": (i32, [vp, i32, i32, vp, vp, vp, i32, vp, vp, vp, vp]),
+    "gsr_insert_points": (i32, [vp, i32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "gsr_insert_finish": (i32, [vp, i32, vp, vp, i32, vp, vp, vp]),
     "gsr_mark_visible": (i32, [vp, i32, vp, vp, vp, vp]),
     "gsr_knn_dist2": (i32, [vp, i32, vp, vp, vp]),
     "gsr_profile_enable": (i32, [i32]),

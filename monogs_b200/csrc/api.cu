@@ -499,6 +499,48 @@ int gsr_backward_rows_marked(void* stream, int P, int p_begin, int p_end, int wi
   return debug_sync(st, debug);
 }
 
+size_t gsr_insert_ws_bytes(int width, int height) {
+  if (width <= 0 || height <= 0) return 0;
+  return INSERT_SELECT_WS_BYTES + align_up((size_t)((width * (size_t)height + 1023) / 1024) * 4);
+}
+
+int gsr_select_kth_f32(void* stream, int64_t n, const float* a, const float* b, int64_t k, float* out, void* ws) {
+  if (n <= 0 || n >= (int64_t)1 << 32 || k < 0 || k >= n || !a || !out || !ws) return GSR_EINVAL;
+  return check(launch_select_kth((cudaStream_t)stream, n, a, b, k, out, (uint32_t*)ws));
+}
+
+int gsr_insert_select(void* stream, int width, int height, const float* gt_depth, const float* render_depth,
+                      const float* render_opacity, int init, const float* median_err, int32_t* selected,
+                      uint32_t* count, void* ws) {
+  if (width <= 0 || height <= 0 || !gt_depth || !selected || !count || !ws) return GSR_EINVAL;
+  if (!init && (!render_depth || !median_err)) return GSR_EINVAL;
+  return check(launch_insert_select((cudaStream_t)stream, width, height, gt_depth, render_depth, render_opacity,
+                                    init, median_err, selected, count,
+                                    (uint32_t*)((char*)ws + INSERT_SELECT_WS_BYTES)));
+}
+
+int gsr_insert_points(void* stream, int K, const int32_t* selected, const int64_t* pick, int width, int height,
+                      const float* rgb, const float* exposure_a, const float* exposure_b, const float* gt_depth,
+                      const int32_t* segmentation, const float* K_inv, const float* c2w, float* xyz,
+                      float* features, int32_t* ids) {
+  if (K < 0 || width <= 0 || height <= 0) return GSR_EINVAL;
+  if (K == 0) return GSR_OK;
+  if (!selected || !rgb || !gt_depth || !K_inv || !c2w || !xyz || !features) return GSR_EINVAL;
+  if ((exposure_a == nullptr) != (exposure_b == nullptr) || (ids && !segmentation)) return GSR_EINVAL;
+  return check(launch_insert_points((cudaStream_t)stream, K, selected, reinterpret_cast<const long long*>(pick),
+                                    width, height, rgb, exposure_a, exposure_b, gt_depth, segmentation, K_inv, c2w,
+                                    xyz, features, ids));
+}
+
+int gsr_insert_finish(void* stream, int K, const float* dist2, const float* median_depth, int scale_cols,
+                      float* scales, float* rotations, float* opacities) {
+  if (K < 0 || (scale_cols != 1 && scale_cols != 3)) return GSR_EINVAL;
+  if (K == 0) return GSR_OK;
+  if (!dist2 || !median_depth || !scales || !rotations || !opacities) return GSR_EINVAL;
+  return check(launch_insert_finish((cudaStream_t)stream, K, dist2, median_depth, scale_cols, scales, rotations,
+                                    opacities));
+}
+
 int gsr_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present) {
   (void)projmatrix;  // the reference computes p_proj but only tests p_view.z (auxiliary.h:149-154)

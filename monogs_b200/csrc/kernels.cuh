@@ -99,6 +99,20 @@ cudaError_t launch_densify_stats(cudaStream_t st, int P, const int* radii, const
 cudaError_t launch_visibility_prune(cudaStream_t st, int P, int K, const int* const* touched, const int* kf_idx,
                                     int min_kf, int coviz, int* nr_obs, uint8_t* to_prune);
 
+// insert.cu  (Gaussian insertion from an RGB-D keyframe, gaussian_model.py:121-319)
+constexpr size_t INSERT_SELECT_WS_BYTES = 8192;  // radix-select state: prefix, rank, tickets, 4 x 256 histogram
+cudaError_t launch_select_kth(cudaStream_t st, long long n, const float* a, const float* b, long long k,
+                              float* out, uint32_t* ws);
+cudaError_t launch_insert_select(cudaStream_t st, int W, int H, const float* gt_depth, const float* render_depth,
+                                 const float* render_opacity, int init, const float* median_err, int32_t* sel,
+                                 uint32_t* total, uint32_t* block_counts);
+cudaError_t launch_insert_points(cudaStream_t st, int K, const int32_t* sel, const long long* pick, int W, int H,
+                                 const float* rgb, const float* exposure_a, const float* exposure_b,
+                                 const float* gt_depth, const int32_t* segmentation, const float* K_inv,
+                                 const float* c2w, float* xyz, float* feat, int32_t* ids);
+cudaError_t launch_insert_finish(cudaStream_t st, int K, const float* dist2, const float* median_depth,
+                                 int scale_cols, float* scales, float* rots, float* opacities);
+
 // knn.cu
 size_t knn_workspace_bytes(int P);
 cudaError_t launch_knn(cudaStream_t st, int P, const float* points, float* mean_dist2, void* ws);
