@@ -254,8 +254,9 @@ int gsr_rows_exchange(void* stream, int P, int rank, int world, int n_ctas, void
  *                      selected[0..*count) = flat indices in ascending order. ws = gsr_insert_ws_bytes(W, H).
  *  gsr_insert_points   for j < K: i = selected[pick ? pick[j] : j] (pick = the host's randperm subsample, int64,
  *                      :247-259): features[j] = rgb (clamp(exp(a) rgb + b, 0, 1) when exposure_a/b given, :135-139),
- *                      ids[j] = segmentation (optional), xyz[j] = c2w * (K_inv * (x+.5, y+.5, 1) * depth)  (:262-279).
- *                      K_inv: row-major 3x3, c2w: row-major 4x4 (device).
+ *                      ids[j] = segmentation (optional), xyz[j] = c2w * (K^-1 * (x+.5, y+.5, 1) * depth)  (:262-279),
+ *                      K = [[fx,0,cx],[0,fy,cy],[0,0,1]] and c2w = [R | T]^-1 inverted in the kernel (the reference
+ *                      calls torch.linalg.inv, :163-165). R: row-major 3x3, T: 3 floats (device, world-to-camera).
  *  gsr_insert_finish   scales[j][0..scale_cols) = log(sqrt(max(dist2[j], 1e-7) * min(0.05, 0.01 * *median_depth)))
  *                      (:169-177,:294-306), rotations[j] = (1,0,0,0), opacities[j] = logit(0.5) = 0  (:308-318). */
 size_t gsr_insert_ws_bytes(int width, int height);
@@ -265,8 +266,8 @@ int gsr_insert_select(void* stream, int width, int height, const float* gt_depth
                       uint32_t* count, void* ws);
 int gsr_insert_points(void* stream, int K, const int32_t* selected, const int64_t* pick, int width, int height,
                       const float* rgb, const float* exposure_a, const float* exposure_b, const float* gt_depth,
-                      const int32_t* segmentation, const float* K_inv, const float* c2w, float* xyz,
-                      float* features, int32_t* ids);
+                      const int32_t* segmentation, const float* R, const float* T, float fx, float fy, float cx,
+                      float cy, float* xyz, float* features, int32_t* ids);
 int gsr_insert_finish(void* stream, int K, const float* dist2, const float* median_depth, int scale_cols,
                       float* scales, float* rotations, float* opacities);
 

@@ -45,7 +45,8 @@ SIGNATURES = {
     "gsr_insert_ws_bytes": (sz, [i32, i32]),
     "gsr_select_kth_f32": (i32, [vp, i64, vp, vp, i64, vp, vp]),
     "gsr_insert_select": (i32, [vp, i32, i32, vp, vp, vp, i32, vp, vp, vp, vp]),
-    "gsr_insert_points": (i32, [vp, i32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "gsr_insert_points": (i32, [vp, i32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, f32, f32, f32, f32, vp, vp,
+                                vp]),
     "gsr_insert_finish": (i32, [vp, i32, vp, vp, i32, vp, vp, vp]),
     "gsr_mark_visible": (i32, [vp, i32, vp, vp, vp, vp]),
     "gsr_knn_dist2": (i32, [vp, i32, vp, vp, vp]),

@@ -521,15 +521,15 @@ int gsr_insert_select(void* stream, int width, int height, const float* gt_depth
 
 int gsr_insert_points(void* stream, int K, const int32_t* selected, const int64_t* pick, int width, int height,
                       const float* rgb, const float* exposure_a, const float* exposure_b, const float* gt_depth,
-                      const int32_t* segmentation, const float* K_inv, const float* c2w, float* xyz,
-                      float* features, int32_t* ids) {
+                      const int32_t* segmentation, const float* R, const float* T, float fx, float fy, float cx,
+                      float cy, float* xyz, float* features, int32_t* ids) {
   if (K < 0 || width <= 0 || height <= 0) return GSR_EINVAL;
   if (K == 0) return GSR_OK;
-  if (!selected || !rgb || !gt_depth || !K_inv || !c2w || !xyz || !features) return GSR_EINVAL;
+  if (!selected || !rgb || !gt_depth || !R || !T || !xyz || !features || fx == 0.f || fy == 0.f) return GSR_EINVAL;
   if ((exposure_a == nullptr) != (exposure_b == nullptr) || (ids && !segmentation)) return GSR_EINVAL;
   return check(launch_insert_points((cudaStream_t)stream, K, selected, reinterpret_cast<const long long*>(pick),
-                                    width, height, rgb, exposure_a, exposure_b, gt_depth, segmentation, K_inv, c2w,
-                                    xyz, features, ids));
+                                    width, height, rgb, exposure_a, exposure_b, gt_depth, segmentation, R, T, fx,
+                                    fy, cx, cy, xyz, features, ids));
 }
 
 int gsr_insert_finish(void* stream, int K, const float* dist2, const float* median_depth, int scale_cols,

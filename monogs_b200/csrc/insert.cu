@@ -162,11 +162,32 @@ __global__ void __launch_bounds__(256)
 insert_points_kernel(int K, const int32_t* __restrict__ sel, const long long* __restrict__ pick, int W, int H,
                      const float* __restrict__ rgb, const float* __restrict__ exposure_a,
                      const float* __restrict__ exposure_b, const float* __restrict__ gt_depth,
-                     const int32_t* __restrict__ segmentation, const float* __restrict__ K_inv,
-                     const float* __restrict__ c2w, float* __restrict__ xyz, float* __restrict__ feat,
-                     int32_t* __restrict__ ids) {
+                     const int32_t* __restrict__ segmentation, const float* __restrict__ Rw2c,
+                     const float* __restrict__ Tw2c, float fx, float fy, float cx, float cy,
+                     float* __restrict__ xyz, float* __restrict__ feat, int32_t* __restrict__ ids) {
   pdl_launch_dependents();
   pdl_wait();
+  // K^-1 of the upper-triangular intrinsics in closed form and c2w = [R | T]^-1 by the adjugate (general R, like the
+  // reference's torch.linalg.inv, :163-165) -- once per CTA, instead of two cuSOLVER calls with host syncs
+  __shared__ float K_inv[9];
+  __shared__ float c2w[12];
+  if (threadIdx.x == 0) {
+    K_inv[0] = 1.0f / fx; K_inv[1] = 0.f; K_inv[2] = -cx / fx;
+    K_inv[3] = 0.f; K_inv[4] = 1.0f / fy; K_inv[5] = -cy / fy;
+    K_inv[6] = 0.f; K_inv[7] = 0.f; K_inv[8] = 1.f;
+    const float a = Rw2c[0], b = Rw2c[1], c = Rw2c[2], d = Rw2c[3], e = Rw2c[4], f = Rw2c[5], g = Rw2c[6],
+                h = Rw2c[7], i = Rw2c[8];
+    const float A = e * i - f * h, B = -(d * i - f * g), Cc = d * h - e * g;
+    const float inv_det = 1.0f / (a * A + b * B + c * Cc);
+    float inv[9] = {A * inv_det, -(b * i - c * h) * inv_det, (b * f - c * e) * inv_det,
+                    B * inv_det, (a * i - c * g) * inv_det, -(a * f - c * d) * inv_det,
+                    Cc * inv_det, -(a * h - b * g) * inv_det, (a * e - b * d) * inv_det};
+    for (int r = 0; r < 3; ++r) {
+      c2w[4 * r] = inv[3 * r]; c2w[4 * r + 1] = inv[3 * r + 1]; c2w[4 * r + 2] = inv[3 * r + 2];
+      c2w[4 * r + 3] = -(inv[3 * r] * Tw2c[0] + inv[3 * r + 1] * Tw2c[1] + inv[3 * r + 2] * Tw2c[2]);
+    }
+  }
+  __syncthreads();
   const int j = blockIdx.x * 256 + threadIdx.x;
   if (j >= K) return;
   const int i = sel[pick ? pick[j] : j];
@@ -235,11 +256,12 @@ cudaError_t launch_insert_select(cudaStream_t st, int W, int H, const float* gt_
 
 cudaError_t launch_insert_points(cudaStream_t st, int K, const int32_t* sel, const long long* pick, int W, int H,
                                  const float* rgb, const float* exposure_a, const float* exposure_b,
-                                 const float* gt_depth, const int32_t* segmentation, const float* K_inv,
-                                 const float* c2w, float* xyz, float* feat, int32_t* ids) {
+                                 const float* gt_depth, const int32_t* segmentation, const float* R,
+                                 const float* T, float fx, float fy, float cx, float cy, float* xyz, float* feat,
+                                 int32_t* ids) {
   count_launch();
   launch_k(insert_points_kernel, (K + 255) / 256, 256, 0, st, K, sel, pick, W, H, rgb, exposure_a, exposure_b,
-           gt_depth, segmentation, K_inv, c2w, xyz, feat, ids);
+           gt_depth, segmentation, R, T, fx, fy, cx, cy, xyz, feat, ids);
   return cudaGetLastError();
 }
 

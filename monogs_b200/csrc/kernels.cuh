@@ -108,8 +108,9 @@ cudaError_t launch_insert_select(cudaStream_t st, int W, int H, const float* gt_
                                  uint32_t* total, uint32_t* block_counts);
 cudaError_t launch_insert_points(cudaStream_t st, int K, const int32_t* sel, const long long* pick, int W, int H,
                                  const float* rgb, const float* exposure_a, const float* exposure_b,
-                                 const float* gt_depth, const int32_t* segmentation, const float* K_inv,
-                                 const float* c2w, float* xyz, float* feat, int32_t* ids);
+                                 const float* gt_depth, const int32_t* segmentation, const float* R,
+                                 const float* T, float fx, float fy, float cx, float cy, float* xyz, float* feat,
+                                 int32_t* ids);
 cudaError_t launch_insert_finish(cudaStream_t st, int K, const float* dist2, const float* median_depth,
                                  int scale_cols, float* scales, float* rots, float* opacities);
 

@@ -10,8 +10,7 @@ The reference assembles it from ~40 framework ops, two of them sort-based `torch
 and four boolean-mask indexings; here the device side is 4 radix-select launches per median, a mask + stable
 compaction pair, one gather/unproject kernel, `distCUDA2` (csrc/knn.cu) and one finishing kernel, all through the
 C ABI (gsr_select_kth_f32, gsr_insert_select, gsr_insert_points, gsr_knn_dist2, gsr_insert_finish).  What stays on
-the host is what the reference also does there: the 3x3 / 4x4 inverses (`torch.linalg.inv`, :163-165), reading the
-number of selected pixels (a boolean-mask indexing in the reference, :242-245) and `torch.randperm` on the host RNG
+the host is what the reference also does there: reading the number of selected pixels (a boolean-mask indexing in the reference, :242-245) and `torch.randperm` on the host RNG
 (:256), so a seeded run keeps the same pixels.  No CPU fallback: CPU tensors raise.
 """
 from __future__ import annotations
@@ -67,11 +66,11 @@ def w2c_from_RT(R: torch.Tensor, T: torch.Tensor) -> torch.Tensor:
 
 
 def create_viewpoint_pcd(viewpoint, cam_intrinsics, render_depth=None, render_opacity=None, init=False,
-                         isotropic=True, random_indices: Optional[torch.Tensor] = None):
+                         isotropic=True, random_indices: Optional[torch.Tensor] = None, rng: str = "host"):
     """See the module docstring. `viewpoint` needs .rgb [3,H,W], .depth [H,W], .segmentation [H,W], .R, .T and,
     unless init, .exposure_a / .exposure_b; `cam_intrinsics` needs fx, fy, cx, cy. `render_depth` /
     `render_opacity` are the rasterizer's [1,H,W] outputs. `random_indices` (optional, int64) replaces the
-    torch.randperm draw -- parity tests pass the reference's draw."""
+    torch.randperm draw -- parity tests pass the reference's draw; rng="device" draws it on the GPU instead."""
     lib = _abi.load()
     rgb = _f32(viewpoint.rgb, "viewpoint.rgb")
     dev = rgb.device
@@ -81,11 +80,9 @@ def create_viewpoint_pcd(viewpoint, cam_intrinsics, render_depth=None, render_op
     seg_dtype = seg.dtype
     seg32 = seg.contiguous().view(torch.int32) if seg.element_size() == 4 else seg.to(torch.int32).contiguous()
     fnum = lambda v: float(v.item()) if torch.is_tensor(v) else float(v)
-    Kmat = torch.tensor([[fnum(cam_intrinsics.fx), 0.0, fnum(cam_intrinsics.cx)],
-                         [0.0, fnum(cam_intrinsics.fy), fnum(cam_intrinsics.cy)],
-                         [0.0, 0.0, 1.0]], dtype=torch.float32, device=dev)
-    K_inv = torch.linalg.inv(Kmat).contiguous()                              # :163
-    c2w = torch.linalg.inv(w2c_from_RT(viewpoint.R.to(dev).float(), viewpoint.T.to(dev).float())).contiguous()  # :164-165
+    fx, fy, cx, cy = (fnum(getattr(cam_intrinsics, k)) for k in ("fx", "fy", "cx", "cy"))
+    R_w2c = viewpoint.R.to(device=dev, dtype=torch.float32).contiguous()      # K^-1 and [R|T]^-1 (:163-165) are
+    T_w2c = viewpoint.T.to(device=dev, dtype=torch.float32).contiguous()      # formed inside gsr_insert_points
 
     with torch.cuda.device(dev):
         st = _stream(dev)
@@ -113,11 +110,16 @@ def create_viewpoint_pcd(viewpoint, cam_intrinsics, render_depth=None, render_op
         factor = DOWNSAMPLE_INIT if init else DOWNSAMPLE
         keep = int(num_points * (1.0 / factor))                              # :249-254
         if random_indices is None:
-            random_indices = torch.randperm(num_points)[:keep]               # host RNG, like the reference (:256)
-        pick = random_indices.to(device=dev, dtype=torch.int64).contiguous()
+            if rng == "device":   # same distribution, drawn on the GPU (no 1-5 ms host permutation + upload)
+                random_indices = torch.randperm(num_points, device=dev)[:keep]
+            else:                 # host RNG, like the reference (:256): a seeded run keeps the same pixels
+                random_indices = torch.randperm(num_points)[:keep]
+        else:
+            ri = torch.as_tensor(random_indices)
+            if ri.numel() and (int(ri.max()) >= num_points or int(ri.min()) < 0):
+                raise RuntimeError("random_indices out of range")
+        pick = torch.as_tensor(random_indices).to(device=dev, dtype=torch.int64, non_blocking=True).contiguous()
         K = int(pick.numel())
-        if K and (int(pick.max()) >= num_points or int(pick.min()) < 0):
-            raise RuntimeError("random_indices out of range")
         xyz = torch.empty(K, 3, dtype=torch.float32, device=dev)
         feat = torch.empty(K, 3, dtype=torch.float32, device=dev)
         ids = torch.empty(K, dtype=torch.int32, device=dev)
@@ -133,8 +135,8 @@ def create_viewpoint_pcd(viewpoint, cam_intrinsics, render_depth=None, render_op
             _abi.check(lib.gsr_insert_points(st, K, sel.data_ptr(), pick.data_ptr(), W, H, rgb.data_ptr(),
                                              ea.data_ptr() if ea is not None else None,
                                              eb.data_ptr() if eb is not None else None, gt_depth.data_ptr(),
-                                             seg32.data_ptr(), K_inv.data_ptr(), c2w.data_ptr(), xyz.data_ptr(),
-                                             feat.data_ptr(), ids.data_ptr()), "gsr_insert_points")
+                                             seg32.data_ptr(), R_w2c.data_ptr(), T_w2c.data_ptr(), fx, fy, cx, cy,
+                                             xyz.data_ptr(), feat.data_ptr(), ids.data_ptr()), "gsr_insert_points")
             dist2 = torch.empty(K, dtype=torch.float32, device=dev)
             knn_ws = torch.empty(int(lib.gsr_knn_bytes(K)), dtype=torch.uint8, device=dev)
             _abi.check(lib.gsr_knn_dist2(st, K, xyz.data_ptr(), dist2.data_ptr(), knn_ws.data_ptr()),
