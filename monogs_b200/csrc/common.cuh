@@ -143,6 +143,8 @@ struct ImageViews {
   float* final_T;        // [H*W]
   uint32_t* n_contrib;   // [H*W]
   uint2* ranges;         // [tiles]
+  uint32_t* tile_work;   // [tiles] largest n_contrib of the tile (written by the forward renderer)
+  uint32_t* tile_order;  // [tiles] tiles by descending tile_work: the backward renderer's CTA -> tile map
 };
 __host__ __device__ inline size_t carve_image(char* base, int W, int H, ImageViews* v) {
   size_t off = 0;
@@ -150,7 +152,11 @@ __host__ __device__ inline size_t carve_image(char* base, int W, int H, ImageVie
   size_t tiles = num_tiles(W, H);
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
   char* a = take(4 * N); char* b = take(4 * N); char* c = take(8 * tiles);
-  if (v) { v->final_T = (float*)a; v->n_contrib = (uint32_t*)b; v->ranges = (uint2*)c; }
+  char* d = take(4 * tiles); char* e = take(4 * tiles);
+  if (v) {
+    v->final_T = (float*)a; v->n_contrib = (uint32_t*)b; v->ranges = (uint2*)c;
+    v->tile_work = (uint32_t*)d; v->tile_order = (uint32_t*)e;
+  }
   return off;
 }
 

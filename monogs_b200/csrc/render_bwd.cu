@@ -14,6 +14,7 @@
 //     lane, and those ten lanes issue ONE warp-wide red.global.add.f32 into a
 //     packed 48-byte per-Gaussian record (1-2 sectors per instruction);
 //   * warps in which no pixel is touched by the Gaussian do nothing.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -109,13 +110,58 @@ GSR_DEVINL int owner_slot(int lane) {
   return (b4 ? 5 : 0) + k5;
 }
 
+// Tiles by descending replay length (counting sort on tile_work / 4, one CTA): the hardware hands CTAs out in
+// linear order, so with this map the long tiles run first and the kernel's tail consists of the shortest ones
+// (measured on the headline scene: the backward renderer's last CTA started at 54 % of the kernel's span and ran
+// for up to half of it). Order inside a bin is arbitrary -- it only affects scheduling.
+constexpr int TO_THREADS = 1024;
+__global__ void __launch_bounds__(TO_THREADS)
+tile_order_kernel(int n_tiles, const uint32_t* __restrict__ tile_work, uint32_t* __restrict__ tile_order) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ uint32_t s_bin[TO_THREADS];
+  __shared__ uint32_t s_warp[TO_THREADS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  s_bin[tid] = 0;
+  __syncthreads();
+  for (int t = tid; t < n_tiles; t += TO_THREADS)
+    atomicAdd(&s_bin[TO_THREADS - 1 - min(tile_work[t] >> 2, (uint32_t)TO_THREADS - 1)], 1u);
+  __syncthreads();
+  // exclusive scan of the 1024 bins (bin 0 = heaviest)
+  const uint32_t c = s_bin[tid];
+  uint32_t inc = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = s_warp[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += v;
+    }
+    s_warp[lane] = w;
+  }
+  __syncthreads();
+  s_bin[tid] = inc - c + (warp ? s_warp[warp - 1] : 0u);
+  __syncthreads();
+  for (int t = tid; t < n_tiles; t += TO_THREADS) {
+    const uint32_t pos = atomicAdd(&s_bin[TO_THREADS - 1 - min(tile_work[t] >> 2, (uint32_t)TO_THREADS - 1)], 1u);
+    tile_order[pos] = (uint32_t)t;
+  }
+}
+
 __global__ void __launch_bounds__(RB_THREADS)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                   int tiles_x, const float* __restrict__ bg, const float4* __restrict__ rec_a,
                   const float4* __restrict__ rec_b, const float4* __restrict__ rec_c,
                   const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
                   const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth, LossView loss,
-                  float* __restrict__ packed /*[P][GRAD_STRIDE]*/) {
+                  float* __restrict__ packed /*[P][GRAD_STRIDE]*/, const uint32_t* __restrict__ tile_order) {
   pdl_launch_dependents();
 #ifdef GSR_CTA_TRACE
   const unsigned long long t_enter = trace_now();
@@ -128,10 +174,15 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   __shared__ uint32_t s_max[RB_THREADS / 32];
 
   const int tid = threadIdx.x, lane = tid & 31, wl = tid >> 5;
-  const int tile_y = blockIdx.y / RB_SUB;
+  int tile_y = blockIdx.y / RB_SUB, tile_x = blockIdx.x;
+  if (RB_SUB == 1 && tile_order) {  // heaviest tiles first (tile_order_kernel)
+    const uint32_t t = tile_order[blockIdx.y * gridDim.x + blockIdx.x];
+    tile_y = (int)(t / (uint32_t)tiles_x);
+    tile_x = (int)(t - (uint32_t)tile_y * (uint32_t)tiles_x);
+  }
   const int w = (blockIdx.y % RB_SUB) * RB_WARPS + wl;   // warp rectangle within the tile
-  const int tile = tile_y * tiles_x + blockIdx.x;
-  const int wx0 = blockIdx.x * TILE_X + (w & 1) * 8;
+  const int tile = tile_y * tiles_x + tile_x;
+  const int wx0 = tile_x * TILE_X + (w & 1) * 8;
   const int wy0 = tile_y * TILE_Y + (w >> 1) * 4;
   const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
   const bool inside = pxi < W && pyi < H;
@@ -324,13 +375,23 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 #endif
 }
 
+static bool tile_order_enabled() {  // GSR_TILE_ORDER=0: linear CTA -> tile map (A/B measurements)
+  static const bool on = [] { const char* e = getenv("GSR_TILE_ORDER"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, const float* dL_dpix,
                               const float* dL_dpix_depth, const LossView& loss, float* packed) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y * RB_SUB);
+  const uint32_t* order = nullptr;
+  if (RB_SUB == 1 && tile_order_enabled() && tiles_x * tiles_y > 2 * 148) {
+    count_launch(); launch_k(tile_order_kernel, 1, TO_THREADS, 0, st, tiles_x * tiles_y, (const uint32_t*)im.tile_work, im.tile_order);
+    order = im.tile_order;
+  }
   count_launch(); launch_k(render_bwd_kernel, grid, RB_THREADS, 0, st, im.ranges, point_list, W, H, tiles_x, bg, g.rec_a, g.rec_b,
-                                                 g.rec_c, im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, loss, packed);
+                                                 g.rec_c, im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, loss, packed, order);
   return cudaGetLastError();
 }
 

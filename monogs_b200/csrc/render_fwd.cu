@@ -65,7 +65,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   int tiles_x, const float4* __restrict__ rec_a, const float4* __restrict__ rec_b,
                   const float4* __restrict__ rec_c, const float* __restrict__ bg, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_depth,
-                  float* __restrict__ out_opacity, int* __restrict__ n_touched) {
+                  float* __restrict__ out_opacity, int* __restrict__ n_touched, uint32_t* __restrict__ tile_work) {
   pdl_launch_dependents();
 #ifdef GSR_CTA_TRACE
   const unsigned long long t_enter = trace_now();
@@ -204,6 +204,20 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     out_depth[pix] = D;
     out_opacity[pix] = fsub(1.0f, T);
   }
+  // the tile's replay length (its largest n_contrib) = the backward renderer's work for this tile: it starts its
+  // heaviest tiles first (tile_order_kernel, render_bwd.cu)
+  if (RF_SUB == 1 && tile_work) {
+    __shared__ uint32_t s_work[RF_WARPS];
+    const uint32_t wm = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
+    if (lane == 0) s_work[tid >> 5] = wm;
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t m = 0;
+#pragma unroll
+      for (int i = 0; i < RF_WARPS; ++i) m = max(m, s_work[i]);
+      tile_work[tile] = m;
+    }
+  }
 #ifdef GSR_CTA_TRACE
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -223,7 +237,7 @@ cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& i
   dim3 grid(tiles_x, tiles_y * RF_SUB);
   count_launch(); launch_k(render_fwd_kernel, grid, RF_THREADS, 0, st, im.ranges, point_list, W, H, tiles_x, g.rec_a, g.rec_b, g.rec_c,
                                                  bg, im.final_T, im.n_contrib, out_color, out_depth, out_opacity,
-                                                 n_touched);
+                                                 n_touched, im.tile_work);
   return cudaGetLastError();
 }
 
