@@ -155,7 +155,10 @@ tile_order_kernel(int n_tiles, const uint32_t* __restrict__ tile_work, uint32_t*
   }
 }
 
-__global__ void __launch_bounds__(RB_THREADS)
+#ifndef GSR_RB_MIN_CTAS
+#define GSR_RB_MIN_CTAS 1
+#endif
+__global__ void __launch_bounds__(RB_THREADS, GSR_RB_MIN_CTAS)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                   int tiles_x, const float* __restrict__ bg, const float4* __restrict__ rec_a,
                   const float4* __restrict__ rec_b, const float4* __restrict__ rec_c,
@@ -297,7 +300,10 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       if (jj < count) {
         const float4 a = sg.a[jj];
         const float ey = sg.c[jj].w;
-        hit = (a.x + a.w >= rx0) && (a.x - a.w <= rx1) && (a.y + ey >= ry0) && (a.y - ey <= ry1);
+        // entries behind this WARP's last contributor are no-ops for all of its pixels (the walk starts at the
+        // tile's largest n_contrib, which is typically 10-20 % beyond a warp's own)
+        const uint32_t posj = (uint32_t)(total - 1 - (b * RB_BATCH + jj));
+        hit = (posj < wm) && (a.x + a.w >= rx0) && (a.x - a.w <= rx1) && (a.y + ey >= ry0) && (a.y - ey <= ry1);
       }
       uint32_t mask = __ballot_sync(0xffffffffu, hit);
       while (mask) {

@@ -60,7 +60,10 @@ GSR_DEVINL void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "m
 template <int N>
 GSR_DEVINL void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-__global__ void __launch_bounds__(RF_THREADS)
+#ifndef GSR_RF_MIN_CTAS
+#define GSR_RF_MIN_CTAS 1
+#endif
+__global__ void __launch_bounds__(RF_THREADS, GSR_RF_MIN_CTAS)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                   int tiles_x, const float4* __restrict__ rec_a, const float4* __restrict__ rec_b,
                   const float4* __restrict__ rec_c, const float* __restrict__ bg, float* __restrict__ final_T,
