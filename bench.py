@@ -615,25 +615,34 @@ def main():
 
     # ---- end to end ---------------------------------------------------------------------------------------------
     e2e = None
+    def e2e_leg(stepper_, k):
+        """k steps through the public API with the host copies inside, device-timed, max over ranks; two passes, the
+        better one is kept (a 70 ms leg is easily disturbed by host jitter on a fresh box)."""
+        for _ in range(5):
+            stepper_.step()
+        best, wall = None, None
+        for _ in range(2):
+            barrier(world)
+            t0 = torch.cuda.Event(enable_timing=True)
+            t1 = torch.cuda.Event(enable_timing=True)
+            w0 = time.perf_counter()
+            t0.record()
+            for _ in range(k):
+                stepper_.step()
+            t1.record()
+            barrier(world)
+            w = time.perf_counter() - w0
+            s_ = max_over_ranks(max(t0.elapsed_time(t1) / 1e3, 0.0), world, dev)
+            if best is None or s_ < best:
+                best, wall = s_, w
+        return best, wall
+
     if not a.no_e2e:
         es = E2EStep(wl, world, impl)
         k_e2e = max(3, min(2 * a.steps, 60))  # longer than the device leg: host-side jitter averages out
-        for _ in range(5):
-            es.step()
-        barrier(world)
-        t0 = torch.cuda.Event(enable_timing=True)
-        t1 = torch.cuda.Event(enable_timing=True)
-        w0 = time.perf_counter()
-        t0.record()
-        for _ in range(k_e2e):
-            es.step()
-        t1.record()
-        barrier(world)
-        wall = time.perf_counter() - w0
-        dev_s = t0.elapsed_time(t1) / 1e3
-        e2e_s = max_over_ranks(max(dev_s, 0.0), world, dev)
+        e2e_s, wall = e2e_leg(es, k_e2e)
         e2e = {"value": world * k_e2e / e2e_s, "unit": "it/s", "h2d_bytes_per_step": es.h2d,
-               "d2h_bytes_per_step": es.d2h, "steps": k_e2e, "wall_s": round(wall, 4),
+               "d2h_bytes_per_step": es.d2h, "steps": k_e2e, "passes": 2, "wall_s": round(wall, 4),
                "api": "GaussianRasterizer.forward + loss.backward()" if impl == "ours" else
                       "reference CUDA via oracle/_ref + loss.backward()"}
 
@@ -641,17 +650,7 @@ def main():
     if not a.no_e2e and impl == "ours":
         # the same iteration through the ADDITIONAL fused entry point (monogs_b200.fused_loss.render_l1_loss)
         ef = E2EStep(wl, world, "ours-fused")
-        for _ in range(5):
-            ef.step()
-        barrier(world)
-        t0 = torch.cuda.Event(enable_timing=True)
-        t1 = torch.cuda.Event(enable_timing=True)
-        t0.record()
-        for _ in range(k_e2e):
-            ef.step()
-        t1.record()
-        barrier(world)
-        ef_s = max_over_ranks(t0.elapsed_time(t1) / 1e3, world, dev)
+        ef_s, _ = e2e_leg(ef, k_e2e)
         e2e_fused = {"value": world * k_e2e / ef_s, "unit": "it/s", "h2d_bytes_per_step": ef.h2d,
                      "d2h_bytes_per_step": ef.d2h, "api": "fused_loss.render_l1_loss + loss.backward()"}
 
