@@ -692,6 +692,19 @@ def main():
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                             "frac": achieved / peak, "traffic": ncu_traffic(dom), "peak_source": peak_src,
                             "algorithmic_bytes_per_launch": sb[dom], "ms_per_launch": per_launch_ms[dom]}
+        # the render kernels are instruction-issue bound, not HBM bound: the same launch against the
+        # issue-slot ceiling = 148 SMs x 4 schedulers x SM clock, with the warp-instruction count of the committed
+        # ncu capture (valid for the headline workload it was taken on)
+        try:
+            wi = json.loads((ROOT / "profiles" / "traffic.json").read_text()).get("_warp_inst", {}).get(dom)
+        except Exception:
+            wi = None
+        if wi and wl_name == "headline" and world == 1 and per_launch_ms[dom] > 0:
+            mhz = (clocks or {}).get("sm_mhz") or 1965.0
+            peak_issue = 148 * 4 * mhz * 1e6
+            ach = wi / (per_launch_ms[dom] * 1e-3)
+            line["roofline"]["issue_slots"] = {"warp_inst_per_launch": wi, "achieved_ginst_s": ach / 1e9,
+                                               "peak_ginst_s": peak_issue / 1e9, "frac": ach / peak_issue}
         # the same kernels against SURVEY 8d's per-instance terms with the FULL instance count R (the formula
         # assumes every instance of a tile list is read; early termination makes the kernels skip most of them)
         full = dict(units, R_consumed=None)
