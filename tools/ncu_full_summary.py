@@ -7,7 +7,16 @@ WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "launch__registers_per_thread", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
         "launch__grid_size", "smsp__inst_executed.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
         "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
-        "lts__throughput.avg.pct_of_peak_sustained_elapsed", "sm__cycles_active.avg"]
+        "lts__throughput.avg.pct_of_peak_sustained_elapsed", "sm__cycles_active.avg",
+        "smsp__inst_executed_op_global_red.sum", "lts__t_sectors_srcunit_tex_op_red.sum",
+        "lts__t_sectors_srcunit_tex_op_red.sum.pct_of_peak_sustained_elapsed",
+        "lts__d_atomic_input_cycles_active.avg.pct_of_peak_sustained_elapsed",
+        "lts__d_atomic_input_cycles_active.max.pct_of_peak_sustained_elapsed",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed",
+        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"]
 def main(rep, header):
     out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
