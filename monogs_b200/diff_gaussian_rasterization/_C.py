@@ -234,12 +234,13 @@ def mark_visible(means3D, viewmatrix, projmatrix):
 def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotations, scale_modifier, viewmatrix,
                                       projmatrix, projmatrix_raw, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth,
                                       geomBuffer, R, point_list, imageBuffer, rows, accumulate, chunks=None,
-                                      chunk_done=None, want_means2D=False, debug=False, marks=None):
+                                      chunk_done=None, want_means2D=False, debug=False, marks=None, rows_gate=None):
     """Backward of one keyframe of the sharded mapping window (gsr_backward_render + gsr_backward_rows): the
     Gaussian gradients are written / added into `rows` f32[P,16] (layout: include/gsr_b200.h) range by range;
     `chunk_done(p0, p1)` is called right after each range has been enqueued (the caller starts its allreduce of
     rows[p0:p1] there). `marks` = (touched_words_ptr, vis_u8_ptr): this rank's slot of the sparse window exchange
-    (gsr_backward_rows_marked, monogs_b200.window.RowExchange.marks). Returns (dL_dtau[6], dL_dmeans2D[P,3] or None)."""
+    (gsr_backward_rows_marked, monogs_b200.window.RowExchange.marks). `rows_gate`: a CUDA event the current stream
+    waits for before the per-Gaussian half (keyframes of one window on several streams accumulate in order). Returns (dL_dtau[6], dL_dmeans2D[P,3] or None)."""
     lib = _abi.load()
     P = int(means3D.size(0))
     dev = means3D.device
@@ -261,6 +262,8 @@ def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotati
         rc = lib.gsr_backward_render(st, P, W, H, _ptr(bg_c), geomBuffer.data_ptr(), imageBuffer.data_ptr(),
                                      _ptr(point_list), int(R), _ptr(gc), _ptr(gd), scratch.data_ptr(), int(bool(debug)))
         _abi.check(rc, "gsr_backward_render")
+        if rows_gate is not None:  # multi-stream window: the row accumulation is ordered across keyframes
+            torch.cuda.current_stream(dev).wait_event(rows_gate)
         for (p0, p1) in chunks:
             rc = lib.gsr_backward_rows_marked(st, P, int(p0), int(p1), W, H, _ptr(m3), _ptr(sc),
                                               float(scale_modifier), _ptr(ro), _ptr(vm), _ptr(pm), _ptr(pr),

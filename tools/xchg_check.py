@@ -21,10 +21,10 @@ ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
 
 
-def run_mode(mode, cams, targets, bg, sc, n_kf):
+def run_mode(mode, cams, targets, bg, sc, n_kf, n_streams=2):
     from monogs_b200 import window
     os.environ["GSR_XCHG"] = mode
-    w = window.MappingWindow(window.make_cuda_render_fn(cams, targets, bg))
+    w = window.MappingWindow(window.make_cuda_render_fn(cams, targets, bg), n_streams=n_streams)
     res = None
     for _ in range(3):  # the first step decides / warms up; later steps must give the same sums
         res = w.step(sc, n_kf)
@@ -55,7 +55,9 @@ def main():
     bg = torch.tensor([0.1, 0.2, 0.3], device=dev)
 
     report = {"world": world, "gaussians": a.gaussians, "keyframes": a.keyframes, "modes": {}}
-    ref, _ = run_mode("all_reduce", cams, targets, bg, sc, a.keyframes)
+    # reference result: ncclAllReduce, every local keyframe on ONE stream; the modes below also run the local
+    # keyframes round-robin on two streams (MappingWindow n_streams=2), so that path is checked as well
+    ref, _ = run_mode("all_reduce", cams, targets, bg, sc, a.keyframes, n_streams=1)
     worst = 0.0
     for mode in ("sparse", "multimem"):
         try:
