@@ -116,6 +116,23 @@ int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs /*M*/, int wid
                 float* out_color, float* out_depth, float* out_opacity, int* n_touched,
                 int64_t* num_rendered, int debug);
 
+/* ---- forward without any host interaction (CUDA-graph capturable) --------------------------------------------
+ * gsr_forward minus the host read of num_rendered: every kernel is enqueued for `capacity` instances and the call
+ * returns at once; nothing in it synchronises, allocates or touches library-global host state, so it may be issued
+ * while `stream` is being captured into a CUDA graph (monogs_b200/tracking.py captures a whole tracking iteration).
+ * total_out (optional; pinned-host or device memory, 8 bytes) receives num_rendered through a stream-ordered copy:
+ * when it exceeds `capacity` the images of that launch are invalid (lists were clipped, nothing went out of
+ * bounds) and the caller re-runs with larger buffers. n_touched must be zero on entry. */
+int gsr_forward_enqueue(void* stream, int P, int sh_degree, int sh_coeffs /*M*/, int width, int height,
+                        const float* background, const float* means3D, const float* shs,
+                        const float* colors_precomp, const float* opacities, const float* scales,
+                        float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                        const float* viewmatrix, const float* projmatrix, const float* campos,
+                        float tan_fovx, float tan_fovy, int prefiltered, int* radii, void* geom_ws,
+                        void* image_ws, void* binning_ws, uint32_t* point_list, int64_t capacity,
+                        float* out_color, float* out_depth, float* out_opacity, int* n_touched,
+                        uint64_t* total_out);
+
 /* ---- backward -----------------------------------------------------------
  * Outputs (all optional except where noted; NULL = not wanted):
  *   dL_dmeans2D[P,3], dL_dcolors[P,3], dL_dopacity[P,1], dL_dmeans3D[P,3],

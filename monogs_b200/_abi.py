@@ -29,6 +29,8 @@ SIGNATURES = {
     "gsr_forward_render": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, i32]),
     "gsr_forward": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, f32, f32, i32,
                           vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, C.POINTER(i64), i32]),
+    "gsr_forward_enqueue": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, f32,
+                                  f32, i32, vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, vp]),
     "gsr_backward": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, f32, f32,
                            vp, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
     "gsr_l1_loss_forward": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, f32, vp, vp]),

@@ -273,6 +273,34 @@ int gsr_forward_render(void* stream, int P, int width, int height, const float* 
                         nullptr, out_color, out_depth, out_opacity, n_touched, debug);
 }
 
+int gsr_forward_enqueue(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
+                        const float* background, const float* means3D, const float* shs,
+                        const float* colors_precomp, const float* opacities, const float* scales,
+                        float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                        const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
+                        float tan_fovy, int prefiltered, int* radii, void* geom_ws, void* image_ws, void* binning_ws,
+                        uint32_t* point_list, int64_t capacity, float* out_color, float* out_depth,
+                        float* out_opacity, int* n_touched, uint64_t* total_out) {
+  if (P <= 0 || width <= 0 || height <= 0 || capacity <= 0 || capacity >= (1ll << 30)) return GSR_EINVAL;
+  GSR_TRY(check_forward_args(P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
+                             rotations, cov3D_precomp, viewmatrix, projmatrix, campos, radii, geom_ws));
+  if (!background || !image_ws || !out_color || !out_depth || !out_opacity || !n_touched || !point_list)
+    return GSR_EINVAL;
+  if (!binning_ws && !use_tile_scatter(width, height)) return GSR_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  GeomViews g;
+  carve_geom((char*)geom_ws, P, width, height, &g);
+  ImageViews im;
+  carve_image((char*)image_ws, width, height, &im);
+  GSR_TRY(enqueue_plan(st, P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
+                       scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy,
+                       prefiltered, radii, (char*)geom_ws, g, 0));
+  if (total_out)
+    GSR_TRY(check(cudaMemcpyAsync(total_out, g.total, sizeof(unsigned long long), cudaMemcpyDefault, st)));
+  return enqueue_render(st, P, width, height, background, g, im, (char*)binning_ws, point_list, capacity, g.total,
+                        out_color, out_depth, out_opacity, n_touched, 0);
+}
+
 int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height, const float* background,
                 const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
                 const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
