@@ -459,6 +459,32 @@ def cpu_baseline(wl: Workload, budget_s=25.0):
                       f"({wl.W}x{wl.H}, P={wl.P}) with oracle/cpu_ref.cpp (OpenMP), best of {len(times)}"}
 
 
+def cpu_torch_c1():
+    """BASELINE.json's reported baseline "a host-core PyTorch reference of the same render() math, with core count
+    stated", on its config C1 (10 k Gaussians, 320x240, one tracking-shaped step fwd + autograd bwd): oracle/torch_ref.py
+    on all host cores, best of 3."""
+    from monogs_b200 import synth
+    from oracle import torch_ref as tr
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cam = synth.make_camera("tum_half", rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))
+    sc = synth.make_scene(10_000, cam, seed=0, device="cpu")
+    view, proj, _, _ = cam.matrices("cpu")
+    g = torch.Generator().manual_seed(7)
+    dcol = torch.randn(3, cam.H, cam.W, generator=g) / (cam.H * cam.W)
+    ddep = torch.randn(1, cam.H, cam.W, generator=g) / (cam.H * cam.W)
+    bg = torch.tensor([0.1, 0.2, 0.3])
+    best = None
+    for _ in range(3):
+        t0 = time.perf_counter()
+        tr.tracking_step(sc, view, proj, cam.W, cam.H, cam.tanfovx, cam.tanfovy, bg, dcol, ddep)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return {"value": 1.0 / best, "unit": "it/s", "cores": cores, "kind": "port",
+            "sample": "config C1 (10 k Gaussians, 320x240), one fwd + autograd bwd with oracle/torch_ref.py "
+                      "(vectorised PyTorch on the host cores), best of 3"}
+
+
 # ------------------------------------------------------------------------------------------------------------
 # timing helpers
 # ------------------------------------------------------------------------------------------------------------
@@ -720,6 +746,10 @@ def main():
                                  "frac": tb / (secs / a.steps) / 1e9 / peak}
         if world == 1 and not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl)
+            try:
+                line["cpu_baseline_torch_c1"] = cpu_torch_c1()
+            except Exception as e:  # noqa: BLE001  (reported extra; never fails the bench line)
+                line["cpu_baseline_torch_c1"] = {"error": repr(e)[:200]}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -1,0 +1,78 @@
+"""oracle/torch_ref.py -- the host-core PyTorch reference of the render() math (autograd): an INDEPENDENT derivation
+of the Gaussian-parameter gradients.  CPU: it agrees with the analytic C++ restatement of the reference's backward
+(oracle/cpu_ref.cpp, which is pinned to the reference CUDA golden vectors) -- integers exactly, images 1e-5, gradients
+1e-4 relative.  GPU: the CUDA kernels agree with it at config C1's shape (10 k Gaussians, 320x240)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import rel_inf
+from monogs_b200 import synth
+from oracle import cpu_oracle as co
+from oracle import torch_ref as tr
+
+GRADS = (("means3D", "means3D"), ("colors", "colors"), ("opacities", "opacity"), ("scales", "scales"),
+         ("rotations", "rotations"))
+
+
+def _case(P, kind, seed, anisotropic=False, layered=False):
+    synth.INTRINSICS.setdefault("tiny", (160, 120, 133.85, 134.8, 80.03, 61.9))
+    synth.INTRINSICS.setdefault("ragged", (150, 97, 125.0, 126.0, 75.3, 48.1))
+    cam = synth.make_camera(kind, rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))
+    sc = synth.make_scene(P, cam, seed=seed, anisotropic=anisotropic, layered=layered)
+    g = torch.Generator().manual_seed(3 + seed)
+    wc = torch.randn(3, cam.H, cam.W, generator=g) / (cam.H * cam.W)
+    wd = torch.randn(1, cam.H, cam.W, generator=g) / (cam.H * cam.W)
+    return cam, sc, torch.tensor([0.1, 0.2, 0.3]), wc, wd
+
+
+@pytest.mark.parametrize("P,kind,seed,aniso,layered", [(1500, "tiny", 5, False, False), (900, "tiny", 6, True, True),
+                                                       (700, "ragged", 7, False, False)])
+def test_autograd_reference_matches_analytic_oracle(P, kind, seed, aniso, layered):
+    cam, sc, bg, wc, wd = _case(P, kind, seed, aniso, layered)
+    view, proj, proj_raw, campos = cam.matrices()
+    n = lambda t: t.detach().numpy()
+    f = co.forward(n(sc["means3D"]), n(sc["scales"]), n(sc["rotations"]), n(sc["opacities"]), n(sc["colors"]), n(view),
+                   n(proj), n(campos), cam.W, cam.H, cam.tanfovx, cam.tanfovy, n(bg))
+    b = co.backward(f, n(sc["means3D"]), n(sc["scales"]), n(sc["rotations"]), n(view), n(proj), n(proj_raw), cam.W,
+                    cam.H, cam.tanfovx, cam.tanfovy, n(bg), n(wc), n(wd))
+    (color, depth, opacity, radii, nt), grads = tr.tracking_step(sc, view, proj, cam.W, cam.H, cam.tanfovx,
+                                                                 cam.tanfovy, bg, wc, wd)
+    assert np.array_equal(radii.numpy(), f["radii"])
+    assert (nt.numpy() != f["n_touched"]).mean() <= 1e-3          # a threshold decision may flip with the fp32 order
+    assert rel_inf(n(color), f["color"].reshape(n(color).shape)) <= 1e-5
+    assert rel_inf(n(depth), f["depth"].reshape(n(depth).shape)) <= 1e-5
+    assert rel_inf(n(opacity), f["opacity"].reshape(n(opacity).shape)) <= 1e-5
+    for k, kb in GRADS:
+        assert rel_inf(n(grads[k]).reshape(b[kb].shape), b[kb]) <= 1e-4, k
+
+
+@pytest.mark.gpu
+def test_cuda_matches_autograd_reference_c1(built):
+    """BASELINE.json config C1: 10 k Gaussians, 320x240, one step; CUDA kernels vs torch autograd on the host."""
+    from monogs_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    synth.INTRINSICS.setdefault("tum_half", (320, 240, 267.7, 269.6, 160.05, 123.8))
+    cam = synth.make_camera("tum_half", rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))
+    sc = synth.make_scene(10_000, cam, seed=0)
+    g = torch.Generator().manual_seed(3)
+    wc = torch.randn(3, cam.H, cam.W, generator=g) / (cam.H * cam.W)
+    wd = torch.randn(1, cam.H, cam.W, generator=g) / (cam.H * cam.W)
+    bg = torch.tensor([0.1, 0.2, 0.3])
+    view, proj, proj_raw, campos = cam.matrices()
+    (color, depth, opacity, radii, nt), grads = tr.tracking_step(sc, view, proj, cam.W, cam.H, cam.tanfovx,
+                                                                 cam.tanfovy, bg, wc, wd)
+    dev = "cuda"
+    leaves = {k: sc[k].to(dev).requires_grad_(True) for k in ("means3D", "colors", "opacities", "scales", "rotations")}
+    s = GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, bg.to(dev), 1.0, view.to(dev),
+                                      proj.to(dev), proj_raw.to(dev), 0, campos.to(dev), False, False)
+    c, r, d, o, t = GaussianRasterizer(s)(means3D=leaves["means3D"], means2D=torch.zeros_like(leaves["means3D"]),
+                                          opacities=leaves["opacities"], colors_precomp=leaves["colors"],
+                                          scales=leaves["scales"], rotations=leaves["rotations"],
+                                          theta=torch.zeros(3, device=dev), rho=torch.zeros(3, device=dev))
+    ((c * wc.to(dev)).sum() + (d * wd.to(dev)).sum()).backward()
+    assert torch.equal(r.cpu().to(torch.int64), radii)
+    assert (t.cpu().to(torch.int64) != nt).float().mean() <= 1e-3
+    n = lambda x: x.detach().cpu().numpy()
+    assert rel_inf(n(c), n(color)) <= 1e-5 and rel_inf(n(d), n(depth)) <= 1e-5 and rel_inf(n(o), n(opacity)) <= 1e-5
+    for k in ("means3D", "colors", "opacities", "scales", "rotations"):
+        assert rel_inf(n(leaves[k].grad), n(grads[k])) <= 1e-4, k
