@@ -10,8 +10,10 @@ The reference assembles it from ~40 framework ops, two of them sort-based `torch
 and four boolean-mask indexings; here the device side is 4 radix-select launches per median, a mask + stable
 compaction pair, one gather/unproject kernel, `distCUDA2` (csrc/knn.cu) and one finishing kernel, all through the
 C ABI (gsr_select_kth_f32, gsr_insert_select, gsr_insert_points, gsr_knn_dist2, gsr_insert_finish).  What stays on
-the host is what the reference also does there: reading the number of selected pixels (a boolean-mask indexing in the reference, :242-245) and `torch.randperm` on the host RNG
-(:256), so a seeded run keeps the same pixels.  No CPU fallback: CPU tensors raise.
+the host is what the reference also does there: reading the number of selected pixels (a boolean-mask indexing in
+the reference, :242-245) and `torch.randperm` on the host RNG (:256), so a seeded run keeps the same pixels
+(`rng="device"` draws on the GPU instead).  The intrinsics inverse and [R|T]^-1 (:163-165) are formed inside the
+gather kernel.  No CPU fallback: CPU tensors raise.
 """
 from __future__ import annotations
 

@@ -77,7 +77,6 @@ def test_graph_reports_capacity_overflow(built):
     tg = tracking.TrackingGraph(ci, sc["means3D"], sc["rotations"], sc["scales"], sc["opacities"], sc["colors"], bg,
                                 gt_rgb, gt_depth, R0=w2c[:3, :3].contiguous(), T0=w2c[:3, 3].contiguous(),
                                 capacity_factor=1.0)
-    tg.capacity_checked = tg.capacity
     near = cam.w2c.to(DEV)
     tg.step(near[:3, :3].contiguous(), near[:3, 3].contiguous())
     # the near pose has far more instances than the capacity captured for the far pose (+64 k slack) may hold
