@@ -22,7 +22,7 @@ ncufull)
 ncuother)
   CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
   $CMD > gpurun_out/plain3.log 2>&1 && \
-  ncu --set full --clock-control none --import-source on -k regex:"onesweep|preprocess_|gather_|tile_|chunk_|tau_|digit_" -s 13 -c 13 -f -o gpurun_out/prof_other $CMD > gpurun_out/ncu_other.log 2>&1 ;;
+  ncu --set full --clock-control none --import-source on -k regex:"onesweep|preprocess_|gather_|tile_|chunk_|tau_|digit_" -s 14 -c 14 -f -o gpurun_out/prof_other $CMD > gpurun_out/ncu_other.log 2>&1 ;;
 ncupre)
   CMD="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
   $CMD > gpurun_out/plain5.log 2>&1 && \
