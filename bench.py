@@ -692,6 +692,9 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl_name, "detail": wl.desc, "image": [wl.W, wl.H], "gaussians": wl.P,
                    "l2": "256 MiB flush write before every timed step (outside the event pairs)",
+                   "schedule": "render CTAs start heaviest tiles first: backward from this step's forward, forward from "
+                               "the previous step's per-tile work left in the image workspace (a hint only; "
+                               "GSR_FWD_TILE_ORDER=0 / GSR_TILE_ORDER=0 switch it off)",
                    "multi_gpu": ("mapping window: one keyframe per GPU; sum of the [P,16] window rows (14 gradient + 2 "
                                  "densification columns) over the ranks inside the step, exchange = "
                                  + getattr(getattr(stepper, "exchange", None), "mode", "all_reduce"))

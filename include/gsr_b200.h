@@ -62,7 +62,10 @@ const char* gsr_version(void);
 /* ---- workspace sizes (bytes). All workspaces need 256-byte alignment. -- */
 /* Per-Gaussian state written by forward and re-read by backward. */
 size_t gsr_geom_bytes(int P, int width, int height);
-/* Per-pixel state (final T, n_contrib) + per-tile ranges; saved for backward. */
+/* Per-pixel state (final T, n_contrib) + per-tile ranges and work counters; saved for backward. Re-using the same
+ * image workspace for consecutive forwards of nearly the same view (tracking / mapping iterations) lets the forward
+ * renderer schedule its heaviest tiles first from the previous call's per-tile work; whatever the workspace holds,
+ * only the CTA schedule depends on it, never a result (a fresh, uninitialised workspace is fine). */
 size_t gsr_image_bytes(int width, int height);
 /* Sorted instance list (Gaussian ids in tile|depth order); saved for backward. */
 size_t gsr_point_list_bytes(int64_t num_rendered);

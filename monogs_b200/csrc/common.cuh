@@ -145,6 +145,7 @@ struct ImageViews {
   uint2* ranges;         // [tiles]
   uint32_t* tile_work;   // [tiles] largest n_contrib of the tile (written by the forward renderer)
   uint32_t* tile_order;  // [tiles] tiles by descending tile_work: the backward renderer's CTA -> tile map
+  uint32_t* tile_order_fwd;  // [tiles] the same from the PREVIOUS forward's tile_work: the forward renderer's map
 };
 __host__ __device__ inline size_t carve_image(char* base, int W, int H, ImageViews* v) {
   size_t off = 0;
@@ -152,10 +153,10 @@ __host__ __device__ inline size_t carve_image(char* base, int W, int H, ImageVie
   size_t tiles = num_tiles(W, H);
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
   char* a = take(4 * N); char* b = take(4 * N); char* c = take(8 * tiles);
-  char* d = take(4 * tiles); char* e = take(4 * tiles);
+  char* d = take(4 * tiles); char* e = take(4 * tiles); char* f = take(4 * tiles);
   if (v) {
     v->final_T = (float*)a; v->n_contrib = (uint32_t*)b; v->ranges = (uint2*)c;
-    v->tile_work = (uint32_t*)d; v->tile_order = (uint32_t*)e;
+    v->tile_work = (uint32_t*)d; v->tile_order = (uint32_t*)e; v->tile_order_fwd = (uint32_t*)f;
   }
   return off;
 }

@@ -56,6 +56,8 @@ cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& i
                               float* out_opacity, int* n_touched);
 
 // render_bwd.cu
+// tile_order[0..n_tiles) = tiles by descending tile_work (any content of tile_work gives a valid permutation)
+cudaError_t launch_tile_order(cudaStream_t st, int n_tiles, const uint32_t* tile_work, uint32_t* tile_order);
 cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, const float* dL_dpix,
                               const float* dL_dpix_depth, const LossView& loss, float* packed);

@@ -381,6 +381,11 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 #endif
 }
 
+cudaError_t launch_tile_order(cudaStream_t st, int n_tiles, const uint32_t* tile_work, uint32_t* tile_order) {
+  count_launch(); launch_k(tile_order_kernel, 1, TO_THREADS, 0, st, n_tiles, tile_work, tile_order);
+  return cudaGetLastError();
+}
+
 static bool tile_order_enabled() {  // GSR_TILE_ORDER=0: linear CTA -> tile map (A/B measurements)
   static const bool on = [] { const char* e = getenv("GSR_TILE_ORDER"); return !(e && e[0] == '0'); }();
   return on;

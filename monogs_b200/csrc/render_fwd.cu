@@ -16,6 +16,7 @@
 // The blended quantities follow the reference's fp32 operation order exactly
 // (explicit fmul/ffma), so final_T, n_contrib and the integer n_touched are
 // bit-identical and colour/depth/opacity agree to the last bit.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -68,7 +69,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   int tiles_x, const float4* __restrict__ rec_a, const float4* __restrict__ rec_b,
                   const float4* __restrict__ rec_c, const float* __restrict__ bg, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_depth,
-                  float* __restrict__ out_opacity, int* __restrict__ n_touched, uint32_t* __restrict__ tile_work) {
+                  float* __restrict__ out_opacity, int* __restrict__ n_touched, uint32_t* __restrict__ tile_work,
+                  const uint32_t* __restrict__ tile_order) {
   pdl_launch_dependents();
 #ifdef GSR_CTA_TRACE
   const unsigned long long t_enter = trace_now();
@@ -80,11 +82,16 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   __shared__ __align__(16) RfStage stage[2];
 
   const int tid = threadIdx.x, lane = tid & 31;
-  const int tile_y = blockIdx.y / RF_SUB;
+  int tile_y = blockIdx.y / RF_SUB, tile_x = blockIdx.x;
+  if (RF_SUB == 1 && tile_order) {  // heaviest tiles (of the previous forward on this workspace) first
+    const uint32_t t = tile_order[blockIdx.y * gridDim.x + blockIdx.x];
+    tile_y = (int)(t / (uint32_t)tiles_x);
+    tile_x = (int)(t - (uint32_t)tile_y * (uint32_t)tiles_x);
+  }
   const int w = (blockIdx.y % RF_SUB) * RF_WARPS + (tid >> 5);   // warp rectangle within the tile
-  const int tile = tile_y * tiles_x + blockIdx.x;
+  const int tile = tile_y * tiles_x + tile_x;
   // warp sub-rectangle: 2 columns x 4 rows of 8x4-pixel rectangles
-  const int wx0 = blockIdx.x * TILE_X + (w & 1) * 8;
+  const int wx0 = tile_x * TILE_X + (w & 1) * 8;
   const int wy0 = tile_y * TILE_Y + (w >> 1) * 4;
   const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
   const bool inside = pxi < W && pyi < H;
@@ -238,9 +245,20 @@ cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& i
                               float* out_opacity, int* n_touched) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y * RF_SUB);
+  // The forward renderer starts the tiles that were heaviest in the PREVIOUS forward on this image workspace first
+  // (tracking / mapping iterate over nearly the same view; a tile's work is only known after it ran). A fresh
+  // workspace holds arbitrary values: any content sorts into a valid permutation, so only the schedule depends on
+  // it, never a result. GSR_FWD_TILE_ORDER=0 restores the linear CTA -> tile map (A/B measurements).
+  static const bool fwd_order = [] { const char* e = getenv("GSR_FWD_TILE_ORDER"); return !(e && e[0] == '0'); }();
+  const uint32_t* order = nullptr;
+  if (RF_SUB == 1 && fwd_order && tiles_x * tiles_y > 2 * 148) {
+    cudaError_t e = launch_tile_order(st, tiles_x * tiles_y, im.tile_work, im.tile_order_fwd);
+    if (e != cudaSuccess) return e;
+    order = im.tile_order_fwd;
+  }
   count_launch(); launch_k(render_fwd_kernel, grid, RF_THREADS, 0, st, im.ranges, point_list, W, H, tiles_x, g.rec_a, g.rec_b, g.rec_c,
                                                  bg, im.final_T, im.n_contrib, out_color, out_depth, out_opacity,
-                                                 n_touched, im.tile_work);
+                                                 n_touched, im.tile_work, order);
   return cudaGetLastError();
 }
 
