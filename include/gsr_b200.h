@@ -227,6 +227,10 @@ int gsr_backward_render(void* stream, int P, int width, int height, const float*
                         const void* geom_ws, const void* image_ws, const uint32_t* point_list,
                         int64_t num_rendered, const float* dL_dout_color, const float* dL_dout_depth,
                         void* scratch, int debug);
+/* gsr_backward_render with dL/dpixel formed in the tile renderer from a gsr_l1_loss descriptor (see gsr_backward_l1). */
+int gsr_backward_render_l1(void* stream, int P, int width, int height, const float* background,
+                           const void* geom_ws, const void* image_ws, const uint32_t* point_list,
+                           int64_t num_rendered, const gsr_l1_loss* loss, void* scratch, int debug);
 int gsr_backward_rows(void* stream, int P, int p_begin, int p_end, int width, int height,
                       const float* means3D, const float* scales, float scale_modifier,
                       const float* rotations, const float* viewmatrix, const float* projmatrix,

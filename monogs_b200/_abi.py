@@ -37,6 +37,7 @@ SIGNATURES = {
     "gsr_backward_l1": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, f32, f32,
                               vp, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32]),
     "gsr_backward_render": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, i64, vp, vp, vp, i32]),
+    "gsr_backward_render_l1": (i32, [vp, i32, i32, i32, vp, vp, vp, vp, i64, vp, vp, i32]),
     "gsr_backward_rows": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, f32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, i32,
                                 vp, vp, i32]),
     "gsr_backward_rows_marked": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, f32, vp, vp, vp, vp, f32, f32, vp, vp, vp,

@@ -414,6 +414,19 @@ int gsr_l1_loss_forward(void* stream, int kind, int width, int height, const flo
                               mask, grad_mask, exposure_a, exposure_b, lambda_rgb, (double*)scratch, out));
 }
 
+static int to_loss_view(const gsr_l1_loss* loss, LossView* lv) {
+  if (!loss || (loss->kind != GSR_LOSS_MAPPING && loss->kind != GSR_LOSS_TRACKING)) return GSR_EINVAL;
+  if (!loss->color || !loss->gt_rgb || !loss->out || (loss->gt_depth && !loss->depth)) return GSR_EINVAL;
+  if (loss->kind == GSR_LOSS_TRACKING && !loss->opacity) return GSR_EINVAL;
+  lv->kind = loss->kind;
+  lv->color = loss->color; lv->depth = loss->depth; lv->opacity = loss->opacity;
+  lv->gt_rgb = loss->gt_rgb; lv->gt_depth = loss->gt_depth;
+  lv->mask = loss->mask; lv->grad_mask = loss->grad_mask;
+  lv->exposure_a = loss->exposure_a; lv->exposure_b = loss->exposure_b;
+  lv->out = loss->out; lv->upstream = loss->upstream;
+  return GSR_OK;
+}
+
 int gsr_backward_l1(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,
                     const float* background, const float* means3D, const float* shs, const float* colors_precomp,
                     const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
@@ -423,16 +436,8 @@ int gsr_backward_l1(void* stream, int P, int sh_degree, int sh_coeffs, int width
                     const gsr_l1_loss* loss, void* scratch, float* dL_dmeans2D, float* dL_dcolors,
                     float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
                     float* dL_drotations, float* dL_dtau_per_gaussian, float* dL_dtau, int debug) {
-  if (!loss || (loss->kind != GSR_LOSS_MAPPING && loss->kind != GSR_LOSS_TRACKING)) return GSR_EINVAL;
-  if (!loss->color || !loss->gt_rgb || !loss->out || (loss->gt_depth && !loss->depth)) return GSR_EINVAL;
-  if (loss->kind == GSR_LOSS_TRACKING && !loss->opacity) return GSR_EINVAL;
   LossView lv{};
-  lv.kind = loss->kind;
-  lv.color = loss->color; lv.depth = loss->depth; lv.opacity = loss->opacity;
-  lv.gt_rgb = loss->gt_rgb; lv.gt_depth = loss->gt_depth;
-  lv.mask = loss->mask; lv.grad_mask = loss->grad_mask;
-  lv.exposure_a = loss->exposure_a; lv.exposure_b = loss->exposure_b;
-  lv.out = loss->out; lv.upstream = loss->upstream;
+  GSR_TRY(to_loss_view(loss, &lv));
   return backward_impl(stream, P, sh_degree, sh_coeffs, width, height, background, means3D, shs, colors_precomp,
                        scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw,
                        campos, tan_fovx, tan_fovy, radii, geom_ws, image_ws, point_list, num_rendered, nullptr,
@@ -440,9 +445,31 @@ int gsr_backward_l1(void* stream, int P, int sh_degree, int sh_coeffs, int width
                        dL_dscales, dL_drotations, dL_dtau_per_gaussian, dL_dtau, debug);
 }
 
+static int backward_render_impl(void* stream, int P, int width, int height, const float* background,
+                                const void* geom_ws, const void* image_ws, const uint32_t* point_list,
+                                int64_t num_rendered, const float* dL_dout_color, const float* dL_dout_depth,
+                                const LossView& loss, void* scratch, int debug);
+
 int gsr_backward_render(void* stream, int P, int width, int height, const float* background, const void* geom_ws,
                         const void* image_ws, const uint32_t* point_list, int64_t num_rendered,
                         const float* dL_dout_color, const float* dL_dout_depth, void* scratch, int debug) {
+  return backward_render_impl(stream, P, width, height, background, geom_ws, image_ws, point_list, num_rendered,
+                              dL_dout_color, dL_dout_depth, no_loss(), scratch, debug);
+}
+
+int gsr_backward_render_l1(void* stream, int P, int width, int height, const float* background, const void* geom_ws,
+                           const void* image_ws, const uint32_t* point_list, int64_t num_rendered,
+                           const gsr_l1_loss* loss, void* scratch, int debug) {
+  LossView lv{};
+  GSR_TRY(to_loss_view(loss, &lv));
+  return backward_render_impl(stream, P, width, height, background, geom_ws, image_ws, point_list, num_rendered,
+                              nullptr, nullptr, lv, scratch, debug);
+}
+
+static int backward_render_impl(void* stream, int P, int width, int height, const float* background,
+                                const void* geom_ws, const void* image_ws, const uint32_t* point_list,
+                                int64_t num_rendered, const float* dL_dout_color, const float* dL_dout_depth,
+                                const LossView& loss, void* scratch, int debug) {
   if (P < 0 || width <= 0 || height <= 0 || num_rendered < 0) return GSR_EINVAL;
   if (P == 0) return GSR_OK;
   if (!background || !geom_ws || !image_ws || !scratch) return GSR_EINVAL;
@@ -458,7 +485,7 @@ int gsr_backward_render(void* stream, int P, int width, int height, const float*
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
-                                    dL_dout_depth, no_loss(), bw.packed)));
+                                    dL_dout_depth, loss, bw.packed)));
   }
   return debug_sync(st, debug);
 }

@@ -234,7 +234,8 @@ def mark_visible(means3D, viewmatrix, projmatrix):
 def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotations, scale_modifier, viewmatrix,
                                       projmatrix, projmatrix_raw, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth,
                                       geomBuffer, R, point_list, imageBuffer, rows, accumulate, chunks=None,
-                                      chunk_done=None, want_means2D=False, debug=False, marks=None, rows_gate=None):
+                                      chunk_done=None, want_means2D=False, debug=False, marks=None, rows_gate=None,
+                                      l1_spec=None, image_hw=None):
     """Backward of one keyframe of the sharded mapping window (gsr_backward_render + gsr_backward_rows): the
     Gaussian gradients are written / added into `rows` f32[P,16] (layout: include/gsr_b200.h) range by range;
     `chunk_done(p0, p1)` is called right after each range has been enqueued (the caller starts its allreduce of
@@ -244,7 +245,10 @@ def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotati
     lib = _abi.load()
     P = int(means3D.size(0))
     dev = means3D.device
-    H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    if l1_spec is not None:   # fused L1 loss: dL/dpixel is formed inside the tile renderer (gsr_backward_render_l1)
+        H, W = int(image_hw[0]), int(image_hw[1])
+    else:
+        H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     if rows.shape != (P, 16) or rows.dtype != torch.float32 or not rows.is_contiguous():
         raise RuntimeError("rows must be a contiguous float32 [P,16] tensor")
     tau = torch.zeros(6, dtype=torch.float32, device=dev)
@@ -254,13 +258,21 @@ def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotati
     chunks = chunks or [(0, P)]
     with _on_device(dev):
         scratch = torch.empty(lib.gsr_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
-        gc, gd = _f32(dL_dout_color, "dL_dout_color"), _f32(dL_dout_depth, "dL_dout_depth")
+        gc = gd = None
+        if l1_spec is None:
+            gc, gd = _f32(dL_dout_color, "dL_dout_color"), _f32(dL_dout_depth, "dL_dout_depth")
         bg_c, m3, sc, ro = _f32(background, "bg"), _f32(means3D, "means3D"), _f32(scales, "scales"), _f32(rotations, "rotations")
         vm, pm, pr = _f32(viewmatrix, "viewmatrix"), _f32(projmatrix, "projmatrix"), _f32(projmatrix_raw, "projmatrix_raw")
         radii_c = radii.contiguous()
         st = _stream()
-        rc = lib.gsr_backward_render(st, P, W, H, _ptr(bg_c), geomBuffer.data_ptr(), imageBuffer.data_ptr(),
-                                     _ptr(point_list), int(R), _ptr(gc), _ptr(gd), scratch.data_ptr(), int(bool(debug)))
+        if l1_spec is not None:
+            rc = lib.gsr_backward_render_l1(st, P, W, H, _ptr(bg_c), geomBuffer.data_ptr(), imageBuffer.data_ptr(),
+                                            _ptr(point_list), int(R), C.byref(l1_spec), scratch.data_ptr(),
+                                            int(bool(debug)))
+        else:
+            rc = lib.gsr_backward_render(st, P, W, H, _ptr(bg_c), geomBuffer.data_ptr(), imageBuffer.data_ptr(),
+                                         _ptr(point_list), int(R), _ptr(gc), _ptr(gd), scratch.data_ptr(),
+                                         int(bool(debug)))
         _abi.check(rc, "gsr_backward_render")
         if rows_gate is not None:  # multi-stream window: the row accumulation is ordered across keyframes
             torch.cuda.current_stream(dev).wait_event(rows_gate)

@@ -385,18 +385,28 @@ def mapping_loss_grad(color, depth, gt_image, gt_depth):
 
 
 def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
-                        loss_grad: Optional[Callable] = None) -> RenderFn:
+                        loss_grad: Optional[Callable] = None, fused_loss: Optional[bool] = None) -> RenderFn:
     """Product backend: the sm_100a rasterizer through the `_C` mirror (C ABI). The per-Gaussian half of the
     backward writes 64-byte window rows straight into `flat` (gsr_backward_rows), range by range.
 
     cameras[k] is a synth.Camera-like object with .matrices(device), .W, .H, .tanfovx, .tanfovy; targets[k] =
     (gt_image[3,H,W], gt_depth[1,H,W]).  loss_grad(color, depth, gt_image, gt_depth) -> (loss, dL_dcolor,
-    dL_ddepth); default = mapping_loss_grad.
+    dL_ddepth) is a custom loss evaluated with framework ops.  Without one (fused_loss defaults to True then) the
+    mapping loss 0.9 L1(rgb) + 0.1 L1(depth over gt_depth > 0) (get_loss_mapping, utils/slam_utils.py:101-146) is
+    reduced by ONE kernel (gsr_l1_loss_forward) and its gradient is formed inside the backward tile renderer
+    (gsr_backward_render_l1): no gradient images, ~12 framework ops less per keyframe -- the Python window loop is
+    host-bound at tracking-sized maps.
     """
+    import ctypes as C
+
+    from . import _abi
     from .diff_gaussian_rasterization import _C
 
     cached = {}
     lg = loss_grad or mapping_loss_grad
+    fused = (loss_grad is None) if fused_loss is None else bool(fused_loss)
+    if fused and loss_grad is not None:
+        raise ValueError("fused_loss=True evaluates the built-in mapping loss; it cannot be combined with loss_grad")
 
     def render(k, params, flat, accumulate, chunks, chunk_done, marks=None, rows_gate=None) -> KeyframeResult:
         cam = cameras[k]
@@ -409,11 +419,30 @@ def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
             bg, params["means3D"], params["colors"], params["opacities"], params["scales"], params["rotations"], 1.0,
             e, view, proj, proj_raw, cam.tanfovx, cam.tanfovy, cam.H, cam.W, e, 0, campos, False, False)
         gt_image, gt_depth = targets[k]
-        loss, dcol, ddep = lg(color, depth, gt_image, gt_depth)
-        tau, _ = _C.rasterize_gaussians_backward_rows(
-            bg, params["means3D"], radii, params["scales"], params["rotations"], 1.0, view, proj, proj_raw,
-            cam.tanfovx, cam.tanfovy, dcol.contiguous(), ddep.contiguous(), geom, R, plist, img, flat, accumulate,
-            chunks=chunks, chunk_done=chunk_done, marks=marks, rows_gate=rows_gate)
+        kw = dict(chunks=chunks, chunk_done=chunk_done, marks=marks, rows_gate=rows_gate)
+        if fused:
+            lib = _abi.load()
+            terms = torch.empty(8, dtype=torch.float32, device=dev)
+            acc = torch.empty(8, dtype=torch.float64, device=dev)
+            gi, gd = _C._f32(gt_image, "gt_image"), _C._f32(gt_depth, "gt_depth")
+            with _C._on_device(dev):
+                rc = lib.gsr_l1_loss_forward(_C._stream(), _abi.LOSS_MAPPING, cam.W, cam.H, color.data_ptr(),
+                                             depth.data_ptr(), opacity.data_ptr(), gi.data_ptr(), gd.data_ptr(),
+                                             None, None, None, None, 0.9, acc.data_ptr(), terms.data_ptr())
+            _abi.check(rc, "gsr_l1_loss_forward")
+            spec = _abi.L1LossSpec(_abi.LOSS_MAPPING, color.data_ptr(), depth.data_ptr(), opacity.data_ptr(),
+                                   gi.data_ptr(), gd.data_ptr(), None, None, None, None, terms.data_ptr(), None)
+            tau, _ = _C.rasterize_gaussians_backward_rows(
+                bg, params["means3D"], radii, params["scales"], params["rotations"], 1.0, view, proj, proj_raw,
+                cam.tanfovx, cam.tanfovy, None, None, geom, R, plist, img, flat, accumulate, l1_spec=spec,
+                image_hw=(cam.H, cam.W), **kw)
+            loss = terms[0]
+        else:
+            loss, dcol, ddep = lg(color, depth, gt_image, gt_depth)
+            tau, _ = _C.rasterize_gaussians_backward_rows(
+                bg, params["means3D"], radii, params["scales"], params["rotations"], 1.0, view, proj, proj_raw,
+                cam.tanfovx, cam.tanfovy, dcol.contiguous(), ddep.contiguous(), geom, R, plist, img, flat, accumulate,
+                **kw)
         return KeyframeResult(index=k, radii=radii, n_touched=n_touched, grad_tau=tau, loss=loss)
 
     render.accepts_marks = True
