@@ -361,12 +361,15 @@ static int backward_impl(void* stream, int P, int sh_degree, int sh_coeffs, int 
   carve_image((char*)image_ws, width, height, &im);
   BackwardViews bw;
   carve_backward((char*)scratch, P, &bw);
-  GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, carve_backward(nullptr, P, nullptr), st)));
+  // the partial-gradient scratch is zeroed by the backward renderer's prologue kernel (alongside its tile ordering)
+  const size_t zero_bytes = carve_backward(nullptr, P, nullptr);
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
-                                    dL_dout_depth, loss, bw.packed)));
+                                    dL_dout_depth, loss, bw.packed, zero_bytes)));
     GSR_TRY(debug_sync(st, debug));
+  } else {
+    GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, zero_bytes, st)));
   }
   const float* shs_used = colors_precomp ? nullptr : shs;
   StageTimer tm_pb(st, GSR_STAGE_PREPROCESS_BWD);
@@ -481,11 +484,13 @@ static int backward_render_impl(void* stream, int P, int width, int height, cons
   carve_image((char*)image_ws, width, height, &im);
   BackwardViews bw;
   carve_backward((char*)scratch, P, &bw);
-  GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, carve_backward(nullptr, P, nullptr), st)));
+  const size_t zero_bytes = carve_backward(nullptr, P, nullptr);
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
-                                    dL_dout_depth, loss, bw.packed)));
+                                    dL_dout_depth, loss, bw.packed, zero_bytes)));
+  } else {
+    GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, zero_bytes, st)));
   }
   return debug_sync(st, debug);
 }

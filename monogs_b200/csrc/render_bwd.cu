@@ -115,10 +115,20 @@ GSR_DEVINL int owner_slot(int lane) {
 // (measured on the headline scene: the backward renderer's last CTA started at 54 % of the kernel's span and ran
 // for up to half of it). Order inside a bin is arbitrary -- it only affects scheduling.
 constexpr int TO_THREADS = 1024;
+// zero_ptr / zero_n16: optional buffer (the backward's partial-gradient scratch) cleared by the OTHER CTAs of the
+// launch while CTA 0 sorts -- one launch instead of a memset node (which also breaks the PDL chain) + a 1-CTA kernel.
 __global__ void __launch_bounds__(TO_THREADS)
-tile_order_kernel(int n_tiles, const uint32_t* __restrict__ tile_work, uint32_t* __restrict__ tile_order) {
+tile_order_kernel(int n_tiles, const uint32_t* __restrict__ tile_work, uint32_t* __restrict__ tile_order,
+                  float4* __restrict__ zero_ptr, size_t zero_n16) {
   pdl_launch_dependents();
   pdl_wait();
+  if (blockIdx.x > 0) {
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (size_t i = (size_t)(blockIdx.x - 1) * TO_THREADS + threadIdx.x; i < zero_n16;
+         i += (size_t)(gridDim.x - 1) * TO_THREADS)
+      zero_ptr[i] = z;
+    return;
+  }
   __shared__ uint32_t s_bin[TO_THREADS];
   __shared__ uint32_t s_warp[TO_THREADS / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -382,7 +392,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 }
 
 cudaError_t launch_tile_order(cudaStream_t st, int n_tiles, const uint32_t* tile_work, uint32_t* tile_order) {
-  count_launch(); launch_k(tile_order_kernel, 1, TO_THREADS, 0, st, n_tiles, tile_work, tile_order);
+  count_launch(); launch_k(tile_order_kernel, 1, TO_THREADS, 0, st, n_tiles, tile_work, tile_order, (float4*)nullptr,
+                           (size_t)0);
   return cudaGetLastError();
 }
 
@@ -393,13 +404,21 @@ static bool tile_order_enabled() {  // GSR_TILE_ORDER=0: linear CTA -> tile map 
 
 cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, const float* dL_dpix,
-                              const float* dL_dpix_depth, const LossView& loss, float* packed) {
+                              const float* dL_dpix_depth, const LossView& loss, float* packed, size_t zero_bytes) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y * RB_SUB);
   const uint32_t* order = nullptr;
   if (RB_SUB == 1 && tile_order_enabled() && tiles_x * tiles_y > 2 * 148) {
-    count_launch(); launch_k(tile_order_kernel, 1, TO_THREADS, 0, st, tiles_x * tiles_y, (const uint32_t*)im.tile_work, im.tile_order);
+    const bool z = zero_bytes > 0 && zero_bytes % 16 == 0;
+    count_launch(); launch_k(tile_order_kernel, z ? 1 + 2 * 148 : 1, TO_THREADS, 0, st, tiles_x * tiles_y,
+                             (const uint32_t*)im.tile_work, im.tile_order, reinterpret_cast<float4*>(packed),
+                             z ? zero_bytes / 16 : (size_t)0);
+    if (z) zero_bytes = 0;
     order = im.tile_order;
+  }
+  if (zero_bytes > 0) {
+    cudaError_t e = cudaMemsetAsync(packed, 0, zero_bytes, st);
+    if (e != cudaSuccess) return e;
   }
   count_launch(); launch_k(render_bwd_kernel, grid, RB_THREADS, 0, st, im.ranges, point_list, W, H, tiles_x, bg, g.rec_a, g.rec_b,
                                                  g.rec_c, im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, loss, packed, order);
