@@ -67,3 +67,28 @@ def test_product_package_never_imports_oracle():
     root = pathlib.Path(monogs_b200.__file__).parent
     for p in root.rglob("*.py"):
         assert not re.search(r"^\s*(from|import)\s+oracle", p.read_text(), flags=re.M), p
+
+
+def test_tracking_graph_rejects_cpu_tensors():
+    import types
+    import torch
+    from monogs_b200 import tracking
+    ci = types.SimpleNamespace(fx=torch.tensor([100.0]), fy=torch.tensor([100.0]), cx=8.0, cy=8.0, width=16, height=16)
+    z = torch.zeros
+    with pytest.raises(RuntimeError):
+        tracking.TrackingGraph(ci, z(4, 3), z(4, 4), z(4, 3), z(4, 1), z(4, 3), z(3), z(3, 16, 16))
+
+
+def test_window_chunks_cover_the_rows_in_order():
+    from monogs_b200 import window
+    for P in (0, 1, 4095, 4096, 100_000, 1_000_003):
+        for n in (1, 2, 4, 7):
+            ch = window.window_chunks(P, n)
+            if P == 0:
+                assert ch == []
+                continue
+            assert ch[0][0] == 0 and ch[-1][1] == P
+            assert all(a[1] == b[0] for a, b in zip(ch[:-1], ch[1:]))          # contiguous, ascending
+            assert all(c[0] % 256 == 0 and c[1] > c[0] for c in ch)            # gsr_backward_rows needs 256-aligned starts
+    sl = window.column_slices()
+    assert sum(s.stop - s.start for s in sl.values()) == window.N_COLS == 16
