@@ -196,6 +196,11 @@ int gsr_l1_loss_forward(void* stream, int kind, int width, int height, const flo
                         const float* gt_depth, const uint8_t* mask, const uint8_t* grad_mask,
                         const float* exposure_a, const float* exposure_b, float lambda_rgb,
                         void* scratch, float* out);
+/* The gradient images gsr_backward_l1 forms on the fly, written out: dL_dcolor[3,H,W] and dL_ddepth[1,H,W]
+ * (either may be NULL) = upstream * d loss / d(color, depth) -- what autograd hands the rasterizer's backward after
+ * get_loss_mapping / get_loss_tracking (utils/slam_utils.py:58-146). Same device code as the fused path. */
+int gsr_l1_loss_grad(void* stream, int width, int height, const gsr_l1_loss* loss, float* dL_dcolor,
+                     float* dL_ddepth);
 int gsr_backward_l1(void* stream, int P, int sh_degree, int sh_coeffs,
                     int width, int height, const float* background,
                     const float* means3D, const float* shs,

@@ -36,8 +36,47 @@ struct HostSlot {
   unsigned long long total;
   int error_flag;
 };
+// The forward's one host read (num_rendered + prefilter flag) goes through a pinned slot + event taken from a
+// pool, one per forward IN FLIGHT and per device: concurrent forwards (several streams, threads or devices of one
+// process) neither share a slot nor serialise on a lock while the host waits. The mutex only guards the free list.
+struct ReadSlot {
+  HostSlot* pinned = nullptr;
+  cudaEvent_t ev = nullptr;
+  int device = -1;
+};
 std::mutex g_mu;
-HostSlot* g_pinned = nullptr;
+std::vector<ReadSlot> g_free_slots;
+int acquire_read_slot(ReadSlot* out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (size_t i = 0; i < g_free_slots.size(); ++i)
+      if (g_free_slots[i].device == dev) {
+        *out = g_free_slots[i];
+        g_free_slots[i] = g_free_slots.back();
+        g_free_slots.pop_back();
+        return GSR_OK;
+      }
+  }
+  ReadSlot s;
+  s.device = dev;
+  e = cudaHostAlloc((void**)&s.pinned, sizeof(HostSlot), cudaHostAllocDefault);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaEventCreateWithFlags(&s.ev, cudaEventDisableTiming);  // bound to the CURRENT device = the stream's
+  if (e != cudaSuccess) { cudaFreeHost(s.pinned); return (int)e; }
+  *out = s;
+  return GSR_OK;
+}
+struct ReadSlotGuard {  // returns the slot to the pool on every exit path
+  ReadSlot s;
+  ~ReadSlotGuard() {
+    if (!s.pinned) return;
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_free_slots.push_back(s);
+  }
+};
 
 int check(cudaError_t e) { return e == cudaSuccess ? GSR_OK : (int)e; }
 int debug_sync(cudaStream_t st, int debug) {
@@ -209,22 +248,15 @@ static int enqueue_render(cudaStream_t st, int P, int width, int height, const f
   return debug_sync(st, debug);
 }
 
-// num_rendered + prefilter flag -> pinned host slot; returns after the two copies have completed on `ev`.
-struct HostRead {
-  std::unique_lock<std::mutex> lk;
-  cudaEvent_t ev = nullptr;
-};
-static cudaEvent_t g_read_event = nullptr;
-static int enqueue_total_read(cudaStream_t st, const GeomViews& g) {
-  if (!g_pinned) GSR_TRY(check(cudaHostAlloc((void**)&g_pinned, sizeof(HostSlot), cudaHostAllocDefault)));
-  if (!g_read_event) GSR_TRY(check(cudaEventCreateWithFlags(&g_read_event, cudaEventDisableTiming)));
-  GSR_TRY(check(cudaMemcpyAsync(&g_pinned->total, g.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st)));
-  GSR_TRY(check(cudaMemcpyAsync(&g_pinned->error_flag, g.error_flag, sizeof(int), cudaMemcpyDeviceToHost, st)));
-  return check(cudaEventRecord(g_read_event, st));
+// num_rendered + prefilter flag -> the slot's pinned words; `finish` waits for the two copies on the slot's event.
+static int enqueue_total_read(cudaStream_t st, const GeomViews& g, const ReadSlot& rs) {
+  GSR_TRY(check(cudaMemcpyAsync(&rs.pinned->total, g.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st)));
+  GSR_TRY(check(cudaMemcpyAsync(&rs.pinned->error_flag, g.error_flag, sizeof(int), cudaMemcpyDeviceToHost, st)));
+  return check(cudaEventRecord(rs.ev, st));
 }
-static int finish_total_read(int64_t* num_rendered) {
-  GSR_TRY(check(cudaEventSynchronize(g_read_event)));
-  const HostSlot slot = *g_pinned;
+static int finish_total_read(const ReadSlot& rs, int64_t* num_rendered) {
+  GSR_TRY(check(cudaEventSynchronize(rs.ev)));
+  const HostSlot slot = *rs.pinned;
   if (slot.error_flag) return GSR_EPREFILTER;
   if (slot.total >= (1ull << 30)) return GSR_EOVERFLOW;
   *num_rendered = (int64_t)slot.total;
@@ -250,9 +282,10 @@ int gsr_forward_plan(void* stream, int P, int sh_degree, int sh_coeffs, int widt
                        scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy,
                        prefiltered, radii, (char*)geom_ws, g, debug));
   // the one host read of the forward (rasterizer_impl.cu:284)
-  std::lock_guard<std::mutex> lk(g_mu);
-  GSR_TRY(enqueue_total_read(st, g));
-  return finish_total_read(num_rendered);
+  ReadSlotGuard rs;
+  GSR_TRY(acquire_read_slot(&rs.s));
+  GSR_TRY(enqueue_total_read(st, g, rs.s));
+  return finish_total_read(rs.s, num_rendered);
 }
 
 int gsr_forward_render(void* stream, int P, int width, int height, const float* background, const int* radii,
@@ -324,12 +357,13 @@ int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs, int width, in
   GSR_TRY(enqueue_plan(st, P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
                        scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy,
                        prefiltered, radii, (char*)geom_ws, g, debug));
-  std::lock_guard<std::mutex> lk(g_mu);
-  GSR_TRY(enqueue_total_read(st, g));
+  ReadSlotGuard rs;
+  GSR_TRY(acquire_read_slot(&rs.s));
+  GSR_TRY(enqueue_total_read(st, g, rs.s));
   // everything downstream is enqueued BEFORE the host waits for num_rendered: the GPU never idles on the read
   GSR_TRY(enqueue_render(st, P, width, height, background, g, im, (char*)binning_ws, point_list, capacity, g.total,
                          out_color, out_depth, out_opacity, n_touched, debug));
-  GSR_TRY(finish_total_read(num_rendered));
+  GSR_TRY(finish_total_read(rs.s, num_rendered));
   return *num_rendered > capacity ? GSR_ECAPACITY : GSR_OK;
 }
 
@@ -428,6 +462,14 @@ static int to_loss_view(const gsr_l1_loss* loss, LossView* lv) {
   lv->exposure_a = loss->exposure_a; lv->exposure_b = loss->exposure_b;
   lv->out = loss->out; lv->upstream = loss->upstream;
   return GSR_OK;
+}
+
+int gsr_l1_loss_grad(void* stream, int width, int height, const gsr_l1_loss* loss, float* dL_dcolor,
+                     float* dL_ddepth) {
+  if (width <= 0 || height <= 0 || (!dL_dcolor && !dL_ddepth)) return GSR_EINVAL;
+  LossView lv{};
+  GSR_TRY(to_loss_view(loss, &lv));
+  return check(launch_l1_loss_grad((cudaStream_t)stream, width, height, lv, dL_dcolor, dL_ddepth));
 }
 
 int gsr_backward_l1(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height,

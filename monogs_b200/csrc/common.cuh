@@ -309,6 +309,34 @@ struct LossView {
   const float* upstream;                                           // dL/dloss (device scalar) or NULL = 1
 };
 
+#ifdef __CUDACC__
+// dL/d(colour rgb, depth) of pixel `pix` for the fused L1 losses (the per-pixel half of loss.cu's reduction):
+//   dL/dI_c = up * k_rgb * sign(e^a I_c + b - gt_c) on the masked pixels, dL/dD = up * k_d * sign(D - gtD) on the
+//   valid-depth pixels (k_rgb = out[3] has e^a folded in, k_d = out[4]).
+// Used by the backward tile renderer's prologue and by gsr_l1_loss_grad, so both form the very same numbers.
+__device__ __forceinline__ void loss_pixel_grad(const LossView& loss, size_t pix, size_t HW, float& dpr, float& dpg,
+                                                float& dpb, float& dpd) {
+  dpr = dpg = dpb = dpd = 0.0f;
+  const float up = loss.upstream ? *loss.upstream : 1.0f;
+  const float ea = loss.exposure_a ? expf(*loss.exposure_a) : 1.0f;
+  const float eb = loss.exposure_b ? *loss.exposure_b : 0.0f;
+  const bool om = loss.kind == GSR_LOSS_TRACKING ? (loss.opacity[pix] > 0.99f) : true;
+  bool m = loss.mask ? loss.mask[pix] != 0 : true;
+  if (loss.kind == GSR_LOSS_TRACKING) m = m && om && (loss.grad_mask ? loss.grad_mask[pix] != 0 : true);
+  auto sgn = [](float d) { return d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f); };
+  if (m) {
+    const float k = up * loss.out[3];
+    dpr = k * sgn(ea * loss.color[pix] + eb - loss.gt_rgb[pix]);
+    dpg = k * sgn(ea * loss.color[HW + pix] + eb - loss.gt_rgb[HW + pix]);
+    dpb = k * sgn(ea * loss.color[2 * HW + pix] + eb - loss.gt_rgb[2 * HW + pix]);
+  }
+  if (loss.gt_depth) {
+    const float gd = loss.gt_depth[pix];
+    if (gd > 0.f && om) dpd = up * loss.out[4] * sgn(loss.depth[pix] - gd);
+  }
+}
+#endif
+
 // Camera constants passed by value (kernel parameter -> constant bank).
 struct CameraParams {
   float view[16];      // W2C^T, flat index 4*col+row  

@@ -69,6 +69,9 @@ cudaError_t launch_l1_loss(cudaStream_t st, int kind, int W, int H, const float*
                            const uint8_t* grad_mask, const float* exposure_a, const float* exposure_b,
                            float lambda_rgb, double* acc, float* out);
 
+cudaError_t launch_l1_loss_grad(cudaStream_t st, int W, int H, const LossView& loss, float* dL_dcolor,
+                                float* dL_ddepth);
+
 // preprocess_bwd.cu
 cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const float* means3D, const int* radii,
                                   const float* shs, const uint8_t* clamped, const float* scales,

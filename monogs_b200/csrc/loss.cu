@@ -100,6 +100,27 @@ __global__ void l1_loss_finish_kernel(int kind, int N, float lambda_rgb, const f
   out[7] = (float)mean_op;
 }
 
+// The gradient images the fused backward forms on the fly, materialised (callers that keep autograd; parity tests).
+__global__ void __launch_bounds__(256)
+l1_loss_grad_kernel(int N, LossView loss, float* __restrict__ dL_dcolor, float* __restrict__ dL_ddepth) {
+  pdl_launch_dependents();
+  pdl_wait();
+  for (int p = blockIdx.x * 256 + threadIdx.x; p < N; p += gridDim.x * 256) {
+    float r, g, b, d;
+    loss_pixel_grad(loss, (size_t)p, (size_t)N, r, g, b, d);
+    if (dL_dcolor) { dL_dcolor[p] = r; dL_dcolor[(size_t)N + p] = g; dL_dcolor[2 * (size_t)N + p] = b; }
+    if (dL_ddepth) dL_ddepth[p] = d;
+  }
+}
+
+cudaError_t launch_l1_loss_grad(cudaStream_t st, int W, int H, const LossView& loss, float* dL_dcolor,
+                                float* dL_ddepth) {
+  const int N = W * H;
+  count_launch();
+  launch_k(l1_loss_grad_kernel, min(148 * 8, (N + 255) / 256), 256, 0, st, N, loss, dL_dcolor, dL_ddepth);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_l1_loss(cudaStream_t st, int kind, int W, int H, const float* color, const float* depth,
                            const float* opacity, const float* gt_rgb, const float* gt_depth, const uint8_t* mask,
                            const uint8_t* grad_mask, const float* exposure_a, const float* exposure_b,

@@ -212,25 +212,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     if (dL_dpix) { dpr = dL_dpix[pix]; dpg = dL_dpix[HW + pix]; dpb = dL_dpix[2 * HW + pix]; }
     if (dL_dpix_depth) dpd = dL_dpix_depth[pix];
   } else if (inside) {
-    // fused L1 loss gradient (loss.cu): dL/dI_c = up * k_rgb * sign(e^a I_c + b - gt_c) on the masked pixels,
-    // dL/dD = up * k_d * sign(D - gtD) on the valid-depth pixels
-    const float up = loss.upstream ? *loss.upstream : 1.0f;
-    const float ea = loss.exposure_a ? expf(*loss.exposure_a) : 1.0f;
-    const float eb = loss.exposure_b ? *loss.exposure_b : 0.0f;
-    const bool om = loss.kind == GSR_LOSS_TRACKING ? (loss.opacity[pix] > 0.99f) : true;
-    bool m = loss.mask ? loss.mask[pix] != 0 : true;
-    if (loss.kind == GSR_LOSS_TRACKING) m = m && om && (loss.grad_mask ? loss.grad_mask[pix] != 0 : true);
-    auto sgn = [](float d) { return d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f); };
-    if (m) {
-      const float k = up * loss.out[3];
-      dpr = k * sgn(ea * loss.color[pix] + eb - loss.gt_rgb[pix]);
-      dpg = k * sgn(ea * loss.color[HW + pix] + eb - loss.gt_rgb[HW + pix]);
-      dpb = k * sgn(ea * loss.color[2 * HW + pix] + eb - loss.gt_rgb[2 * HW + pix]);
-    }
-    if (loss.gt_depth) {
-      const float gd = loss.gt_depth[pix];
-      if (gd > 0.f && om) dpd = up * loss.out[4] * sgn(loss.depth[pix] - gd);
-    }
+    loss_pixel_grad(loss, pix, HW, dpr, dpg, dpb, dpd);  // fused L1 loss gradient (loss.cu)
   }
   const float bg_dot_dpixel = bg[0] * dpr + bg[1] * dpg + bg[2] * dpb;
 

@@ -42,6 +42,45 @@ def _scalar(t):
     return t.detach().reshape(-1)[:1].to(torch.float32).contiguous()
 
 
+def l1_loss_images(kind, color, depth, opacity, gt_rgb, gt_depth=None, mask=None, grad_mask=None, exposure_a=None,
+                   exposure_b=None, lambda_rgb=0.9, upstream=None, want_grads=True):
+    """The callers' loss on given images, without the rasterizer: -> (terms f32[8], dL_dcolor [3,H,W], dL_ddepth
+    [1,H,W]).  terms = {loss, l1_rgb, l1_depth, k_rgb, k_depth, dL/da, dL/db, mean opacity} (gsr_l1_loss_forward);
+    the two images are upstream * d loss / d(color, depth) exactly as the fused backward forms them per pixel
+    (gsr_l1_loss_grad) -- i.e. what autograd would hand the rasterizer after get_loss_mapping / get_loss_tracking
+    (utils/slam_utils.py:58-146)."""
+    if kind not in KINDS:
+        raise ValueError(f"kind must be one of {sorted(KINDS)}")
+    lib = _abi.load()
+    color = _C._f32(color, "color")
+    H, W = int(color.shape[-2]), int(color.shape[-1])
+    dev = color.device
+    depth_c = None if depth is None else _C._f32(depth, "depth")
+    opac_c = None if opacity is None else _C._f32(opacity, "opacity")
+    gt_rgb_c = _C._f32(gt_rgb, "gt_rgb")
+    gt_depth_c = None if gt_depth is None else _C._f32(gt_depth, "gt_depth")
+    mask_c, gmask_c = _u8(mask, "mask", H, W), _u8(grad_mask, "grad_mask", H, W)
+    ea, eb = _scalar(exposure_a), _scalar(exposure_b)
+    up = None if upstream is None else upstream.detach().reshape(1).to(torch.float32).contiguous()
+    out = torch.empty(8, dtype=torch.float32, device=dev)
+    acc = torch.empty(8, dtype=torch.float64, device=dev)
+    p = _C._ptr
+    with _C._on_device(dev):
+        rc = lib.gsr_l1_loss_forward(_C._stream(), KINDS[kind], W, H, color.data_ptr(), p(depth_c), p(opac_c),
+                                     p(gt_rgb_c), p(gt_depth_c), p(mask_c), p(gmask_c), p(ea), p(eb),
+                                     float(lambda_rgb), acc.data_ptr(), out.data_ptr())
+        _abi.check(rc, "gsr_l1_loss_forward")
+        if not want_grads:
+            return out, None, None
+        spec = _abi.L1LossSpec(KINDS[kind], color.data_ptr(), p(depth_c), p(opac_c), p(gt_rgb_c), p(gt_depth_c),
+                               p(mask_c), p(gmask_c), p(ea), p(eb), out.data_ptr(), p(up))
+        d_color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+        d_depth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
+        rc = lib.gsr_l1_loss_grad(_C._stream(), W, H, C.byref(spec), d_color.data_ptr(), d_depth.data_ptr())
+    _abi.check(rc, "gsr_l1_loss_grad")
+    return out, d_color, d_depth
+
+
 class _RenderL1(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,

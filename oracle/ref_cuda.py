@@ -17,6 +17,20 @@ import torch
 _LIB = Path(__file__).resolve().parent / "_ref" / "libref_dgr.so"
 _lib = None
 vp, i32, f32 = C.c_void_p, C.c_int, C.c_float
+# Saved-state slots of the shim (oracle/ref_shim.cu): with a ring of n > 1 every forward takes the next slot and
+# returns its number in the `geomBuffer` position, the place where the reference keeps that state
+# (diff_gaussian_rasterization/__init__.py:104); the backward then consumes the slot it is handed. n = 1 (default)
+# keeps the one-state behaviour: backward consumes the last forward.
+_ring = 1
+_next_slot = 0
+
+
+def set_ring(n: int) -> None:
+    global _ring, _next_slot
+    if not 1 <= n <= 16:
+        raise ValueError("ring size must be 1..16")
+    _ring, _next_slot = n, 0
+    load().ref_set_slot(0)
 
 
 def available() -> bool:
@@ -42,6 +56,8 @@ def load():
         lib.ref_knn.restype = None
         lib.ref_knn.argtypes = [i32, vp, vp]
         lib.ref_sync.restype = i32
+        lib.ref_set_slot.restype = i32
+        lib.ref_set_slot.argtypes = [i32]
         _lib = lib
     return _lib
 
@@ -69,6 +85,13 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     radii = torch.zeros(P, dtype=torch.int32, device=dev)
     n_touched = torch.zeros(P, dtype=torch.int32, device=dev)
     R = 0
+    slot_t = None
+    if _ring > 1:
+        global _next_slot
+        slot = _next_slot
+        _next_slot = (_next_slot + 1) % _ring
+        lib.ref_set_slot(slot)
+        slot_t = torch.tensor([slot], dtype=torch.int32)
     if P != 0:
         M = int(sh.size(1)) if (sh is not None and sh.numel()) else 0
         keep = [_c(t) for t in (background, means3D, sh, colors, opacity, scales, rotations, cov3D_precomp,
@@ -78,7 +101,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                             float(scale_modifier), _p(ro), _p(cv), _p(vm), _p(pm), _p(cp), float(tan_fovx),
                             float(tan_fovy), int(bool(prefiltered)), color.data_ptr(), depth.data_ptr(),
                             opac.data_ptr(), radii.data_ptr(), n_touched.data_ptr(), int(bool(debug)))
-    return R, color, radii, None, None, None, depth, opac, n_touched
+    return R, color, radii, slot_t, None, None, depth, opac, n_touched
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
@@ -96,6 +119,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     dmeans3D, dmeans2D, dcolors, ddepths = z(P, 3), z(P, 3), z(P, 3), z(P, 1)
     dconic, dopacity, dcov3D, dsh = z(P, 2, 2), z(P, 1), z(P, 6), z(P, M, 3)
     dscales, drots, dtau = z(P, 3), z(P, 4), z(P, 6)
+    if isinstance(geomBuffer, torch.Tensor) and geomBuffer.numel() == 1:
+        lib.ref_set_slot(int(geomBuffer.item()))
     if P != 0:
         keep = [_c(t) for t in (background, means3D, sh, colors, scales, rotations, cov3D_precomp, viewmatrix,
                                 projmatrix, projmatrix_raw, campos, radii, dL_dout_color, dL_dout_depth)]

@@ -33,11 +33,33 @@ struct Buf {
     return p;
   }
 };
-Buf g_geom, g_bin, g_img;
-int g_P = 0, g_R = 0, g_N = 0;
+// One forward's saved state. The reference keeps it in three torch byte tensors saved on the autograd
+// context (diff_gaussian_rasterization/__init__.py:104); here a small ring of slots plays that role so that
+// several forwards can be alive before their backwards run (a mapping window sums the keyframes' losses and
+// calls backward once, utils/slam_mapper.py:273-322,394).
+struct State {
+  Buf geom, bin, img;
+  int P = 0, R = 0, N = 0;
+};
+constexpr int kSlots = 16;
+State g_state[kSlots];
+int g_slot = 0;
+#define g_geom (g_state[g_slot].geom)
+#define g_bin (g_state[g_slot].bin)
+#define g_img (g_state[g_slot].img)
+#define g_P (g_state[g_slot].P)
+#define g_R (g_state[g_slot].R)
+#define g_N (g_state[g_slot].N)
 }  // namespace
 
 extern "C" {
+
+// Selects the state slot used by the following ref_forward / ref_backward / ref_last_state calls.
+int ref_set_slot(int slot) {
+  if (slot < 0 || slot >= kSlots) return -1;
+  g_slot = slot;
+  return kSlots;
+}
 
 int ref_forward(int P, int D, int M, const float* bg, int W, int H,
                 const float* means3D, const float* shs, const float* colors,

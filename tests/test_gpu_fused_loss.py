@@ -1,10 +1,20 @@
-"""Fused render + L1 loss (monogs_b200.fused_loss) against the reference's loss formulas evaluated by torch autograd
-on top of the plain rasterizer node: loss value within 1e-6 relative, every gradient within 1e-4 relative."""
+"""Fused render + L1 loss (monogs_b200.fused_loss), pinned to the REFERENCE's own loss functions
+(utils/slam_utils.py:58-146) two ways:
+  * golden vectors tests/golden/loss.npz = get_loss_mapping / get_loss_tracking imported from /root/reference and
+    differentiated by autograd on CPU (tests/golden/make_loss_golden.py): loss value, dL/dimage, dL/ddepth, exposure
+    gradients of the CUDA loss kernels (gsr_l1_loss_forward / gsr_l1_loss_grad, the device code the fused backward
+    uses per pixel) -- loss 2e-6 relative, gradient images and exposure gradients 1e-5 relative;
+  * on the GPU box, the unmodified reference file itself (oracle/_ref/callers/utils/slam_utils.py) evaluated by torch
+    autograd on top of the plain rasterizer node against the fused node: every gradient within 1e-4 relative.
+"""
+import types
+
 import numpy as np
 import pytest
 import torch
 
-from conftest import rel_inf
+import ref_callers
+from conftest import ROOT, rel_inf
 from monogs_b200 import synth
 from monogs_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
 from monogs_b200.fused_loss import render_l1_loss
@@ -33,6 +43,27 @@ def ref_loss_tracking(image, depth, opacity, gt_rgb, gt_depth, gt_mask, grad_mas
     depth_mask = (gt_depth > 0) * opacity_mask
     l1_depth = torch.abs(depth[depth_mask] - gt_depth[depth_mask]).mean() if depth_mask.any() else 0.0
     return 0.5 * l1_rgb + l1_depth
+
+
+def _reference_losses():
+    """(get_loss_mapping, get_loss_tracking) of the reference's unmodified utils/slam_utils.py when it was shipped
+    (oracle/_ref/callers), as functions of explicit tensors; else the formulas restated above."""
+    if not ref_callers.available():
+        return ref_loss_mapping, ref_loss_tracking
+    ref_callers.verify_unmodified()
+    S = ref_callers.load_stack("ours")
+
+    def vp(gt_rgb, gt_depth, gt_mask, grad_mask, a, b):
+        return types.SimpleNamespace(rgb=gt_rgb, depth=gt_depth[0], mask=gt_mask, grad_mask=grad_mask, exposure_a=a,
+                                     exposure_b=b)
+
+    def mapping(image, depth, gt_rgb, gt_depth, gt_mask, a, b):
+        return S.get_loss_mapping(image, depth, vp(gt_rgb, gt_depth, gt_mask, None, a, b), init=False)
+
+    def tracking(image, depth, opacity, gt_rgb, gt_depth, gt_mask, grad_mask, a, b):
+        return S.get_loss_tracking(image, depth, opacity, vp(gt_rgb, gt_depth, gt_mask, grad_mask, a, b))
+
+    return mapping, tracking
 
 
 def _setup(P=12_000, seed=3):
@@ -68,10 +99,11 @@ def test_fused_loss_matches_autograd(built, kind):
     color, radii, depth, opacity, nt = GaussianRasterizer(s)(
         means3D=A["means3D"], means2D=A["means2D"], colors_precomp=A["colors"], opacities=A["opacities"],
         scales=A["scales"], rotations=A["rotations"], theta=A["theta"], rho=A["rho"])
+    loss_mapping, loss_tracking = _reference_losses()
     if kind == "mapping":
-        loss_ref = ref_loss_mapping(color, depth, gt_rgb, gt_depth, mask, A["a"], A["b"])
+        loss_ref = loss_mapping(color, depth, gt_rgb, gt_depth, mask, A["a"], A["b"])
     else:
-        loss_ref = ref_loss_tracking(color, depth, opacity, gt_rgb, gt_depth, mask, grad_mask, A["a"], A["b"])
+        loss_ref = loss_tracking(color, depth, opacity, gt_rgb, gt_depth, mask, grad_mask, A["a"], A["b"])
         assert int((opacity > 0.99).sum()) > 1000   # the opacity mask must actually select something
     (3.0 * loss_ref).backward()                      # upstream gradient != 1
     # fused
@@ -105,3 +137,39 @@ def test_fused_loss_no_masks_no_depth(built):
     with pytest.raises(ValueError):
         render_l1_loss(s, B["means3D"], B["means2D"], B["opacities"], colors_precomp=B["colors"], scales=B["scales"],
                        rotations=B["rotations"], gt_rgb=gt_rgb, kind="nope")
+
+
+@pytest.fixture(scope="module")
+def loss_golden():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_loss_golden", ROOT / "tests" / "golden" / "make_loss_golden.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod, np.load(ROOT / "tests" / "golden" / "loss.npz")
+
+
+@pytest.mark.parametrize("name", ["mapping", "mapping_init", "tracking", "tracking_sparse"])
+def test_loss_kernels_match_reference_golden(built, loss_golden, name):
+    """gsr_l1_loss_forward + gsr_l1_loss_grad against the reference functions' own outputs (see module docstring)."""
+    from monogs_b200.fused_loss import l1_loss_images
+    mod, g = loss_golden
+    c = mod.case_inputs(name)
+    d = lambda t: t.to(DEV)
+    no_exposure = c["kind"] == "mapping" and c["init"]
+    terms, d_color, d_depth = l1_loss_images(
+        c["kind"], d(c["image"]), d(c["depth"]), d(c["opacity"]), d(c["gt_rgb"]), d(c["gt_depth"])[None],
+        mask=d(c["mask"]), grad_mask=d(c["grad_mask"]) if c["kind"] == "tracking" else None,
+        exposure_a=None if no_exposure else d(c["exposure_a"]), exposure_b=None if no_exposure else d(c["exposure_b"]),
+        lambda_rgb=0.9, upstream=torch.tensor([c["upstream"]], device=DEV))
+    terms = terms.cpu().numpy().astype(np.float64)
+    want = float(g[f"{name}/loss"])
+    assert abs(terms[0] - want) <= 2e-6 * abs(want), (terms[0], want)          # tolerance: 2e-6 relative
+    assert rel_inf(d_color.cpu().numpy(), g[f"{name}/d_image"]) <= 1e-5          # tolerance: 1e-5 relative
+    assert rel_inf(d_depth.cpu().numpy(), g[f"{name}/d_depth"]) <= 1e-5
+    # where the reference's gradient image is exactly zero (masked-out pixels) ours is too
+    assert ((d_color.cpu().numpy() == 0) == (g[f"{name}/d_image"] == 0)).all()
+    assert ((d_depth.cpu().numpy() == 0) == (g[f"{name}/d_depth"] == 0)).all()
+    if not no_exposure:
+        up = c["upstream"]
+        assert abs(up * terms[5] - float(g[f"{name}/d_a"][0])) <= 1e-5 * abs(float(g[f"{name}/d_a"][0]))
+        assert abs(up * terms[6] - float(g[f"{name}/d_b"][0])) <= 1e-5 * abs(float(g[f"{name}/d_b"][0]))

@@ -171,6 +171,11 @@ REF_CASES = [
     (300_000, "replica", 4, False, False),
     (200_000, "hd", 5, False, False),        # 8160 tiles > 4096: the instance radix-sort binning path (C5 shape)
     (3_000, "tum_half", 6, False, False),    # fewer Gaussians than binning CTAs
+    # BASELINE.json's real sizes (the cases tools/compare_gpu.py ran by hand in round 1)
+    (1_000_000, "tum", 0, False, False),     # HEADLINE: 640x480, 1 M Gaussians
+    (500_000, "replica", 0, False, False),   # C3: 1200x680, 500 k
+    (2_000_000, "replica", 2, True, True),   # C4: 1200x680, 2 M, anisotropic + layered (long per-tile lists)
+    (4_000_000, "hd", 0, False, False),      # C5: 1920x1080, 4 M (8160 tiles -> instance radix-sort binning)
 ]
 
 
@@ -199,6 +204,8 @@ def test_against_reference_cuda(built, P, kind, seed, aniso, layered):
     final_T, n_contrib, ranges = _image_state(o["img"], cam.W, cam.H)
     assert (ranges.ravel() == st["ranges"].cpu().numpy()).all()
     assert (n_contrib == st["n_contrib"].cpu().numpy()).all()
+    assert (final_T.view(np.uint32) == st["accum_alpha"].cpu().numpy().view(np.uint32)).all()
+    assert torch.equal(o["color"].view(torch.int32), col_r.view(torch.int32))        # image BITS, not just 1e-5
     n = lambda t: t.detach().cpu().numpy()
     for a, r, k in ((o["color"], col_r, "color"), (o["depth"], dep_r, "depth"), (o["opacity"], opa_r, "opacity")):
         assert rel_inf(n(a), n(r)) <= 1e-5, k
