@@ -218,11 +218,7 @@ def test_mapping_window_loop_unchanged(built):
     for a, b in zip(out["ours"][0], out["ref"][0]):
         compare_pkg(a, b)
     assert abs(out["ours"][1] - out["ref"][1]) <= 1e-5 * abs(out["ref"][1])
-    # isotropic [P,1] scales here (MonoGS's default): dL/drotation is analytically zero, i.e. rounding noise in both
-    compare_grads(out["ours"][2], out["ref"][2], ["xyz", "scale", "opacity", "rgb"])
-    scale_of = float(out["ref"][2]["xyz"].grad.abs().max())
-    for k in ("ours", "ref"):
-        assert float(out[k][2]["rot"].grad.abs().max()) <= 1e-3 * scale_of
+    compare_grads(out["ours"][2], out["ref"][2], ["xyz", "rot", "scale", "opacity", "rgb"])
     for va, vb, pa, pb in zip(out["ours"][3], out["ref"][3], out["ours"][0], out["ref"][0]):
         for k in ("cam_rot_delta", "cam_trans_delta", "exposure_a", "exposure_b"):
             assert rel_inf(n(getattr(va, k).grad), n(getattr(vb, k).grad)) <= 1e-4, k
