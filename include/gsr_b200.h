@@ -361,10 +361,10 @@ int gsr_sort_pairs_u64(void* stream, int64_t n, const uint64_t* keys_in,
 /* Pointers into the workspaces, for bit-exact checks against the reference's
  * GeometryState / BinningState / ImageState (rasterizer_impl.h:33-62).
  * geom record layout: see DESIGN.md "Data layout in HBM". */
-int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, const float** rec_a /*float4[P]: x,y,depth,ext_x*/,
-                         const float** rec_b /*float4[P]: conic xyz, opacity*/,
-                         const float** rec_c /*float4[P]: rgb, ext_y*/,
-                         const uint32_t** tiles_touched);
+/* The three views point INTO one packed 48-byte record per Gaussian: element i of a view is the float4 at
+ * view + 12 * i floats (rec_a: x, y, depth, cull threshold; rec_b: conic xyz, opacity; rec_c: rgb, 0). */
+int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, const float** rec_a,
+                         const float** rec_b, const float** rec_c, const uint32_t** tiles_touched);
 int gsr_debug_image_views(const void* image_ws, int width, int height,
                           const float** final_T, const uint32_t** n_contrib,
                           const uint32_t** ranges /*uint2[tiles]*/);

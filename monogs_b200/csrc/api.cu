@@ -737,9 +737,10 @@ int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, cons
   if (!geom_ws) return GSR_EINVAL;
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
-  if (rec_a) *rec_a = (const float*)g.rec_a;
-  if (rec_b) *rec_b = (const float*)g.rec_b;
-  if (rec_c) *rec_c = (const float*)g.rec_c;
+  // ONE packed record per Gaussian: element i of each view lives at view + 12 * i floats
+  if (rec_a) *rec_a = (const float*)g.rec;
+  if (rec_b) *rec_b = (const float*)(g.rec + 1);
+  if (rec_c) *rec_c = (const float*)(g.rec + 2);
   if (tiles_touched) *tiles_touched = g.tiles_touched;
   return GSR_OK;
 }
@@ -778,7 +779,7 @@ int gsr_debug_sorted_keys(void* stream, const void* geom_ws, const void* binning
   BinningViews bv;
   carve_binning((char*)binning_ws, num_rendered, &bv);
   const uint32_t* tk = (tile_sort_plan(width, height).n_passes & 1) ? bv.tkeys_b : bv.tkeys_a;
-  return check(launch_rebuild_keys((cudaStream_t)stream, num_rendered, tk, point_list, g.rec_a, keys_sorted));
+  return check(launch_rebuild_keys((cudaStream_t)stream, num_rendered, tk, point_list, g.rec, keys_sorted));
 }
 
 }  // extern "C"

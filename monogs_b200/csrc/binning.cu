@@ -153,12 +153,12 @@ tile_ranges_kernel(long long cap, const unsigned long long* __restrict__ n_dev,
 // Test hook: rebuild the reference's sorted 64-bit keys = (tile << 32) | depth bits.
 __global__ void __launch_bounds__(256)
 rebuild_keys_kernel(long long L, const uint32_t* __restrict__ tkeys_sorted, const uint32_t* __restrict__ point_list,
-                    const float4* __restrict__ rec_a, uint64_t* __restrict__ keys) {
+                    const float4* __restrict__ rec, uint64_t* __restrict__ keys) {
   pdl_launch_dependents();
   pdl_wait();
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= L) return;
-  keys[i] = ((uint64_t)tkeys_sorted[i] << 32) | __float_as_uint(rec_a[point_list[i]].z);
+  keys[i] = ((uint64_t)tkeys_sorted[i] << 32) | __float_as_uint(rec[3 * (size_t)point_list[i]].z);
 }
 
 cudaError_t launch_gather_rects(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g) {
@@ -186,9 +186,9 @@ cudaError_t launch_tile_ranges(cudaStream_t st, long long cap, const unsigned lo
 }
 
 cudaError_t launch_rebuild_keys(cudaStream_t st, long long L, const uint32_t* tkeys_sorted,
-                                const uint32_t* point_list, const float4* rec_a, uint64_t* keys) {
+                                const uint32_t* point_list, const float4* rec, uint64_t* keys) {
   if (L <= 0) return cudaSuccess;
-  count_launch(); launch_k(rebuild_keys_kernel, (unsigned)((L + 255) / 256), 256, 0, st, L, tkeys_sorted, point_list, rec_a, keys);
+  count_launch(); launch_k(rebuild_keys_kernel, (unsigned)((L + 255) / 256), 256, 0, st, L, tkeys_sorted, point_list, rec, keys);
   return cudaGetLastError();
 }
 

@@ -19,15 +19,13 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;
 // ---------------------------------------------------------------------------
 __host__ __device__ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
-// Per-Gaussian geometry state ("GeometryState" of rasterizer_impl.h:33-48,
-// re-laid out as three float4 records so the renderers gather 3 x 16 B).
-//   rec_a = {mean2D.x, mean2D.y, depth(view z), cull extent x}
-//   rec_b = {conic.x, conic.y, conic.z, opacity}
-//   rec_c = {r, g, b, cull extent y}
+// Per-Gaussian geometry state ("GeometryState" of rasterizer_impl.h:33-48), re-laid out as ONE packed 48-byte
+// record per Gaussian = 3 consecutive float4, so a renderer's gather of an instance touches two 32-byte sectors:
+//   rec[3i + 0] = {mean2D.x, mean2D.y, depth(view z), tau}   tau = cull threshold ln(255 o) + margins (preprocess.cu)
+//   rec[3i + 1] = {conic.x, conic.y, conic.z, opacity}
+//   rec[3i + 2] = {r, g, b, 0}
 struct GeomViews {
-  float4* rec_a;
-  float4* rec_b;
-  float4* rec_c;
+  float4* rec;               // [3P]
   uint32_t* tiles_touched;   // [P]
   uint2* rect;               // [P] tile rectangle x0 | x1 << 16, y0 | y1 << 16 (empty when culled)
   uint2* rect_sorted;        // [P] the same in (depth, id) order
@@ -106,9 +104,7 @@ __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, Ge
   const size_t ts_tiles = num_tiles(W, H) <= (size_t)TS_MAX_TILES ? num_tiles(W, H) : 0;
   size_t off = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
-  char* a = take(sizeof(float4) * (size_t)P);
-  char* b = take(sizeof(float4) * (size_t)P);
-  char* c = take(sizeof(float4) * (size_t)P);
+  char* a = take(sizeof(float4) * 3 * (size_t)P);
   char* t = take(sizeof(uint32_t) * (size_t)P);
   char* rc = take(sizeof(uint2) * (size_t)P); char* rs = take(sizeof(uint2) * (size_t)P);
   char* cl = take((size_t)3 * P);
@@ -125,7 +121,7 @@ __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, Ge
   char* tot = take(256);
   size_t ze = off;
   if (v) {
-    v->rec_a = (float4*)a; v->rec_b = (float4*)b; v->rec_c = (float4*)c;
+    v->rec = (float4*)a;
     v->tiles_touched = (uint32_t*)t; v->clamped = (uint8_t*)cl;
     v->rect = (uint2*)rc; v->rect_sorted = (uint2*)rs;
     v->dkeys_a = (uint32_t*)ka; v->dkeys_b = (uint32_t*)kb; v->order_a = (uint32_t*)oa; v->order_b = (uint32_t*)ob;

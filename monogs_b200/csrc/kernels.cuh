@@ -26,7 +26,7 @@ cudaError_t launch_emit_instances(cudaStream_t st, int P, const uint32_t* order,
 cudaError_t launch_tile_ranges(cudaStream_t st, long long cap, const unsigned long long* n_dev,
                                const uint32_t* tkeys_sorted, uint2* ranges, size_t n_tiles);
 cudaError_t launch_rebuild_keys(cudaStream_t st, long long L, const uint32_t* tkeys_sorted,
-                                const uint32_t* point_list, const float4* rec_a, uint64_t* keys);
+                                const uint32_t* point_list, const float4* rec, uint64_t* keys);
 
 // tile_scatter.cu  (sort-free binning for images of <= TS_MAX_TILES tiles)
 cudaError_t launch_tile_count(cudaStream_t st, int P, const GeomViews& g, int tiles_x, int n_tiles);

@@ -250,7 +250,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     const float px = s_mean[3 * tid], py = s_mean[3 * tid + 1], pz = s_mean[3 * tid + 2];
     int my_radius_i = 0;
     float4 ra = make_float4(0.f, 0.f, 0.f, -1e30f), rb = make_float4(0.f, 0.f, 0.f, 0.f),
-           rc = make_float4(0.f, 0.f, 0.f, -1e30f);
+           rc = make_float4(0.f, 0.f, 0.f, 0.f);
 
     // near culling (in_frustum, auxiliary.h:139-164): p_view.z <= 0.2 -> invisible
     const float depth = affine_row(view, 2, px, py, pz);
@@ -296,17 +296,11 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
         } else {
           my_rect = make_uint2(rmin.x | (rmax.x << 16), rmin.y | (rmax.y << 16));
           const float opac = my_opac;
-          // Conservative per-axis reach of alpha >= 1/255 (see DESIGN.md "culling"):
-          // q(d) <= 2*ln(255*o); inflated so fp32 rounding in `power` can never
-          // make a pixel outside the box pass the reference's alpha test.
-          const float tau2 = 2.0f * logf(255.0f * opac) + 1.0f;
-          float ex = -1e30f, ey = -1e30f;
-          if (tau2 > 0.0f) {
-            ex = sqrtf(tau2 * c2.x) * 1.001f + 0.01f;
-            ey = sqrtf(tau2 * c2.z) * 1.001f + 0.01f;
-          } else if (!(tau2 <= 0.0f)) {  // NaN opacity: never cull
-            ex = ey = 1e30f;
-          }
+          // Cull threshold of the renderers (render_common.cuh): a pixel can pass the reference's alpha >= 1/255
+          // test only where q = -power <= ln(255 o). Margins: 0.1 % + 1e-3 cover expf / fmul rounding of alpha and
+          // logf here; the renderers add a term for the rounding of `power` itself. NaN opacity -> NaN -> never culled.
+          const float lg = logf(255.0f * opac);
+          const float tau = lg + 1e-3f * fabsf(lg) + 1e-3f;
           float3 rgb;
           if (colors_precomp != nullptr) {
             rgb = my_col;
@@ -318,9 +312,9 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
             g.clamped[3 * (size_t)idx + 2] = rgb.z < 0.f;
             rgb.x = fmaxf(rgb.x, 0.f); rgb.y = fmaxf(rgb.y, 0.f); rgb.z = fmaxf(rgb.z, 0.f);
           }
-          ra = make_float4(pix_x, pix_y, depth, ex);
+          ra = make_float4(pix_x, pix_y, depth, tau);
           rb = make_float4(conx, cony, conz, opac);
-          rc = make_float4(rgb.x, rgb.y, rgb.z, ey);
+          rc = make_float4(rgb.x, rgb.y, rgb.z, 0.0f);
 
         }
       }
@@ -328,9 +322,9 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     radii[idx] = my_radius_i;
     g.tiles_touched[idx] = my_tiles;
     g.rect[idx] = my_rect;
-    g.rec_a[idx] = ra;
-    g.rec_b[idx] = rb;
-    g.rec_c[idx] = rc;
+    g.rec[3 * (size_t)idx + 0] = ra;
+    g.rec[3 * (size_t)idx + 1] = rb;
+    g.rec[3 * (size_t)idx + 2] = rc;
     // depth sort key: positive floats order like their bit patterns; culled Gaussians go last
     const uint32_t dkey = my_tiles ? __float_as_uint(ra.z) : 0xFFFFFFFFu;
     g.dkeys_a[idx] = dkey;

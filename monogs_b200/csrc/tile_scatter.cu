@@ -404,7 +404,7 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
 // Test hook: the sorted tile id of every list position, from the tile starts (last tile with start <= i).
 __global__ void __launch_bounds__(256)
 rebuild_keys_from_starts_kernel(long long L, int n_tiles, const uint32_t* __restrict__ start,
-                                const uint32_t* __restrict__ point_list, const float4* __restrict__ rec_a,
+                                const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
                                 uint64_t* __restrict__ keys) {
   pdl_launch_dependents();
   pdl_wait();
@@ -415,7 +415,7 @@ rebuild_keys_from_starts_kernel(long long L, int n_tiles, const uint32_t* __rest
     const int m = (l + h + 1) >> 1;
     if ((long long)start[m] <= i) l = m; else h = m - 1;
   }
-  keys[i] = ((uint64_t)(uint32_t)l << 32) | __float_as_uint(rec_a[point_list[i]].z);
+  keys[i] = ((uint64_t)(uint32_t)l << 32) | __float_as_uint(rec[3 * (size_t)point_list[i]].z);
 }
 
 static size_t ts_scatter_smem(int n_tiles) {
@@ -457,7 +457,7 @@ cudaError_t launch_rebuild_keys_from_starts(cudaStream_t st, long long L, int n_
   if (L <= 0) return cudaSuccess;
   count_launch();
   launch_k(rebuild_keys_from_starts_kernel, (unsigned)((L + 255) / 256), 256, 0, st, L, n_tiles, g.ts_start, point_list,
-                                                                               g.rec_a, keys);
+                                                                               g.rec, keys);
   return cudaGetLastError();
 }
 

@@ -56,8 +56,9 @@ def _geom_state(geom, P, W, H):
     pa, pb, pc, pt = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
     assert lib.gsr_debug_geom_views(geom.data_ptr(), P, W, H, C.byref(pa), C.byref(pb), C.byref(pc), C.byref(pt)) == 0
     v = lambda p, n: geom[p.value - geom.data_ptr(): p.value - geom.data_ptr() + 4 * n]
-    ra = v(pa, 4 * P).view(torch.float32).view(P, 4).cpu().numpy()
-    rb = v(pb, 4 * P).view(torch.float32).view(P, 4).cpu().numpy()
+    assert pb.value - pa.value == 16 and pc.value - pa.value == 32      # one packed 48-byte record per Gaussian
+    rec = v(pa, 12 * P).view(torch.float32).view(P, 12).cpu().numpy()
+    ra, rb = rec[:, 0:4], rec[:, 4:8]
     tt = v(pt, P).view(torch.int32).cpu().numpy()
     return ra, rb, tt
 
@@ -179,15 +180,11 @@ REF_CASES = [
 ]
 
 
-@needs_ref
-@pytest.mark.parametrize("P,kind,seed,aniso,layered", REF_CASES)
-def test_against_reference_cuda(built, P, kind, seed, aniso, layered):
-    cam = synth.make_camera(kind, rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))
-    sc = synth.make_scene(P, cam, seed=seed, anisotropic=aniso, layered=layered, device=DEV)
-    bg = torch.tensor([0.1, 0.2, 0.3], device=DEV)
-    g = torch.Generator().manual_seed(seed + 7)
-    dcol = (torch.randn(3, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
-    ddep = (torch.randn(1, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
+def _compare_with_reference(cam, sc, bg, dcol, ddep, grad_tol=1e-4, well_conditioned=None):
+    """well_conditioned: optional bool[P]; the gradients that pass through the 2D-covariance inverse (means3D, cov3D,
+    scales, rotations, tau) are then compared on those Gaussians only (the renderer's own outputs -- mean2D, colour,
+    opacity gradients -- always on all)."""
+    P = sc["means3D"].shape[0]
     o = _run_ours(cam, sc, bg, dcol, ddep)
     fa = o["fa"]
     Rr, col_r, rad_r, _, _, _, dep_r, opa_r, nt_r = ref.rasterize_gaussians(*fa)
@@ -211,9 +208,60 @@ def test_against_reference_cuda(built, P, kind, seed, aniso, layered):
         assert rel_inf(n(a), n(r)) <= 1e-5, k
     for name, a, r, r2 in zip(GRAD_NAMES, o["grads"], gr, gr2):
         if a.numel():
+            if well_conditioned is not None and name in ("dmeans3D", "dcov3D", "dscales", "drots", "dtau"):
+                a, r, r2 = a[well_conditioned], r[well_conditioned], r2[well_conditioned]
             spread = rel_inf(n(r2), n(r))  # the reference's own run-to-run spread (fp32 atomics)
-            assert rel_inf(n(a), n(r)) <= max(1e-4, 3 * spread), (name, rel_inf(n(a), n(r)), spread)
-    assert rel_inf(n(o["tau"]), n(gr[8]).astype(np.float64).sum(0)) <= 1e-4
+            assert rel_inf(n(a), n(r)) <= max(grad_tol, 3 * spread), (name, rel_inf(n(a), n(r)), spread)
+    if well_conditioned is None:
+        assert rel_inf(n(o["tau"]), n(gr[8]).astype(np.float64).sum(0)) <= max(grad_tol, 1e-4)
+    return o
+
+
+@needs_ref
+@pytest.mark.parametrize("P,kind,seed,aniso,layered", REF_CASES)
+def test_against_reference_cuda(built, P, kind, seed, aniso, layered):
+    cam = synth.make_camera(kind, rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))
+    sc = synth.make_scene(P, cam, seed=seed, anisotropic=aniso, layered=layered, device=DEV)
+    bg = torch.tensor([0.1, 0.2, 0.3], device=DEV)
+    g = torch.Generator().manual_seed(seed + 7)
+    dcol = (torch.randn(3, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
+    ddep = (torch.randn(1, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
+    _compare_with_reference(cam, sc, bg, dcol, ddep)
+
+
+@needs_ref
+def test_huge_and_near_degenerate_gaussians_against_reference(built):
+    """Splats the per-rectangle cull of the renderers must never get wrong: footprints of hundreds to thousands of
+    pixels, needle-shaped (near-singular 2D covariance, conic terms that cancel), faint (255 * opacity barely above
+    1) and fully opaque ones, mixed into an ordinary scene. Every integer output and the image bits must still equal
+    the reference's: a pair culled although the reference blends it would change final_T / n_contrib / colour bits."""
+    P = 30_000
+    cam = synth.make_camera("tum_half", rot=(0.004, -0.006, 0.003), trans=(0.02, -0.01, 0.015))
+    sc = synth.make_scene(P, cam, seed=77, anisotropic=True, device=DEV)
+    g = torch.Generator().manual_seed(78)
+    k = 600
+    idx = torch.randperm(P, generator=g)[:k].to(DEV)
+    z = sc["means3D"][idx, 2].abs().clamp_min(0.3)
+    shape = torch.ones(k, 3)
+    shape[:200] = torch.tensor([3.0, 1e-3, 1e-3])                      # needles: ~1000 px long, ~0.3 px wide
+    shape[200:400] = torch.tensor([2.0, 2.0, 1e-3])                    # sheets seen at random angles
+    shape[400:] = torch.tensor([1.5, 1.5, 1.5])                        # blobs covering the whole image
+    sc["scales"][idx] = (shape.to(DEV) * z[:, None] * (0.2 + torch.rand(k, 1, generator=g).to(DEV))).contiguous()
+    op = sc["opacities"].clone()
+    op[idx[0:k:3]] = 1.0                                               # fully opaque
+    op[idx[1:k:3]] = (1.0 / 255.0) * (1.0 + 0.05 * torch.rand(len(idx[1:k:3]), 1, generator=g).to(DEV))  # barely visible
+    sc["opacities"] = op.contiguous()
+    bg = torch.tensor([0.1, 0.2, 0.3], device=DEV)
+    dcol = (torch.randn(3, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
+    ddep = (torch.randn(1, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
+    # The needles and sheets have 2D covariances of aspect ratio ~3000: the gradient THROUGH their inverse is
+    # ill-conditioned in both implementations (the reference disagrees with its own second run by 30 % on them:
+    # atomic order), so those gradients are compared on all other Gaussians; the renderer's own gradient outputs
+    # (mean2D, colour, opacity) are compared on every Gaussian, and every integer / image-bit bar stays exact.
+    well = torch.ones(P, dtype=torch.bool, device=DEV)
+    well[idx[:400]] = False
+    o = _compare_with_reference(cam, sc, bg, dcol, ddep, well_conditioned=well)
+    assert int(o["radii"].max()) > 500
 
 
 @needs_ref

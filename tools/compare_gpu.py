@@ -84,7 +84,8 @@ def run_pair(P, kind, seed, anisotropic, layered, timing_iters, log):
         o = ptr.value - geom.data_ptr()
         return geom[o:o + 4 * n].view(torch.int32)
     vis = rad_r > 0
-    ra = gview(pa, 4 * P).view(P, 4); rb = gview(pb, 4 * P).view(P, 4)
+    rec = gview(pa, 12 * P).view(P, 12)   # one packed 48-byte record per Gaussian
+    ra = rec[:, 0:4]; rb = rec[:, 4:8]
     res["means2D_bits_mismatch"] = int((ra[:, :2][vis] != st["means2D"].view(torch.int32).view(P, 2)[vis]).sum())
     res["depth_bits_mismatch"] = int((ra[:, 2][vis] != st["depths"].view(torch.int32)[vis]).sum())
     res["conic_bits_mismatch"] = int((rb[vis] != st["conic_opacity"].view(torch.int32).view(P, 4)[vis]).sum())
