@@ -169,8 +169,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int n_batches = (total + RENDER_BATCH - 1) / RENDER_BATCH;
 
   float T = T_final;
-  float acc_r = 0.f, acc_g = 0.f, acc_b = 0.f, acc_d = 0.f;
-  float last_alpha = 0.f, last_r = 0.f, last_g = 0.f, last_b = 0.f, last_d = 0.f;
+  float acc_w = 0.f, last_w = 0.f, last_alpha = 0.f;
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
   // phase-2 role of this lane: Gaussian g2 of the round, pixels [16 h2, 16 h2 + 16) of the warp's rectangle
   const int g2 = lane & (RB_GROUP - 1), h2 = lane >> 4;
@@ -219,21 +218,25 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 
     for (int i0 = 0; i0 < qn; i0 += RB_GROUP) {
       const int gn = min(RB_GROUP, qn - i0);
-      // ---- phase 1 (lane = pixel): replay gn Gaussians, park S = G dL/dalpha and A = alpha T per (Gaussian, pixel)
+      // ---- phase 1 (lane = pixel): replay gn Gaussians, park S = G dL/dalpha and A = alpha T per (Gaussian, pixel).
+      //      The records of Gaussian k+1 are fetched from shared memory while k is computed.
+      int j = (int)my_queue[i0];
+      float4 a = sg.rec[3 * j], co = sg.rec[3 * j + 1], c = sg.rec[3 * j + 2];
       for (int k = 0; k < gn; ++k) {
-        const int j = (int)my_queue[i0 + k];
         const uint32_t pos = (uint32_t)(total - 1 - (b * RENDER_BATCH + j));  // 0-based list position
-        const float4 a = sg.rec[3 * j];
-        const float4 co = sg.rec[3 * j + 1];
-        const float dx = fsub(a.x, pixx), dy = fsub(a.y, pixy);
-        const float power = gauss_power(dx, dy, co.x, co.y, co.z);
+        const float4 a_k = a, co_k = co, c_k = c;
+        if (k + 1 < gn) {
+          j = (int)my_queue[i0 + k + 1];
+          a = sg.rec[3 * j]; co = sg.rec[3 * j + 1]; c = sg.rec[3 * j + 2];
+        }
+        const float dx = fsub(a_k.x, pixx), dy = fsub(a_k.y, pixy);
+        const float power = gauss_power(dx, dy, co_k.x, co_k.y, co_k.z);
         const float G = expf(power);
-        const float alpha = fminf(fmul(co.w, G), 0.99f);
+        const float alpha = fminf(fmul(co_k.w, G), 0.99f);
         // skip rules of backward.cu:676-689
         const bool skip = !inside || pos >= last_contributor || power > 0.0f || alpha < 1.0f / 255.0f;
         float S = 0.0f, A = 0.0f;
         if (!skip) {
-          const float4 c = sg.rec[3 * j + 2];
           // 1 / (1 - alpha): ONE reciprocal (SFU estimate + a Newton step: <= 1 ulp on [0.01, 1], no special cases),
           // shared by the transmittance recovery and the background term; the reference's two IEEE divisions
           // (backward.cu:700,742) cost ~20 instructions per pair here. Gradients are compared at 1e-4.
@@ -243,18 +246,14 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           inv_1ma = fmaf(inv_1ma, fmaf(-one_m_alpha, inv_1ma, 1.0f), inv_1ma);  // one Newton step
           T = T * inv_1ma;
           A = alpha * T;                                   // dchannel_dcolor (backward.cu:702)
-          float dL_dalpha = 0.0f;
-          acc_r = last_alpha * last_r + (1.f - last_alpha) * acc_r; last_r = c.x;
-          dL_dalpha += (c.x - acc_r) * dpr;
-          acc_g = last_alpha * last_g + (1.f - last_alpha) * acc_g; last_g = c.y;
-          dL_dalpha += (c.y - acc_g) * dpg;
-          acc_b = last_alpha * last_b + (1.f - last_alpha) * acc_b; last_b = c.z;
-          dL_dalpha += (c.z - acc_b) * dpb;
-          acc_d = last_alpha * last_d + (1.f - last_alpha) * acc_d; last_d = a.z;
-          dL_dalpha += (a.z - acc_d) * dpd;
-          dL_dalpha *= T;
+          // dL/dalpha = T sum_ch (c_ch - accum_rec_ch) dL/dpixel_ch (backward.cu:707-731). The per-channel recurrence
+          // accum_rec = last_alpha last_c + (1 - last_alpha) accum_rec is linear, so it is carried for the ONE scalar
+          // w = colour . dL/dpixel instead of the four channels.
+          const float wk = fmaf(c_k.x, dpr, fmaf(c_k.y, dpg, fmaf(c_k.z, dpb, a_k.z * dpd)));
+          acc_w = fmaf(last_alpha, last_w - acc_w, acc_w);
+          last_w = wk;
           last_alpha = alpha;
-          dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
+          const float dL_dalpha = fmaf(wk - acc_w, T, (-T_final * inv_1ma) * bg_dot_dpixel);
           S = G * dL_dalpha;
         }
         my_S[k * RB_PITCH + lane] = S;
@@ -264,9 +263,9 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       // ---- phase 2 (lane = Gaussian g2 x pixel half h2): moments of S and A dL/dpixel over 16 pixels in registers
       {
         const bool have = g2 < gn;
-        const int j = (int)my_queue[i0 + (have ? g2 : 0)];
-        const float4 a = sg.rec[3 * j];
-        const float4 co = sg.rec[3 * j + 1];
+        const int jg = (int)my_queue[i0 + (have ? g2 : 0)];
+        const float4 ag = sg.rec[3 * jg];
+        const float4 cog = sg.rec[3 * jg + 1];
         const float* rowS = my_S + g2 * RB_PITCH + 16 * h2;
         const float* rowA = my_A + g2 * RB_PITCH + 16 * h2;
         const float4* dp = sh.dp[w] + 16 * h2;
@@ -277,7 +276,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
             const float S = rowS[k], A = rowA[k];
             const float4 d = dp[k];
             // pixel k of this half: x = wx0 + (k & 7), y = wy0 + 2 h2 + (k >> 3); same fp32 offsets as phase 1
-            const float dx = fsub(a.x, (float)(wx0 + (k & 7))), dy = fsub(a.y, py2 + (float)(k >> 3));
+            const float dx = fsub(ag.x, (float)(wx0 + (k & 7))), dy = fsub(ag.y, py2 + (float)(k >> 3));
             const float sx = S * dx, sy = S * dy;
             m0 += S; mx += sx; my += sy;
             mxx = fmaf(sx, dx, mxx); mxy = fmaf(sx, dy, mxy); myy = fmaf(sy, dy, myy);
@@ -292,10 +291,10 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         cb += __shfl_xor_sync(0xffffffffu, cb, 16); cd += __shfl_xor_sync(0xffffffffu, cd, 16);
         if (have && h2 == 0) {
           // dL/dG = o dL/dalpha; dG/ddelx = -G (dx cx + dy cy), dG/ddely = -G (dy cz + dx cy)   (backward.cu:746-771)
-          const float o = co.w;
-          float* dst = packed + (size_t)sg.id[j] * GRAD_STRIDE;
-          atomicAdd(dst + 0, -o * (co.x * mx + co.y * my) * ddelx_dx);
-          atomicAdd(dst + 1, -o * (co.z * my + co.y * mx) * ddely_dy);
+          const float o = cog.w;
+          float* dst = packed + (size_t)sg.id[jg] * GRAD_STRIDE;
+          atomicAdd(dst + 0, -o * (cog.x * mx + cog.y * my) * ddelx_dx);
+          atomicAdd(dst + 1, -o * (cog.z * my + cog.y * mx) * ddely_dy);
           atomicAdd(dst + 2, -0.5f * o * mxx);
           atomicAdd(dst + 3, -0.5f * o * mxy);
           atomicAdd(dst + 4, -0.5f * o * myy);

@@ -77,6 +77,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   float T = 1.0f, Cr = 0.f, Cg = 0.f, Cb = 0.f, D = 0.f;
   uint32_t last_contributor = 0;
   bool done = !inside;
+  bool touch_live = true;   // warp-uniform: some pixel of the warp can still satisfy T(1-alpha) > 0.5
 
   // prologue: gather batch 0, prefetch the id of batch 1
   uint32_t id_next = 0;
@@ -118,7 +119,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         qn += __popc(m);
       }
       __syncwarp();
-      // ---- blend the queued Gaussians in list order ----
+      // ---- blend the queued Gaussians in list order (prefetching Gaussian i+1's record one iteration ahead was
+      //      measured SLOWER here: 0.094 vs 0.081 ms; it pays in the backward kernel) ----
       for (int i = 0; i < qn; ++i) {
         const int j = c0 + (int)my_queue[i];
         const float4 a = sg.rec[3 * j];
@@ -138,9 +140,13 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           T = test_T;
           last_contributor = (uint32_t)(b * RENDER_BATCH + j + 1);
         }
-        // n_touched: pixels where this Gaussian is seen with T(1-alpha) > 0.5 (forward.cu:369-371)
-        const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
-        if (tv != 0 && lane == 0) atomicAdd(&n_touched[sg.id[j]], __popc(tv));
+        // n_touched: pixels where this Gaussian is seen with T(1-alpha) > 0.5 (forward.cu:369-371). T only falls, so
+        // once no pixel of the warp has T > 0.5 the vote can never fire again and is skipped for the rest of the tile.
+        if (touch_live) {
+          const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
+          if (tv != 0 && lane == 0) atomicAdd(&n_touched[sg.id[j]], __popc(tv));
+          touch_live = __any_sync(0xffffffffu, !done && T > 0.5f);
+        }
         if (__all_sync(0xffffffffu, done)) break;
       }
       __syncwarp();   // the queue is rewritten by the next chunk
