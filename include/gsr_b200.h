@@ -252,7 +252,10 @@ int gsr_backward_rows(void* stream, int P, int p_begin, int p_end, int width, in
  *   marks into slot [rank] of its own buffer: touched_words = local + offsets[1] + 4*rank*words_per_rank (bit i of
  *   word i/32 = row i is non-zero here), vis_u8 = local + offsets[2] + rank*vis_bytes_per_rank (keyframes of this
  *   rank that see Gaussian i). Both NULL = plain gsr_backward_rows.
- * gsr_rows_exchange: ONE kernel, enqueued on every rank with the same P / world / n_ctas / epoch: rows that are
+ * The buffer is laid out for a CAPACITY of rows (the `P` argument of gsr_rows_exchange_bytes / _layout): offsets and
+ *   slot strides depend on the capacity only, so a map that grows inside it (keyframe insertion, densification)
+ *   keeps its buffer, its marks pointers and its barrier flags; gsr_rows_exchange takes the live P <= capacity.
+ * gsr_rows_exchange: ONE kernel, enqueued on every rank with the same P / capacity / world / n_ctas / epoch: rows that are
  *   non-zero on some rank are summed in the NVSwitch (multimem.ld_reduce) and multicast back (multimem.st); all
  *   other rows are left alone (zero gradients everywhere). vis_count[P] (local, optional) = sum over the ranks of
  *   the visibility counts; column 15 of the rows is not meaningful afterwards. peer_bufs = DEVICE array of
@@ -269,8 +272,11 @@ int gsr_backward_rows_marked(void* stream, int P, int p_begin, int p_end, int wi
                              const float* projmatrix_raw, float tan_fovx, float tan_fovy, const int* radii,
                              const void* geom_ws, void* scratch, float* rows, int accumulate, float* dL_dmeans2D,
                              float* dL_dtau, uint32_t* touched_words, uint8_t* vis_u8, int debug);
-int gsr_rows_exchange(void* stream, int P, int rank, int world, int n_ctas, void* local_buf, void* multicast_buf,
-                      const uint64_t* peer_bufs, uint32_t epoch, float* vis_count, int* status);
+int gsr_rows_exchange(void* stream, int P, int capacity, int rank, int world, int n_ctas, void* local_buf,
+                      void* multicast_buf, const uint64_t* peer_bufs, uint32_t epoch, float* vis_count, int* status);
+/* Measurement hook: globaltimer (ns) at kernel start / after the marks multicast / after barrier 1 / after the row
+ * sums / after barrier 2 of the LAST gsr_rows_exchange on the current device (host_out[5]; synchronise first). */
+int gsr_debug_exchange_trace(uint64_t* host_out);
 
 /* ---- Gaussian insertion from an RGB-D keyframe: the device side of
  * GaussianModel.create_viewpoint_pcd (gaussian_splatting/scene/gaussian_model.py:121-319), the caller of distCUDA2.

@@ -45,7 +45,8 @@ SIGNATURES = {
                                        vp, i32, vp, vp, vp, vp, i32]),
     "gsr_rows_exchange_bytes": (C.c_size_t, [i32, i32]),
     "gsr_rows_exchange_layout": (i32, [i32, i32, C.POINTER(C.c_size_t), C.POINTER(i32), C.POINTER(i32)]),
-    "gsr_rows_exchange": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, C.c_uint32, vp, vp]),
+    "gsr_rows_exchange": (i32, [vp, i32, i32, i32, i32, i32, vp, vp, vp, C.c_uint32, vp, vp]),
+    "gsr_debug_exchange_trace": (i32, [vp]),
     "gsr_insert_ws_bytes": (sz, [i32, i32]),
     "gsr_select_kth_f32": (i32, [vp, i64, vp, vp, i64, vp, vp]),
     "gsr_insert_select": (i32, [vp, i32, i32, vp, vp, vp, i32, vp, vp, vp, vp]),

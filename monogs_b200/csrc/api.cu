@@ -561,14 +561,19 @@ int gsr_rows_exchange_layout(int P, int world, size_t* offsets, int* words_per_r
   return GSR_OK;
 }
 
-int gsr_rows_exchange(void* stream, int P, int rank, int world, int n_ctas, void* local_buf, void* multicast_buf,
-                      const uint64_t* peer_bufs, uint32_t epoch, float* vis_count, int* status) {
-  if (P < 0 || world < 1 || world > XCHG_MAX_WORLD || rank < 0 || rank >= world) return GSR_EINVAL;
+int gsr_rows_exchange(void* stream, int P, int capacity, int rank, int world, int n_ctas, void* local_buf,
+                      void* multicast_buf, const uint64_t* peer_bufs, uint32_t epoch, float* vis_count, int* status) {
+  if (P < 0 || capacity < P || world < 1 || world > XCHG_MAX_WORLD || rank < 0 || rank >= world) return GSR_EINVAL;
   if (n_ctas < 1 || n_ctas > XCHG_MAX_CTAS || !local_buf || !multicast_buf || !peer_bufs) return GSR_EINVAL;
   if (P == 0) return GSR_OK;
-  return check(launch_rows_exchange((cudaStream_t)stream, P, rank, world, n_ctas, local_buf, multicast_buf,
+  return check(launch_rows_exchange((cudaStream_t)stream, P, capacity, rank, world, n_ctas, local_buf, multicast_buf,
                                     reinterpret_cast<const unsigned long long*>(peer_bufs), epoch, vis_count,
                                     status));
+}
+
+int gsr_debug_exchange_trace(uint64_t* host_out) {
+  if (!host_out) return GSR_EINVAL;
+  return check(read_exchange_trace(reinterpret_cast<unsigned long long*>(host_out)));
 }
 
 int gsr_backward_rows_marked(void* stream, int P, int p_begin, int p_end, int width, int height,

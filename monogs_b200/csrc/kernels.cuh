@@ -94,9 +94,10 @@ struct XchgLayout {
 constexpr int XCHG_MAX_CTAS = 256;
 constexpr int XCHG_MAX_WORLD = 32;
 XchgLayout xchg_layout(int P, int world);
-cudaError_t launch_rows_exchange(cudaStream_t st, int P, int rank, int world, int n_ctas, void* local_buf,
-                                 void* multicast_buf, const unsigned long long* peer_bufs, uint32_t epoch,
-                                 float* vis_count, int* status);
+cudaError_t launch_rows_exchange(cudaStream_t st, int P, int capacity, int rank, int world, int n_ctas,
+                                 void* local_buf, void* multicast_buf, const unsigned long long* peer_bufs,
+                                 uint32_t epoch, float* vis_count, int* status);
+cudaError_t read_exchange_trace(unsigned long long* host_out /*[5]*/);
 
 // stats.cu
 constexpr int VIS_MAX_KEYFRAMES = 16;  // keyframes per window the visibility kernel takes in one launch

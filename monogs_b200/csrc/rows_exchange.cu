@@ -73,7 +73,10 @@ GSR_DEVINL unsigned long long xchg_now_ns() {
 // arrival at epoch e is the value e in word [c][q] of EVERY rank's flags.
 GSR_DEVINL void xchg_barrier(char* local, const unsigned long long* peers, size_t flags_off, int rank, int world,
                              uint32_t epoch, int* status) {
-  __threadfence_system();
+  // Release pattern with cumulativity (PTX memory model): the CTA barrier orders every thread's earlier writes
+  // (incl. the relaxed multimem stores) before the flag threads, whose fence.sys + st.release.sys then publish them
+  // at system scope -- ONE fence per flag thread instead of one per thread of the CTA (round 1: 1024 x 148 fences
+  // per barrier, 13-21 us per barrier at 2 GPUs).
   __syncthreads();
   const int t = threadIdx.x;
   if (t < world) {
@@ -94,12 +97,18 @@ GSR_DEVINL void xchg_barrier(char* local, const unsigned long long* peers, size_
   __syncthreads();
 }
 
+// Phase timestamps of the LAST exchange on this device (CTA 0, thread 0; globaltimer ns): kernel start, phase 0 done,
+// barrier 1 passed, phase 1 done, barrier 2 passed. Read back with gsr_debug_exchange_trace (tools/xchg_check.py).
+__device__ unsigned long long g_xchg_trace[5];
+
 __global__ void __launch_bounds__(XCHG_THREADS, 1)
 rows_exchange_kernel(int P, int rank, int world, char* __restrict__ local, char* __restrict__ mc,
                      const unsigned long long* __restrict__ peers, XchgLayout L, uint32_t epoch,
                      float* __restrict__ vis_count, int* __restrict__ status) {
   pdl_launch_dependents();
   pdl_wait();
+  const bool tracer = blockIdx.x == 0 && threadIdx.x == 0;
+  if (tracer) g_xchg_trace[0] = xchg_now_ns();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nC = gridDim.x, c = blockIdx.x;
   const int n_gran = L.n_gran;
@@ -127,7 +136,9 @@ rows_exchange_kernel(int P, int rank, int world, char* __restrict__ local, char*
       mm_st(mc + off, *reinterpret_cast<const float4*>(local + off));
     }
   }
+  if (tracer) g_xchg_trace[1] = xchg_now_ns();
   xchg_barrier(local, peers, L.flags, rank, world, epoch, status);
+  if (tracer) g_xchg_trace[2] = xchg_now_ns();
 
   // ---- phase 1a: visibility sum (every rank, all Gaussians) ----
   if (vis_count) {
@@ -181,17 +192,26 @@ rows_exchange_kernel(int P, int rank, int world, char* __restrict__ local, char*
         if (off[i] != ~(size_t)0) mm_st(mc + L.rows + off[i], v[i]);
     }
   }
+  if (tracer) g_xchg_trace[3] = xchg_now_ns();
   xchg_barrier(local, peers, L.flags, rank, world, epoch + 1, status);
+  if (tracer) g_xchg_trace[4] = xchg_now_ns();
 }
 
-cudaError_t launch_rows_exchange(cudaStream_t st, int P, int rank, int world, int n_ctas, void* local_buf,
-                                 void* multicast_buf, const unsigned long long* peer_bufs, uint32_t epoch,
-                                 float* vis_count, int* status) {
-  const XchgLayout L = xchg_layout(P, world);
+cudaError_t launch_rows_exchange(cudaStream_t st, int P, int capacity, int rank, int world, int n_ctas,
+                                 void* local_buf, void* multicast_buf, const unsigned long long* peer_bufs,
+                                 uint32_t epoch, float* vis_count, int* status) {
+  // offsets and slot strides follow the buffer's CAPACITY (so they never move while the map grows inside it);
+  // the loops cover the live P rows only
+  XchgLayout L = xchg_layout(capacity, world);
+  L.n_gran = (P + 127) / 128;
   count_launch();
   launch_k(rows_exchange_kernel, n_ctas, XCHG_THREADS, 0, st, P, rank, world, (char*)local_buf,
            (char*)multicast_buf, peer_bufs, L, epoch, vis_count, status);
   return cudaGetLastError();
+}
+
+cudaError_t read_exchange_trace(unsigned long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, g_xchg_trace, sizeof(g_xchg_trace));
 }
 
 }  // namespace gsr

@@ -111,30 +111,66 @@ class RowExchange:
         self.marks = None          # (touched_words_ptr, vis_u8_ptr) of this rank's slot, or None
         self.vis = None            # f32[P] visibility sum of the sparse mode
         self._name = None
-        self._buf = None
+        self._buf = None           # symmetric block (f32), sized for self._cap rows
+        self._plain = None         # ordinary rows buffer of the NCCL / gloo mode, f32[cap, 16]
+        self._hdl = self._peers = None
         self._P = 0
+        self._cap = 0              # grow-only row capacity of the current buffer
+        self._decided_mode = None  # survives re-allocations
 
     # -- allocation ------------------------------------------------------------------------------------------
+    @staticmethod
+    def _capacity_for(P: int, old: int) -> int:
+        """Grow-only row capacity: at least 1.5x the previous one, a multiple of 4096 rows."""
+        want = max(P, old + old // 2, 4096)
+        return (want + 4095) // 4096 * 4096
+
     def allocate(self, P: int, device) -> torch.Tensor:
+        """-> flat f32[P, 16] rows for the live P. The buffer behind it is sized for a grow-only CAPACITY, so a map
+        that grows by keyframe insertion / densification (every few iterations in MonoGS) re-uses the symmetric
+        block, its peer mappings and the mode decided on the first exchange; only outgrowing the capacity allocates
+        (and rendezvouses) again, and then the previous block and handle are dropped first."""
         device = torch.device(device)
         world = dist.get_world_size(self.group) if dist.is_initialized() else 1
         self._P = P
+        if self._buf is not None and P <= self._cap and self._buf.device == device:
+            return self._buf[:P * N_COLS].view(P, N_COLS)          # fits: same block, same marks, same decision
+        if self._plain is not None and P <= self._cap and self._plain.device == device:
+            return self._plain[:P]
+        cap = self._capacity_for(P, self._cap)
         if device.type == "cuda" and world > 1 and os.environ.get("GSR_XCHG", "auto") != "nccl":
+            self._release()
+            flat, err = None, None
             try:
-                flat = self._allocate_symmetric(P, device, world)
-                if flat is not None:
-                    return flat
-            except Exception as e:  # no symmetric memory / multicast on this system: NCCL ring/tree instead
-                self.report["symmetric_memory_error"] = repr(e)[:200]
-        return torch.empty(P, N_COLS, dtype=torch.float32, device=device)
+                flat = self._allocate_symmetric(P, cap, device, world)
+            except Exception as e:  # no symmetric memory / multicast on this system
+                err = repr(e)[:200]
+            # every rank must take the same branch (a rank-local failure would pair our spin-barrier kernel on one
+            # side with ncclAllReduce on the other and hang): agree with one MIN-allreduce of the outcome
+            ok = torch.tensor([1 if flat is not None else 0], dtype=torch.int32, device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+            if int(ok.item()) == 1:
+                return flat
+            if err is not None:
+                self.report["symmetric_memory_error"] = err
+            self._release()
+            self.candidates, self.mode, self.decided = ["all_reduce"], "all_reduce", True
+        self._cap = cap
+        self._plain = torch.empty(cap, N_COLS, dtype=torch.float32, device=device)
+        return self._plain[:P]
 
-    def _allocate_symmetric(self, P, device, world):
+    def _release(self):
+        """Drop the symmetric block, its rendezvous handle and the peer-pointer tensor before replacing them."""
+        self._buf = self._hdl = self._peers = self._plain = None
+        self.marks = self.vis = None
+
+    def _allocate_symmetric(self, P, cap, device, world):
         import ctypes as C
         import torch.distributed._symmetric_memory as symm_mem
         from . import _abi
         lib = _abi.load()
         grp = self.group if self.group is not None else dist.group.WORLD
-        total = int(lib.gsr_rows_exchange_bytes(P, world))
+        total = int(lib.gsr_rows_exchange_bytes(cap, world))
         if total == 0:
             return None
         t = symm_mem.empty(total // 4, dtype=torch.float32, device=device)
@@ -147,9 +183,10 @@ class RowExchange:
         torch.cuda.synchronize(device)
         offs = (C.c_size_t * 4)()
         wpr, vpr = C.c_int(0), C.c_int(0)
-        _abi.check(lib.gsr_rows_exchange_layout(P, world, offs, C.byref(wpr), C.byref(vpr)), "gsr_rows_exchange_layout")
+        _abi.check(lib.gsr_rows_exchange_layout(cap, world, offs, C.byref(wpr), C.byref(vpr)), "gsr_rows_exchange_layout")
         rank = dist.get_rank(self.group)
         self._lib, self._hdl, self._buf, self._name = lib, hdl, t, grp.group_name
+        self._cap = cap
         self._rank, self._world = rank, world
         self._offs, self._wpr, self._vpr = [int(o) for o in offs], int(wpr.value), int(vpr.value)
         base_off = int(getattr(hdl, "offset", 0) or 0)
@@ -159,20 +196,27 @@ class RowExchange:
         self._peers = torch.tensor([int(p) + base_off for p in hdl.buffer_ptrs], dtype=torch.int64, device=device)
         self.marks = (self._local_ptr + self._offs[1] + 4 * rank * self._wpr,
                       self._local_ptr + self._offs[2] + rank * self._vpr)
-        self.vis = torch.zeros(P, dtype=torch.float32, device=device)
+        self.vis = torch.zeros(cap, dtype=torch.float32, device=device)
         self._status = torch.zeros(1, dtype=torch.int32, device=device)
-        self._epoch = 1
+        self._epoch = 1   # a fresh (zero-filled) block restarts the barrier epochs on every rank alike
         sms = torch.cuda.get_device_properties(device).multi_processor_count
         self._ctas = max(1, min(int(os.environ.get("GSR_XCHG_CTAS", "148")), sms, 256))
         forced = os.environ.get("GSR_XCHG", "auto")
-        self.candidates = []
-        if forced in ("auto", "sparse"):
-            self.candidates.append("sparse")
-        if forced in ("auto", "multimem") and hasattr(torch.ops.symm_mem, "multimem_all_reduce_"):
-            self.candidates.append("multimem")
-        if forced in ("auto", "all_reduce") or not self.candidates:
-            self.candidates.append("all_reduce")
-        self.mode, self.decided = self.candidates[0], len(self.candidates) == 1
+        if self._decided_mode is not None and self._decided_mode != "all_reduce":
+            # a mode was already chosen (and the sparse kernel verified) on a smaller block of this window
+            self.candidates, self.mode, self.decided = [self._decided_mode], self._decided_mode, True
+        else:
+            self.candidates = []
+            if forced in ("auto", "sparse"):
+                self.candidates.append("sparse")
+            if forced in ("auto", "multimem") and hasattr(torch.ops.symm_mem, "multimem_all_reduce_"):
+                self.candidates.append("multimem")
+            if forced in ("auto", "all_reduce") or not self.candidates:
+                self.candidates.append("all_reduce")
+            # never "decided" up front while the sparse kernel is a candidate: its result is always checked once
+            # against a dense sum of the same rows (also when GSR_XCHG=sparse forces it)
+            self.mode = self.candidates[0]
+            self.decided = len(self.candidates) == 1 and self.candidates[0] != "sparse"
         return t[:P * N_COLS].view(P, N_COLS)
 
     def zero_marks(self):
@@ -186,15 +230,15 @@ class RowExchange:
 
     def vis_count(self, flat: torch.Tensor) -> torch.Tensor:
         """Number of keyframes (over all ranks) in which each Gaussian is visible, after the exchange."""
-        return self.vis if self.mode == "sparse" else flat[:, N_COLS - 1]
+        return self.vis[:flat.shape[0]] if self.mode == "sparse" else flat[:, N_COLS - 1]
 
     # -- the exchange ----------------------------------------------------------------------------------------
     def _run(self, mode, flat, p0, p1):
         if mode == "sparse":
             if p1 < self._P:
                 return None  # ranges: the sparse kernel runs once, when the last range is in place
-            rc = self._lib.gsr_rows_exchange(torch.cuda.current_stream(flat.device).cuda_stream, self._P, self._rank,
-                                             self._world, self._ctas, self._local_ptr, self._mc_ptr,
+            rc = self._lib.gsr_rows_exchange(torch.cuda.current_stream(flat.device).cuda_stream, self._P, self._cap,
+                                             self._rank, self._world, self._ctas, self._local_ptr, self._mc_ptr,
                                              self._peers.data_ptr(), self._epoch, self.vis.data_ptr(),
                                              self._status.data_ptr())
             self._epoch = (self._epoch + 2) & 0xFFFFFFFF
@@ -219,7 +263,10 @@ class RowExchange:
                 b[o:o + n].copy_(s)
 
         times, results = {}, {}
-        for mode in self.candidates:
+        trial = list(self.candidates)
+        if trial == ["sparse"]:            # forced sparse: still verified once, against ncclAllReduce of the same rows
+            trial.append("all_reduce")
+        for mode in trial:
             ts = []
             for rep in range(4):
                 restore()
@@ -233,7 +280,7 @@ class RowExchange:
                 if rep > 0:
                     ts.append(a.elapsed_time(e))
             times[mode] = sorted(ts)[len(ts) // 2]
-            results[mode] = (flat.clone(), self.vis.clone())
+            results[mode] = (flat.clone(), self.vis[:P].clone())
         ok = 1.0
         dense = next((m for m in ("multimem", "all_reduce") if m in results), None)
         if "sparse" in results and dense is not None:
@@ -245,7 +292,7 @@ class RowExchange:
             self.report.update(sparse_vs_dense_rel_err=err, sparse_vis_err=verr)
             if not (err <= 1e-5 and verr == 0.0) or int(self._status.item()) != 0:
                 ok = 0.0
-        order = list(self.candidates)
+        order = trial
         t = torch.tensor([times[m] for m in order] + [-ok], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         tl = [float(x) for x in t.tolist()]
@@ -253,8 +300,10 @@ class RowExchange:
         if -tl[-1] < 0.5:  # some rank saw a wrong sparse result: never use it
             agreed.pop("sparse", None)
             self.report["sparse_rejected"] = True
-        self.mode = min(agreed, key=agreed.get)
+        allowed = {m: v for m, v in agreed.items() if m in self.candidates} or agreed
+        self.mode = min(allowed, key=allowed.get)
         self.decided = True
+        self._decided_mode = self.mode
         import numpy as np
         o = self._offs[1] // 4 + self._rank * self._wpr
         words = self._buf.view(torch.int32)[o:o + self._wpr].cpu().numpy()
@@ -262,8 +311,14 @@ class RowExchange:
                            touched_rows_local=int(np.unpackbits(words.view(np.uint8)).sum()))
         restore()
 
-    def reduce(self, flat: torch.Tensor, p0: int, p1: int):
-        """Start the sum of rows [p0, p1); returns a handle with .wait() or None when already stream-ordered."""
+    def reduce(self, flat: torch.Tensor, p0: int, p1: int, marks_written: bool = True):
+        """Start the sum of rows [p0, p1); returns a handle with .wait() or None when already stream-ordered.
+        marks_written=False (a render backend that does not fill the touched-row bitmaps) rules the sparse kernel
+        out: it would exchange nothing."""
+        if not marks_written and "sparse" in self.candidates:
+            self.candidates = [m for m in self.candidates if m != "sparse"] or ["all_reduce"]
+            if self.mode == "sparse":
+                self.mode, self.decided = self.candidates[0], len(self.candidates) == 1
         if not self.decided:
             if (p0, p1) != (0, self._P):   # ranges are not supported by the sparse kernel's trial: drop it
                 self.candidates = [m for m in self.candidates if m != "sparse"] or ["all_reduce"]
@@ -288,6 +343,7 @@ class MappingWindow:
         self.exchange = RowExchange(group)
         self._flat: Optional[torch.Tensor] = None
         self._radii: Optional[torch.Tensor] = None
+        self._radii_buf: Optional[torch.Tensor] = None
 
     @property
     def world_size(self) -> int:
@@ -299,8 +355,10 @@ class MappingWindow:
 
     def _buffers(self, P: int, device) -> None:
         if self._flat is None or self._flat.shape[0] != P or self._flat.device != torch.device(device):
-            self._flat = self.exchange.allocate(P, device)
-            self._radii = torch.empty(P, dtype=torch.int32, device=device)
+            self._flat = self.exchange.allocate(P, device)   # same block while P stays inside its capacity
+            if self._radii_buf is None or self._radii_buf.numel() < P or self._radii_buf.device != torch.device(device):
+                self._radii_buf = torch.empty(self.exchange._cap or P, dtype=torch.int32, device=device)
+            self._radii = self._radii_buf[:P]
 
     def step(self, params: Dict[str, torch.Tensor], n_keyframes: int) -> WindowStepResult:
         """One window iteration: local keyframes -> partial sums -> exchange. `params` maps the names of
@@ -314,9 +372,11 @@ class MappingWindow:
         chunks = window_chunks(P, self.n_chunks if world > 1 else 1)
         works = []
 
+        marks_written = bool(getattr(self.render_fn, "accepts_marks", False))
+
         def chunk_done(p0, p1):
             if world > 1:
-                w = self.exchange.reduce(flat, p0, p1)
+                w = self.exchange.reduce(flat, p0, p1, marks_written=marks_written)
                 if w is not None:
                     works.append(w)
 

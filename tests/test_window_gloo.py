@@ -119,3 +119,26 @@ def test_two_ranks_equal_one_rank(built, tmp_path):
     assert torch.allclose(r0["g2"], ref["g2"], rtol=1e-5, atol=1e-12)
     assert sorted(list(r0["taus"]) + list(r1["taus"])) == list(range(N_KF))       # pose grads stay with their owner
     assert float(ref["vc"].max()) <= N_KF and float(ref["vc"].max()) >= 1
+
+
+def test_row_buffer_capacity_is_grow_only():
+    """the rows buffer must not be re-allocated on every change of P (keyframe insertion / densification
+    change P every few iterations): capacity grows by >= 1.5x, rows views of a smaller or slightly larger map share
+    the same storage, and a decided exchange mode survives."""
+    from monogs_b200 import window
+    ex = window.RowExchange()
+    a = ex.allocate(5000, "cpu")
+    assert a.shape == (5000, window.N_COLS) and ex._cap == 8192
+    ptr = a.untyped_storage().data_ptr()
+    b = ex.allocate(6000, "cpu")
+    assert b.shape == (6000, window.N_COLS) and b.untyped_storage().data_ptr() == ptr and ex._cap == 8192
+    c = ex.allocate(4000, "cpu")                        # pruning shrinks the map: still the same block
+    assert c.untyped_storage().data_ptr() == ptr
+    d = ex.allocate(9000, "cpu")                        # outgrown: one re-allocation to 1.5x
+    assert ex._cap == 12288 and d.shape == (9000, window.N_COLS) and d.untyped_storage().data_ptr() != ptr
+    assert ex.mode == "all_reduce" and ex.decided
+    w = window.MappingWindow(lambda *a, **k: None)
+    w._buffers(5000, "cpu")
+    f0 = w._flat.untyped_storage().data_ptr()
+    w._buffers(5100, "cpu")
+    assert w._flat.shape[0] == 5100 and w._flat.untyped_storage().data_ptr() == f0 and w._radii.shape[0] == 5100

@@ -33,7 +33,27 @@ def run_mode(mode, cams, targets, bg, sc, n_kf, n_streams=2):
     out["grad2d_norm"] = res.grad2d_norm.clone()
     out["vis_count"] = res.vis_count.clone()
     out["max_radii"] = res.max_radii.clone().float()
-    return out, w.exchange
+    return out, w.exchange, w
+
+
+def snapshot(res):
+    out = {k: v.clone() for k, v in res.grads.items()}
+    out["grad2d_norm"] = res.grad2d_norm.clone()
+    out["vis_count"] = res.vis_count.clone()
+    out["max_radii"] = res.max_radii.clone().float()
+    return out
+
+
+def exchange_trace_us():
+    """Phase durations (us) of the last gsr_rows_exchange on this device: marks multicast, barrier 1, row sums, barrier 2."""
+    import ctypes as C
+    from monogs_b200 import _abi
+    t = (C.c_uint64 * 5)()
+    torch.cuda.synchronize()
+    if _abi.load().gsr_debug_exchange_trace(t) != 0 or t[0] == 0:
+        return None
+    names = ("marks_multicast", "barrier1", "row_sums", "barrier2")
+    return {n: round((t[i + 1] - t[i]) / 1e3, 2) for i, n in enumerate(names)} | {"total": round((t[4] - t[0]) / 1e3, 2)}
 
 
 def main():
@@ -57,11 +77,16 @@ def main():
     report = {"world": world, "gaussians": a.gaussians, "keyframes": a.keyframes, "modes": {}}
     # reference result: ncclAllReduce, every local keyframe on ONE stream; the modes below also run the local
     # keyframes round-robin on two streams (MappingWindow n_streams=2), so that path is checked as well
-    ref, _ = run_mode("all_reduce", cams, targets, bg, sc, a.keyframes, n_streams=1)
+    ref, _, w_ref = run_mode("all_reduce", cams, targets, bg, sc, a.keyframes, n_streams=1)
     worst = 0.0
+    w_sparse = None
     for mode in ("sparse", "multimem"):
         try:
-            got, ex = run_mode(mode, cams, targets, bg, sc, a.keyframes)
+            got, ex, w_mode = run_mode(mode, cams, targets, bg, sc, a.keyframes)
+            if mode == "sparse":
+                w_sparse = w_mode
+                report["sparse_phases_us"] = exchange_trace_us()
+                report["sparse_report"] = {k: v for k, v in ex.report.items() if k != "symmetric_memory_error"}
         except Exception as e:  # noqa: BLE001
             report["modes"][mode] = {"error": repr(e)[:300]}
             continue
@@ -73,6 +98,26 @@ def main():
         report["modes"][mode] = {"used_mode": ex.mode, "rel_err": errs, "status": st}
         if ex.mode == mode:
             worst = max(worst, max(errs.values()))
+    # the map grows (keyframe insertion / densification): first past the buffer's capacity (one re-allocation and
+    # rendezvous, mode kept), then inside the new capacity (same block) -- both must still equal the NCCL sums
+    if w_sparse is not None:
+        g = torch.Generator().manual_seed(99)
+        grow = {}
+        for extra in (max(4096, a.gaussians // 20), max(8192, a.gaussians // 16)):
+            more = synth.make_scene(extra, synth.make_camera(a.kind), seed=7)
+            sc2 = {k: torch.cat([sc[k], more[k].to(dev)]).contiguous() for k in sc}
+            cap_before = w_sparse.exchange._cap
+            os.environ["GSR_XCHG"] = "sparse"
+            got2 = snapshot(w_sparse.step(sc2, a.keyframes))
+            os.environ["GSR_XCHG"] = "all_reduce"
+            ref2 = snapshot(w_ref.step(sc2, a.keyframes))
+            errs = {k: float((got2[k].reshape(r.shape) - r).abs().max()) / float(r.abs().max().clamp_min(1e-30))
+                    for k, r in ref2.items()}
+            grow[str(sc2["means3D"].shape[0])] = {"mode": w_sparse.exchange.mode, "capacity": w_sparse.exchange._cap,
+                                                  "reallocated": w_sparse.exchange._cap != cap_before,
+                                                  "rel_err": max(errs.values())}
+            worst = max(worst, max(errs.values()))
+        report["grow"] = grow
     t = torch.tensor([worst], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     report["worst_rel_err_all_ranks"] = float(t)
