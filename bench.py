@@ -189,6 +189,7 @@ class OursDeviceStep:
         self.tau = torch.zeros(6, device=dev)
         self.R = 0
         self.rows, self.chunks = None, None
+        self.zero_stream, self.zero_done = None, None
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream().cuda_stream)
@@ -204,6 +205,16 @@ class OursDeviceStep:
         st = self._stream()
         R = C.c_int64(0)
         self.n_touched.zero_()
+        self.zero_done = None
+        ex = getattr(self, "exchange", None)
+        if self.world > 1 and ex is not None and ex.decided and ex.mode == "sparse" and ex.marks is not None:
+            if self.zero_stream is None:
+                self.zero_stream = torch.cuda.Stream(device=wl.dev)
+            self.zero_stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.zero_stream):
+                self.rows.zero_()
+                self.zero_done = torch.cuda.Event()
+                self.zero_done.record(self.zero_stream)
         if self.cap < 0:  # first call of this shape: two-phase forward sizes the instance buffers
             rc = lib.gsr_forward_plan(st, P, 0, 0, W, H, sc["means3D"].data_ptr(), None, sc["colors"].data_ptr(),
                                       sc["opacities"].data_ptr(), sc["scales"].data_ptr(), 1.0,
@@ -258,6 +269,12 @@ class OursDeviceStep:
                                      self.plist.data_ptr(), R, wl.dcol.data_ptr(), wl.ddep.data_ptr(),
                                      self.scratch.data_ptr(), 0)
         assert rc == 0, rc
+        # sparse exchange decided: rows zero-filled on a side stream during the forward (step()), only touched rows
+        # written by the per-Gaussian backward (GSR_ROWS_TOUCHED_ONLY) -- what MappingWindow.step does
+        flags = 0
+        if self.zero_done is not None:
+            torch.cuda.current_stream().wait_event(self.zero_done)
+            flags = 2
         works = []
         for (p0, p1) in self.chunks:
             mk = self.exchange.marks or (None, None)
@@ -265,8 +282,8 @@ class OursDeviceStep:
                                               sc["scales"].data_ptr(), 1.0, sc["rotations"].data_ptr(),
                                               wl.view.data_ptr(), wl.proj.data_ptr(), wl.proj_raw.data_ptr(),
                                               wl.cam.tanfovx, wl.cam.tanfovy, self.radii.data_ptr(),
-                                              self.geom.data_ptr(), self.scratch.data_ptr(), self.rows.data_ptr(), 0,
-                                              self.means2D.data_ptr(), self.tau.data_ptr(), mk[0], mk[1], 0)
+                                              self.geom.data_ptr(), self.scratch.data_ptr(), self.rows.data_ptr(),
+                                              flags, self.means2D.data_ptr(), self.tau.data_ptr(), mk[0], mk[1], 0)
             assert rc == 0, rc
             w = self.exchange.reduce(self.rows, p0, p1)
             if w is not None:

@@ -227,7 +227,13 @@ int gsr_backward_l1(void* stream, int P, int sh_degree, int sh_coeffs,
  *   A Gaussian range is one contiguous slice of `rows`, so the caller can hand finished ranges to an
  *   allreduce while later ranges are still being computed. Ranges must be issued in ascending order; the
  *   call with p_end == P also writes dL_dtau[6] (rho | theta). dL_dmeans2D[P,3] is optional.
- *   Precomputed colours + scales/rotations only (what MonoGS's mapper renders with). */
+ *   Precomputed colours + scales/rotations only (what MonoGS's mapper renders with).
+ *   `accumulate` is a bit set: GSR_ROWS_ADD (1) adds to the rows instead of overwriting them;
+ *   GSR_ROWS_TOUCHED_ONLY (2): the caller zero-filled `rows` (or they hold earlier keyframes' sums) and only the rows
+ *   of Gaussians whose gradient is non-zero are written / added -- every other row is left untouched, and column 15
+ *   (the dense visibility flag) is not maintained (the sparse exchange carries visibility in vis_u8). */
+#define GSR_ROWS_ADD 1
+#define GSR_ROWS_TOUCHED_ONLY 2
 int gsr_backward_render(void* stream, int P, int width, int height, const float* background,
                         const void* geom_ws, const void* image_ws, const uint32_t* point_list,
                         int64_t num_rendered, const float* dL_dout_color, const float* dL_dout_depth,

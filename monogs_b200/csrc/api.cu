@@ -396,7 +396,7 @@ static int backward_impl(void* stream, int P, int sh_degree, int sh_coeffs, int 
   BackwardViews bw;
   carve_backward((char*)scratch, P, &bw);
   // the partial-gradient scratch is zeroed by the backward renderer's prologue kernel (alongside its tile ordering)
-  const size_t zero_bytes = carve_backward(nullptr, P, nullptr);
+  const size_t zero_bytes = bw.zero_bytes;
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
@@ -526,7 +526,7 @@ static int backward_render_impl(void* stream, int P, int width, int height, cons
   carve_image((char*)image_ws, width, height, &im);
   BackwardViews bw;
   carve_backward((char*)scratch, P, &bw);
-  const size_t zero_bytes = carve_backward(nullptr, P, nullptr);
+  const size_t zero_bytes = bw.zero_bytes;
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,

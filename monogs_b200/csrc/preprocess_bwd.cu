@@ -98,36 +98,122 @@ GSR_DEVINL V3 sh_backward(int deg, int M, const float* __restrict__ sh, const ui
 #ifndef PB_BLOCKS_PER_SM
 #define PB_BLOCKS_PER_SM 2
 #endif
-// One Gaussian's global input loads, all issued up front, unconditionally (the kernel is latency-bound: a chain
-// radii -> packed -> inputs would serialise three DRAM round trips).  Prefetching the next chunk's loads was
-// measured: the extra 23 registers spill and cost more than the overlap gains.
+// Loads of one Gaussian, in two groups. EVERY Gaussian streams its radius and its packed 48-byte gradient record
+// (52 B); only a TOUCHED Gaussian -- visible and with a non-zero record -- goes on to read its mean / scale /
+// rotation (44 B) and to run the ~500-instruction gradient chain. Everything the kernel outputs is linear in the ten
+// packed partials, so an all-zero record means all-zero outputs: on a map where most Gaussians are occluded or
+// off-screen for a given keyframe (headline scene: 3.5 % touched) the touched ones are compacted to the front
+// threads of the CTA and seven of its eight warps skip the arithmetic.
 struct PbLoads {
-  int radius;
-  float4 pk0, pk1, pk2, rot;
+  float4 rot;
   float m[3], s[3];
 };
-GSR_DEVINL PbLoads pb_issue_loads(int idx, int P, const int* __restrict__ radii, const float* __restrict__ packed,
-                                  const float* __restrict__ means3D, const float* __restrict__ scales,
+GSR_DEVINL PbLoads pb_issue_loads(int idx, const float* __restrict__ means3D, const float* __restrict__ scales,
                                   const float* __restrict__ rotations, bool has_cov3D) {
   PbLoads L;
-  L.radius = 0;
-  L.pk0 = make_float4(0.f, 0.f, 0.f, 0.f); L.pk1 = L.pk0; L.pk2 = L.pk0; L.rot = L.pk0;
+  L.rot = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-  for (int k = 0; k < 3; ++k) { L.m[k] = 0.f; L.s[k] = 0.f; }
-  if (idx < P) {
-    L.radius = __ldg(radii + idx);
-    L.pk0 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE));
-    L.pk1 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 4));
-    L.pk2 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 8));
+  for (int k = 0; k < 3; ++k) { L.s[k] = 0.f; L.m[k] = __ldg(means3D + 3 * (size_t)idx + k); }
+  if (!has_cov3D) {
 #pragma unroll
-    for (int k = 0; k < 3; ++k) L.m[k] = __ldg(means3D + 3 * (size_t)idx + k);
-    if (!has_cov3D) {
-#pragma unroll
-      for (int k = 0; k < 3; ++k) L.s[k] = __ldg(scales + 3 * (size_t)idx + k);
-      L.rot = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
-    }
+    for (int k = 0; k < 3; ++k) L.s[k] = __ldg(scales + 3 * (size_t)idx + k);
+    L.rot = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
   }
   return L;
+}
+
+// Kernel 1 of 2 (streaming, high occupancy): every Gaussian reads its radius and its packed record (52 B), is
+// classified, gets its marks written and -- when untouched -- its all-zero outputs; the touched ones of every
+// 256-Gaussian chunk are listed (chunk-local index, ascending) for kernel 2.
+__global__ void __launch_bounds__(PB_THREADS)
+preprocess_bwd_classify_kernel(int P, int M, const int* __restrict__ radii, const float* __restrict__ shs,
+                               const float* __restrict__ packed, float* __restrict__ dL_dmeans2D,
+                               float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
+                               float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
+                               float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
+                               float* __restrict__ dL_drots, float* __restrict__ dL_dtau_pg, int p_begin,
+                               float* __restrict__ rows, int accumulate, uint32_t* __restrict__ touched_words,
+                               uint8_t* __restrict__ vis_u8, uint16_t* __restrict__ touched_list,
+                               uint32_t* __restrict__ touched_count) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ uint32_t s_wcnt[PB_THREADS / 32];
+  const int tid = threadIdx.x;
+  const bool rows_touched_only = (accumulate & 2) != 0;   // rows pre-zeroed by the caller: only touched rows are written
+  const bool rows_add = (accumulate & 1) != 0;
+  const int n_chunks = (P - p_begin + PB_THREADS - 1) / PB_THREADS;
+  for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+  const int chunk_base = p_begin + chunk * PB_THREADS;  // P = end of this launch's Gaussian range
+  int n_touched = 0;
+  {  // ---- phase A (thread = Gaussian of the chunk): classify, marks, zero outputs of the untouched ----
+    const int idx = chunk_base + tid;
+    const bool in_range = idx < P;
+    int my_radius = 0;
+    float4 pk0 = make_float4(0.f, 0.f, 0.f, 0.f), pk1 = pk0, pk2 = pk0;
+    if (in_range) {
+      my_radius = __ldg(radii + idx);
+      pk0 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE));
+      pk1 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 4));
+      pk2 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 8));
+    }
+    const bool visible = in_range && my_radius > 0;
+    const bool nonzero = visible && (pk0.x != 0.f || pk0.y != 0.f || pk0.z != 0.f || pk0.w != 0.f || pk1.x != 0.f ||
+                                     pk1.y != 0.f || pk1.z != 0.f || pk1.w != 0.f || pk2.x != 0.f || pk2.y != 0.f);
+    // with SH colours the zero-gradient Gaussians still get their dL_dsh written by the full path
+    const bool touched = nonzero || (visible && shs && dL_dsh);
+    const unsigned bal = __ballot_sync(0xffffffffu, touched);
+    if (touched_words) {
+      // marks for the sparse window exchange (rows_exchange.cu): bit i of word idx/32 = this rank holds a non-zero
+      // gradient row for Gaussian idx; vis_u8 = number of this rank's keyframes that see the Gaussian.
+      const unsigned nz = __ballot_sync(0xffffffffu, nonzero);
+      if ((tid & 31) == 0 && in_range) {
+        uint32_t* wp = touched_words + (idx >> 5);
+        *wp = rows_add ? (*wp | nz) : nz;
+      }
+      if (in_range) vis_u8[idx] = (uint8_t)((rows_add ? vis_u8[idx] : 0) + (visible ? 1 : 0));
+    }
+    if ((tid & 31) == 0) s_wcnt[tid >> 5] = __popc(bal);
+    __syncthreads();
+    int before = 0;
+#pragma unroll
+    for (int w2 = 0; w2 < PB_THREADS / 32; ++w2) {
+      const int c = (int)s_wcnt[w2];
+      before += (w2 < (tid >> 5)) ? c : 0;
+      n_touched += c;
+    }
+    if (touched) touched_list[(size_t)chunk_base + before + __popc(bal & ((1u << (tid & 31)) - 1u))] = (uint16_t)tid;
+    if (in_range && !touched) {
+      // all-zero gradients (and, for the window rows, the visibility flag)
+      const size_t i3 = 3 * (size_t)idx;
+      if (dL_dmeans2D) { dL_dmeans2D[i3] = 0.f; dL_dmeans2D[i3 + 1] = 0.f; dL_dmeans2D[i3 + 2] = 0.f; }
+      if (dL_dcolors) { dL_dcolors[i3] = 0.f; dL_dcolors[i3 + 1] = 0.f; dL_dcolors[i3 + 2] = 0.f; }
+      if (dL_dopacity) dL_dopacity[idx] = 0.f;
+      if (dL_dmeans3D) { dL_dmeans3D[i3] = 0.f; dL_dmeans3D[i3 + 1] = 0.f; dL_dmeans3D[i3 + 2] = 0.f; }
+      if (dL_dcov3D) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) dL_dcov3D[6 * (size_t)idx + k] = 0.f;
+      }
+      if (dL_dsh) for (int k = 0; k < M * 3; ++k) dL_dsh[(size_t)idx * M * 3 + k] = 0.f;
+      if (dL_dscales) { dL_dscales[i3] = 0.f; dL_dscales[i3 + 1] = 0.f; dL_dscales[i3 + 2] = 0.f; }
+      if (dL_drots) *reinterpret_cast<float4*>(dL_drots + 4 * (size_t)idx) = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (dL_dtau_pg) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) dL_dtau_pg[6 * (size_t)idx + k] = 0.f;
+      }
+      if (rows && !rows_touched_only) {
+        float4* r4 = reinterpret_cast<float4*>(rows + 16 * (size_t)idx);
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rows_add) {
+          if (visible) rows[16 * (size_t)idx + 15] += 1.f;
+        } else {
+          r4[0] = z; r4[1] = z; r4[2] = z; r4[3] = make_float4(0.f, 0.f, 0.f, visible ? 1.f : 0.f);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (tid == 0) touched_count[chunk_base / PB_THREADS] = (uint32_t)n_touched;
+  }  // chunk loop
 }
 
 __global__ void __launch_bounds__(PB_THREADS, PB_BLOCKS_PER_SM)
@@ -143,8 +229,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       float* __restrict__ dL_dscales, float* __restrict__ dL_drots,
                       float* __restrict__ dL_dtau_pg, double* __restrict__ tau_partial, int p_begin,
                       float* __restrict__ rows /*[P,16] window rows or NULL*/, int accumulate,
-                      uint32_t* __restrict__ touched_words /*sparse exchange marks or NULL*/,
-                      uint8_t* __restrict__ vis_u8) {
+                      const uint16_t* __restrict__ touched_list, const uint32_t* __restrict__ touched_count) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float s_cam[40];
@@ -160,26 +245,35 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   const float* v = s_cam;
   const float* p = s_cam + 16;
 
-  // persistent grid: every CTA walks chunks of PB_THREADS Gaussians of the range [p_begin, P) and keeps ONE fp64
-  // pose-gradient accumulator per thread (fixed chunk assignment: the sums are deterministic)
+  // Kernel 2 of 2: the gradient chain for the touched Gaussians only. Persistent grid; WARP g of the grid walks the
+  // chunks g, g + n_warps, ... and its lanes take the chunk's listed Gaussians 32 at a time; every thread keeps ONE
+  // fp64 pose-gradient accumulator (fixed chunk -> warp and slot -> lane assignment: the sums are deterministic).
+  const bool rows_add = (accumulate & 1) != 0;
   double tacc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   const int n_chunks = (P - p_begin + PB_THREADS - 1) / PB_THREADS;
-  for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
-  const int idx = p_begin + chunk * PB_THREADS + tid;  // P = end of this launch's Gaussian range
+  const int lane = tid & 31;
+  const int n_warps = gridDim.x * (PB_THREADS / 32);
+  for (int chunk = blockIdx.x * (PB_THREADS / 32) + (tid >> 5); chunk < n_chunks; chunk += n_warps) {
+  const int chunk_base = p_begin + chunk * PB_THREADS;  // P = end of this launch's Gaussian range
+  const int n_touched = (int)touched_count[chunk_base / PB_THREADS];
+  for (int k0 = 0; k0 < n_touched; k0 += 32) {
+  // ---- phase B (thread k < n_touched = k-th touched Gaussian of the chunk): the gradient chain ----
   float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (k0 + lane < n_touched) {
+  const int idx = chunk_base + (int)touched_list[(size_t)chunk_base + k0 + lane];
   float g2x = 0.f, g2y = 0.f, gop = 0.f, gcr = 0.f, gcg = 0.f, gcb = 0.f;
   V3 dmean = v3(0, 0, 0);
   float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   float dscale[3] = {0.f, 0.f, 0.f};
   float drot[4] = {0.f, 0.f, 0.f, 0.f};
-  const bool in_range = idx < P;
-  const PbLoads L = pb_issue_loads(idx, P, radii, packed, means3D, scales, rotations, cov3D_precomp != nullptr);
-  const int my_radius = L.radius;
-  const float4 pk0 = L.pk0, pk1 = L.pk1, pk2 = L.pk2, ld_rot = L.rot;
+  // the record was read by this CTA a moment ago (L1 / L2 hit); the 44 B of parameters are read here only
+  const float4 pk0 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE));
+  const float4 pk1 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 4));
+  const float4 pk2 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 8));
+  const PbLoads L = pb_issue_loads(idx, means3D, scales, rotations, cov3D_precomp != nullptr);
+  const float4 ld_rot = L.rot;
   const float ld_m[3] = {L.m[0], L.m[1], L.m[2]}, ld_s[3] = {L.s[0], L.s[1], L.s[2]};
-  const bool visible = in_range && my_radius > 0;
-
-  if (visible) {
+  {
     g2x = pk0.x; g2y = pk0.y;
     const float dcx = pk0.z, dcy = pk0.w, dcz = pk1.x;
     gop = pk1.y; gcr = pk1.z; gcg = pk1.w; gcb = pk2.x;
@@ -357,11 +451,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       // the reference's dL_dscale is w.r.t. the UNmodified scale only through s = mod*scale in M;
       // it stores dot(Rt, dL_dMt) without the modifier (backward.cu:394-397) -- same here.
     }
-  } else if (in_range && shs && dL_dsh) {
-    for (int k = 0; k < M * 3; ++k) dL_dsh[(size_t)idx * M * 3 + k] = 0.f;
   }
-
-  if (in_range) {
+  {
     const size_t i3 = 3 * (size_t)idx;
     if (dL_dmeans2D) { dL_dmeans2D[i3] = g2x; dL_dmeans2D[i3 + 1] = g2y; dL_dmeans2D[i3 + 2] = 0.f; }
     if (dL_dcolors) { dL_dcolors[i3] = gcr; dL_dcolors[i3 + 1] = gcg; dL_dcolors[i3 + 2] = gcb; }
@@ -384,8 +475,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       float4 o0 = make_float4(dmean.x, dmean.y, dmean.z, gcr);
       float4 o1 = make_float4(gcg, gcb, gop, dscale[0]);
       float4 o2 = make_float4(dscale[1], dscale[2], drot[0], drot[1]);
-      float4 o3 = make_float4(drot[2], drot[3], visible ? sqrtf(g2x * g2x + g2y * g2y) : 0.f, visible ? 1.f : 0.f);
-      if (accumulate) {
+      float4 o3 = make_float4(drot[2], drot[3], sqrtf(g2x * g2x + g2y * g2y), 1.f);
+      if (rows_add) {
         const float4 a0 = r4[0], a1 = r4[1], a2 = r4[2], a3 = r4[3];
         o0.x += a0.x; o0.y += a0.y; o0.z += a0.z; o0.w += a0.w;
         o1.x += a1.x; o1.y += a1.y; o1.z += a1.z; o1.w += a1.w;
@@ -395,21 +486,10 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       r4[0] = o0; r4[1] = o1; r4[2] = o2; r4[3] = o3;
     }
   }
-  if (touched_words) {
-    // marks for the sparse window exchange (rows_exchange.cu): bit i of word idx/32 = this rank holds a non-zero
-    // gradient row for Gaussian idx (every output above is linear in the ten packed partials, so an all-zero record
-    // gives an all-zero row); vis_u8 = number of this rank's keyframes that see the Gaussian.
-    const bool t = visible && (pk0.x != 0.f || pk0.y != 0.f || pk0.z != 0.f || pk0.w != 0.f || pk1.x != 0.f ||
-                               pk1.y != 0.f || pk1.z != 0.f || pk1.w != 0.f || pk2.x != 0.f || pk2.y != 0.f);
-    const unsigned bal = __ballot_sync(0xffffffffu, t);
-    if ((tid & 31) == 0 && in_range) {
-      uint32_t* wp = touched_words + (idx >> 5);
-      *wp = accumulate ? (*wp | bal) : bal;
-    }
-    if (in_range) vis_u8[idx] = (uint8_t)((accumulate ? vis_u8[idx] : 0) + (visible ? 1 : 0));
-  }
+  }  // touched
 #pragma unroll
   for (int k = 0; k < 6; ++k) tacc[k] += (double)tau[k];
+  }  // 32 listed Gaussians
   }  // chunk loop
 
   // ---- block reduction of dL/dtau in fp64 ----
@@ -473,16 +553,23 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
   const float focal_x = W / (2.0f * tan_fovx);
   // p_begin is a multiple of 256 (checked by the caller); persistent grid of 148 SMs x PB_BLOCKS_PER_SM CTAs. Partial slot of CTA b
   // = p_begin / 256 + b: distinct over the ranges of one backward; slots no CTA writes stay zero (memset with packed)
-  int nb = num_pre_blocks(p_end - p_begin);
+  const int n_chunks = num_pre_blocks(p_end - p_begin);
+  int nb = (n_chunks + PB_THREADS / 32 - 1) / (PB_THREADS / 32);   // kernel 2: one warp per chunk and round
   if (nb > 148 * PB_BLOCKS_PER_SM) nb = 148 * PB_BLOCKS_PER_SM;
-  if (nb > 0) {
+  if (n_chunks > 0) {
+    const int nb1 = n_chunks < 148 * 8 ? n_chunks : 148 * 8;
+    count_launch();
+    launch_k(preprocess_bwd_classify_kernel, nb1, PB_THREADS, 0, st, p_end, M, radii, shs, bw.packed, dL_dmeans2D,
+             dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drots, dL_dtau_pg, p_begin, rows,
+             accumulate, touched_words, vis_u8, bw.touched_list, bw.touched_count);
     count_launch();
     launch_k(preprocess_bwd_kernel, nb, PB_THREADS, 0, st, p_end, D, M, means3D, radii, shs, clamped, scales, rotations,
                                                      scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
                                                      projmatrix_raw, campos, focal_x, focal_y, tan_fovx, tan_fovy,
                                                      bw.packed, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D,
                                                      dL_dcov3D, dL_dsh, dL_dscales, dL_drots, dL_dtau_pg,
-                                                     bw.tau_partial, p_begin, rows, accumulate, touched_words, vis_u8);
+                                                     bw.tau_partial, p_begin, rows, accumulate, bw.touched_list,
+                                                     bw.touched_count);
   }
   // the pose gradient is complete once the LAST range has run (ranges are issued in ascending order)
   if (dL_dtau && p_end == P) {

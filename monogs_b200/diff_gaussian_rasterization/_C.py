@@ -235,13 +235,16 @@ def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotati
                                       projmatrix, projmatrix_raw, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth,
                                       geomBuffer, R, point_list, imageBuffer, rows, accumulate, chunks=None,
                                       chunk_done=None, want_means2D=False, debug=False, marks=None, rows_gate=None,
-                                      l1_spec=None, image_hw=None):
+                                      l1_spec=None, image_hw=None, touched_only=False):
     """Backward of one keyframe of the sharded mapping window (gsr_backward_render + gsr_backward_rows): the
     Gaussian gradients are written / added into `rows` f32[P,16] (layout: include/gsr_b200.h) range by range;
     `chunk_done(p0, p1)` is called right after each range has been enqueued (the caller starts its allreduce of
     rows[p0:p1] there). `marks` = (touched_words_ptr, vis_u8_ptr): this rank's slot of the sparse window exchange
     (gsr_backward_rows_marked, monogs_b200.window.RowExchange.marks). `rows_gate`: a CUDA event the current stream
-    waits for before the per-Gaussian half (keyframes of one window on several streams accumulate in order). Returns (dL_dtau[6], dL_dmeans2D[P,3] or None)."""
+    waits for before the per-Gaussian half (keyframes of one window on several streams accumulate in order).
+    `touched_only`: `rows` was zero-filled by the caller (or holds earlier keyframes' sums) and only the rows of
+    Gaussians with a non-zero gradient are written / added (GSR_ROWS_TOUCHED_ONLY); column 15 is then not maintained.
+    Returns (dL_dtau[6], dL_dmeans2D[P,3] or None)."""
     lib = _abi.load()
     P = int(means3D.size(0))
     dev = means3D.device
@@ -281,7 +284,8 @@ def rasterize_gaussians_backward_rows(background, means3D, radii, scales, rotati
                                               float(scale_modifier), _ptr(ro), _ptr(vm), _ptr(pm), _ptr(pr),
                                               float(tan_fovx), float(tan_fovy), radii_c.data_ptr(),
                                               geomBuffer.data_ptr(), scratch.data_ptr(), rows.data_ptr(),
-                                              int(bool(accumulate)), _ptr(m2d), tau.data_ptr(),
+                                              int(bool(accumulate)) | (2 if touched_only else 0), _ptr(m2d),
+                                              tau.data_ptr(),
                                               marks[0] if marks else None, marks[1] if marks else None,
                                               int(bool(debug)))
             _abi.check(rc, "gsr_backward_rows_marked")

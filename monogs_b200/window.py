@@ -344,6 +344,7 @@ class MappingWindow:
         self._flat: Optional[torch.Tensor] = None
         self._radii: Optional[torch.Tensor] = None
         self._radii_buf: Optional[torch.Tensor] = None
+        self._zero_stream = None
 
     @property
     def world_size(self) -> int:
@@ -391,6 +392,21 @@ class MappingWindow:
         kwargs = {}
         if self.exchange.marks is not None and getattr(self.render_fn, "accepts_marks", False):
             kwargs["marks"] = self.exchange.marks
+        # Sparse exchange decided: the per-Gaussian backward only writes the rows it has a gradient for (a few % of the
+        # map per keyframe) into rows zero-filled HERE, on a side stream, while the forward renders -- instead of
+        # streaming 64 bytes per Gaussian through the rows kernel in front of the exchange.
+        zero_done = None
+        if (world > 1 and mine and dev.type == "cuda" and self.exchange.decided and self.exchange.mode == "sparse"
+                and "marks" in kwargs and getattr(self.render_fn, "accepts_touched_only", False) and len(chunks) == 1):
+            if self._zero_stream is None:
+                self._zero_stream = torch.cuda.Stream(device=dev)
+            main0 = torch.cuda.current_stream(dev)
+            self._zero_stream.wait_stream(main0)
+            with torch.cuda.stream(self._zero_stream):
+                flat.zero_()
+                zero_done = torch.cuda.Event()
+                zero_done.record(self._zero_stream)
+            kwargs["touched_only"] = True
         n_streams = min(self.n_streams, len(mine))
         if (n_streams > 1 and dev.type == "cuda" and len(chunks) == 1
                 and getattr(self.render_fn, "accepts_rows_gate", False)):
@@ -401,7 +417,7 @@ class MappingWindow:
             side = self._streams[:n_streams]
             for st in side:
                 st.wait_stream(main)
-            gate = None
+            gate = zero_done
             for i, k in enumerate(mine):
                 st = side[i % n_streams]
                 with torch.cuda.stream(st):
@@ -418,6 +434,10 @@ class MappingWindow:
         else:
             for i, k in enumerate(mine):
                 last = i == len(mine) - 1
+                if i == 0 and zero_done is not None:
+                    kwargs["rows_gate"] = zero_done
+                else:
+                    kwargs.pop("rows_gate", None)
                 r = self.render_fn(k, params, flat, i > 0, chunks, chunk_done if last else None, **kwargs)
                 torch.maximum(radii, r.radii.to(torch.int32), out=radii)
                 local.append(r)
@@ -468,7 +488,8 @@ def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
     if fused and loss_grad is not None:
         raise ValueError("fused_loss=True evaluates the built-in mapping loss; it cannot be combined with loss_grad")
 
-    def render(k, params, flat, accumulate, chunks, chunk_done, marks=None, rows_gate=None) -> KeyframeResult:
+    def render(k, params, flat, accumulate, chunks, chunk_done, marks=None, rows_gate=None,
+               touched_only=False) -> KeyframeResult:
         cam = cameras[k]
         dev = flat.device
         if k not in cached:
@@ -479,7 +500,7 @@ def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
             bg, params["means3D"], params["colors"], params["opacities"], params["scales"], params["rotations"], 1.0,
             e, view, proj, proj_raw, cam.tanfovx, cam.tanfovy, cam.H, cam.W, e, 0, campos, False, False)
         gt_image, gt_depth = targets[k]
-        kw = dict(chunks=chunks, chunk_done=chunk_done, marks=marks, rows_gate=rows_gate)
+        kw = dict(chunks=chunks, chunk_done=chunk_done, marks=marks, rows_gate=rows_gate, touched_only=touched_only)
         if fused:
             lib = _abi.load()
             terms = torch.empty(8, dtype=torch.float32, device=dev)
@@ -507,4 +528,5 @@ def make_cuda_render_fn(cameras: Sequence, targets: Sequence, bg: torch.Tensor,
 
     render.accepts_marks = True
     render.accepts_rows_gate = True
+    render.accepts_touched_only = True
     return render

@@ -460,6 +460,20 @@ def test_window_rows_backward_equals_plain_backward(built):
         bg, sc["means3D"], radii, sc["scales"], sc["rotations"], 1.0, view, proj, proj_raw, cam.tanfovx, cam.tanfovy,
         dcol, ddep, geom, R, plist, img, rows, True, chunks=[(0, P)])
     assert rel_inf(n(rows), 2 * n(once)) <= 1e-5
+    # GSR_ROWS_TOUCHED_ONLY: into zero-filled rows only the Gaussians with a gradient are written (then added);
+    # columns 0..14 must equal the dense form, untouched rows stay exactly zero, column 15 is not maintained
+    sparse = torch.zeros(P, 16, device=DEV)
+    tau_s, _ = ours.rasterize_gaussians_backward_rows(
+        bg, sc["means3D"], radii, sc["scales"], sc["rotations"], 1.0, view, proj, proj_raw, cam.tanfovx, cam.tanfovy,
+        dcol, ddep, geom, R, plist, img, sparse, False, chunks=[(0, P)], touched_only=True)
+    assert rel_inf(n(sparse[:, :15]), n(once[:, :15])) <= 5e-5
+    untouched = (once[:, :15] == 0).all(1)
+    assert int(untouched.sum()) > 0 and float(sparse[untouched].abs().max()) == 0.0
+    assert rel_inf(n(tau_s), n(tau)) <= 1e-5
+    ours.rasterize_gaussians_backward_rows(
+        bg, sc["means3D"], radii, sc["scales"], sc["rotations"], 1.0, view, proj, proj_raw, cam.tanfovx, cam.tanfovy,
+        dcol, ddep, geom, R, plist, img, sparse, True, chunks=[(0, P)], touched_only=True)
+    assert rel_inf(n(sparse[:, :15]), 2 * n(once[:, :15])) <= 5e-5
 
 
 def test_mapping_window_cuda_backend_single_gpu(built):
