@@ -62,6 +62,8 @@ def main():
     ap.add_argument("--keyframes", type=int, default=5)
     ap.add_argument("--kind", default="tum")
     ap.add_argument("--out", default="")
+    ap.add_argument("--opacity-scale", type=float, default=1.0,
+                    help="multiply the opacities (a translucent map: most Gaussians receive a gradient = low occlusion)")
     a = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
@@ -71,10 +73,13 @@ def main():
 
     cams = synth.arc_cameras(a.kind, a.keyframes)
     sc = {k: v.to(dev) for k, v in synth.make_scene(a.gaussians, synth.make_camera(a.kind), seed=1).items()}
+    if a.opacity_scale != 1.0:
+        sc["opacities"] = (sc["opacities"] * a.opacity_scale).contiguous()
     targets = [tuple(t.to(dev) for t in synth.make_targets(c, seed=i)) for i, c in enumerate(cams)]
     bg = torch.tensor([0.1, 0.2, 0.3], device=dev)
 
-    report = {"world": world, "gaussians": a.gaussians, "keyframes": a.keyframes, "modes": {}}
+    report = {"world": world, "gaussians": a.gaussians, "keyframes": a.keyframes, "kind": a.kind,
+              "opacity_scale": a.opacity_scale, "modes": {}}
     # reference result: ncclAllReduce, every local keyframe on ONE stream; the modes below also run the local
     # keyframes round-robin on two streams (MappingWindow n_streams=2), so that path is checked as well
     ref, _, w_ref = run_mode("all_reduce", cams, targets, bg, sc, a.keyframes, n_streams=1)
@@ -98,6 +103,9 @@ def main():
         report["modes"][mode] = {"used_mode": ex.mode, "rel_err": errs, "status": st}
         if ex.mode == mode:
             worst = max(worst, max(errs.values()))
+    # rows that carry a gradient on SOME rank (what the sparse kernel moves) as a fraction of the map
+    nz = (ref["means3D"].abs().sum(1) + ref["colors"].abs().sum(1)) > 0
+    report["touched_fraction_union"] = float(nz.float().mean())
     # the map grows (keyframe insertion / densification): first past the buffer's capacity (one re-allocation and
     # rendezvous, mode kept), then inside the new capacity (same block) -- both must still equal the NCCL sums
     if w_sparse is not None:
