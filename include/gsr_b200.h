@@ -312,6 +312,23 @@ int gsr_insert_points(void* stream, int K, const int32_t* selected, const int64_
 int gsr_insert_finish(void* stream, int K, const float* dist2, const float* median_depth, int scale_cols,
                       float* scales, float* rotations, float* opacities);
 
+/* ---- map growth / pruning: the tensor surgery of GaussianModel (gaussian_splatting/scene/gaussian_model.py:642-778:
+ * cat_tensors_to_optimizer, _prune_optimizer, densification_postfix, prune_points) on capacity-backed row arrays
+ * (monogs_b200/optimizer_surgery.py is the drop-in host side).  All pointer tables are HOST arrays of device pointers.
+ *  gsr_rows_append   for every group g < n_groups (<= 8): param[g][P_old .. P_old+K) = new_rows[g] ([K, cols[g]] fp32)
+ *                    and, where given, exp_avg[g] / exp_avg_sq[g] rows [P_old, P_old+K) = 0 (the zeros_like extension
+ *                    of :711-718) -- ONE launch, O(K) (the reference's torch.cat copies all P_old rows 15 times).
+ *                    The arrays must have room for P_old + K rows.
+ *  gsr_rows_compact  stable compaction by keep[P] (uint8 0/1, = ~mask of prune_points :679-695) of n_arrays (<= 32) row
+ *                    arrays at once: row i of src[j] (row_bytes[j] bytes, a multiple of 4) moves to row
+ *                    #{i' < i : keep[i']} of dst[j] (dst != src). *new_count (device u32) = number of kept rows.
+ *                    ws: gsr_surgery_ws_bytes(P) bytes of device scratch. */
+size_t gsr_surgery_ws_bytes(int64_t P);
+int gsr_rows_append(void* stream, int n_groups, float* const* param, float* const* exp_avg, float* const* exp_avg_sq,
+                    const float* const* new_rows, const int* cols, int64_t P_old, int64_t K);
+int gsr_rows_compact(void* stream, int n_arrays, const void* const* src, void* const* dst, const int* row_bytes,
+                     int64_t P, const uint8_t* keep, uint32_t* new_count, void* ws);
+
 /* present[P] (uint8 0/1) = p_view.z > 0.2  (auxiliary.h:139-164). */
 int gsr_mark_visible(void* stream, int P, const float* means3D,
                      const float* viewmatrix, const float* projmatrix,

@@ -53,6 +53,9 @@ SIGNATURES = {
     "gsr_insert_points": (i32, [vp, i32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, f32, f32, f32, f32, vp, vp,
                                 vp]),
     "gsr_insert_finish": (i32, [vp, i32, vp, vp, i32, vp, vp, vp]),
+    "gsr_surgery_ws_bytes": (sz, [i64]),
+    "gsr_rows_append": (i32, [vp, i32, vp, vp, vp, vp, vp, i64, i64]),
+    "gsr_rows_compact": (i32, [vp, i32, vp, vp, vp, i64, vp, vp, vp]),
     "gsr_mark_visible": (i32, [vp, i32, vp, vp, vp, vp]),
     "gsr_knn_dist2": (i32, [vp, i32, vp, vp, vp]),
     "gsr_profile_enable": (i32, [i32]),

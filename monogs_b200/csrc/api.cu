@@ -684,6 +684,30 @@ int gsr_visibility_prune(void* stream, int P, int K, const int* const* n_touched
                                        to_prune));
 }
 
+size_t gsr_surgery_ws_bytes(int64_t P) { return P > 0 ? surgery_ws_bytes(P) : 256; }
+
+int gsr_rows_append(void* stream, int n_groups, float* const* param, float* const* exp_avg, float* const* exp_avg_sq,
+                    const float* const* new_rows, const int* cols, int64_t P_old, int64_t K) {
+  if (n_groups < 1 || n_groups > SURGERY_MAX_GROUPS || P_old < 0 || K < 0 || !param || !new_rows || !cols)
+    return GSR_EINVAL;
+  if (K == 0) return GSR_OK;
+  for (int g = 0; g < n_groups; ++g)
+    if (!param[g] || !new_rows[g] || cols[g] < 1) return GSR_EINVAL;
+  return check(launch_rows_append((cudaStream_t)stream, n_groups, param, exp_avg, exp_avg_sq, new_rows, cols, P_old, K));
+}
+
+int gsr_rows_compact(void* stream, int n_arrays, const void* const* src, void* const* dst, const int* row_bytes,
+                     int64_t P, const uint8_t* keep, uint32_t* new_count, void* ws) {
+  if (n_arrays < 0 || n_arrays > SURGERY_MAX_ARRAYS || P < 0 || P >= ((int64_t)1 << 32) || !new_count || !ws)
+    return GSR_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (P == 0) return check(cudaMemsetAsync(new_count, 0, sizeof(uint32_t), st));
+  if (!keep || (n_arrays > 0 && (!src || !dst || !row_bytes))) return GSR_EINVAL;
+  for (int j = 0; j < n_arrays; ++j)
+    if (!src[j] || !dst[j] || src[j] == dst[j] || row_bytes[j] < 4 || row_bytes[j] % 4 != 0) return GSR_EINVAL;
+  return check(launch_rows_compact(st, n_arrays, src, dst, row_bytes, P, keep, new_count, ws));
+}
+
 int gsr_knn_dist2(void* stream, int P, const float* points, float* mean_dist2, void* knn_ws) {
   if (P < 0) return GSR_EINVAL;
   if (P == 0) return GSR_OK;

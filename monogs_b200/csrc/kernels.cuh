@@ -99,6 +99,16 @@ cudaError_t launch_rows_exchange(cudaStream_t st, int P, int capacity, int rank,
                                  uint32_t epoch, float* vis_count, int* status);
 cudaError_t read_exchange_trace(unsigned long long* host_out /*[5]*/);
 
+// surgery.cu  (append rows to / compact the rows of the parameter + Adam-state arrays)
+constexpr int SURGERY_MAX_GROUPS = 8;
+constexpr int SURGERY_MAX_ARRAYS = 32;
+cudaError_t launch_rows_append(cudaStream_t st, int n_groups, float* const* param, float* const* exp_avg,
+                               float* const* exp_avg_sq, const float* const* rows, const int* cols, long long P_old,
+                               long long K);
+size_t surgery_ws_bytes(long long P);
+cudaError_t launch_rows_compact(cudaStream_t st, int n_arrays, const void* const* src, void* const* dst,
+                                const int* row_bytes, long long P, const uint8_t* keep, uint32_t* new_count, void* ws);
+
 // stats.cu
 constexpr int VIS_MAX_KEYFRAMES = 16;  // keyframes per window the visibility kernel takes in one launch
 cudaError_t launch_densify_stats(cudaStream_t st, int P, const int* radii, const float* grad2d, float* max_radii_2d,
