@@ -16,9 +16,15 @@ launches and ~15 framework ops.  The pose (R, T) and the exposure parameters are
 `step`; the map tensors are read in place (they do not change while tracking).  Results are the same kernels'
 results as `fused_loss.render_l1_loss(kind="tracking")` + `backward()`.
 
-The instance-list capacity is fixed at capture time (1.5 x the count of the first pose + slack); every replay
-copies its `num_rendered` to pinned memory and `overflowed()` tells whether a replay exceeded it (the images of that
-replay are then invalid: re-create the graph; nothing is written out of bounds).
+The instance-list capacity is fixed at capture time (1.5 x the count of the first pose + slack).  A replay whose
+`num_rendered` exceeds it writes nothing out of bounds, but its images are incomplete: the graph itself (device side,
+no host read) then turns the loss `terms[0]` and the pose gradient `tau` of that replay into NaN, so a caller that never
+asks `overflowed()` cannot silently optimise on a truncated render.  `overflowed()` (one host read of the pinned
+count) says so explicitly; `recapture()` sizes the lists for the current pose and captures again.
+
+The map tensors are captured BY ADDRESS: they must be contiguous fp32 CUDA tensors (a hidden converted copy would be
+frozen into the graph and the caller's later in-place updates never seen) -- anything else is refused.  After an
+in-place change of `scales` of an isotropic map ([P, 1], expanded here to [P, 3]) call `refresh_scales()`.
 """
 from __future__ import annotations
 
@@ -35,7 +41,7 @@ from .render import camera_constants
 class TrackingGraph:
     def __init__(self, cam_intrinsics, means, rotations, scales, opacity, features, bg_color, gt_rgb, gt_depth=None,
                  mask=None, grad_mask=None, R0: Optional[torch.Tensor] = None, T0: Optional[torch.Tensor] = None,
-                 want_gaussian_grads: bool = False, capacity_factor: float = 1.5):
+                 want_gaussian_grads: bool = False, capacity_factor: float = 1.5, capacity_slack: int = 65536):
         lib = self.lib = _abi.load()
         if not means.is_cuda:
             raise RuntimeError("monogs_b200.tracking: CUDA tensors required (there is no CPU path)")
@@ -49,9 +55,16 @@ class TrackingGraph:
         self.tanfovx, self.tanfovy, proj_T = camera_constants(cam_intrinsics)
         self.proj_T = proj_T.detach().contiguous()
         # the map: read in place (static storage for the lifetime of the graph)
-        self.means, self.rots, self.opac, self.feat = f(means, "means"), f(rotations, "rotations"), f(opacity, "opacity"), f(features, "features")
-        sc = f(scales, "scales")
-        self.scales = sc.expand(-1, 3).contiguous() if sc.shape[-1] == 1 else sc
+        def static(t, n):
+            t = t.detach()
+            if t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev:
+                raise RuntimeError(f"monogs_b200.tracking: `{n}` must be a contiguous float32 tensor on {dev} "
+                                   "(the graph captures its address; a converted copy would go stale)")
+            return t
+        self.means, self.rots, self.opac, self.feat = (static(means, "means"), static(rotations, "rotations"),
+                                                       static(opacity, "opacity"), static(features, "features"))
+        self._scales_src = static(scales, "scales")
+        self.scales = self._scales_src.expand(-1, 3).contiguous() if self._scales_src.shape[-1] == 1 else self._scales_src
         self.bg = f(bg_color, "bg")
         # per-frame targets (set_frame overwrites them in place)
         self.gt_rgb = f(gt_rgb, "gt_rgb").clone()
@@ -81,7 +94,16 @@ class TrackingGraph:
         self.acc = torch.empty(8, dtype=torch.float64, device=dev)
         self.up = torch.ones(1, **fo)
         self.total = torch.zeros(1, dtype=torch.int64).pin_memory()
-        # capacity from the first pose (one synchronising plan call, outside the graph)
+        self.total_dev = torch.zeros(1, dtype=torch.int64, device=dev)   # the replay's num_rendered, device side
+        self.over = torch.zeros(1, dtype=torch.bool, device=dev)
+        self.capacity_factor, self.capacity_slack = float(capacity_factor), int(capacity_slack)
+        self.graph = None
+        self._size_and_capture()
+
+    def _size_and_capture(self):
+        """Capacity from the current pose (one synchronising plan call, outside the graph), buffers, capture."""
+        lib, dev, P, W, H = self.lib, self.dev, self.P, self.W, self.H
+        ws = lambda n: torch.empty(max(int(n), 256), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             self._camera_setup()
             R = C.c_int64(0)
@@ -91,7 +113,7 @@ class TrackingGraph:
                                       self.tanfovx, self.tanfovy, 0, self.radii.data_ptr(), self.geom.data_ptr(),
                                       C.byref(R), 0)
             _abi.check(rc, "gsr_forward_plan")
-        self.capacity = int(R.value * capacity_factor) + 65536
+        self.capacity = max(int(R.value * self.capacity_factor) + self.capacity_slack, 1)
         self.plist = ws(lib.gsr_point_list_bytes(self.capacity))
         self.binning = ws(lib.gsr_binning_bytes(self.capacity)) if lib.gsr_binning_needed(W, H) else None
         self.spec = _abi.L1LossSpec(_abi.LOSS_TRACKING, self.color.data_ptr(), self.depth.data_ptr(),
@@ -100,6 +122,17 @@ class TrackingGraph:
                                     self.exposure.data_ptr() + 4, self.terms.data_ptr(), self.up.data_ptr())
         self.graph = None
         self._capture()
+
+    def refresh_scales(self):
+        """Re-expand an isotropic map's [P, 1] scales into the captured [P, 3] buffer (after an in-place update)."""
+        if self.scales is not self._scales_src:
+            self.scales.copy_(self._scales_src.expand(-1, 3))
+
+    def recapture(self):
+        """Size the instance lists for the CURRENT pose (self.R, self.T) and capture the graph again."""
+        torch.cuda.synchronize(self.dev)
+        self.graph = None
+        self._size_and_capture()
 
     # ------------------------------------------------------------------------------------------------------
     def _st(self):
@@ -122,8 +155,9 @@ class TrackingGraph:
                                      0, self.radii.data_ptr(), self.geom.data_ptr(), self.img.data_ptr(),
                                      _C._ptr(self.binning), self.plist.data_ptr(), self.capacity,
                                      self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr(),
-                                     self.n_touched.data_ptr(), self.total.data_ptr())
+                                     self.n_touched.data_ptr(), self.total_dev.data_ptr())
         _abi.check(rc, "gsr_forward_enqueue")
+        self.total.copy_(self.total_dev, non_blocking=True)
         rc = lib.gsr_l1_loss_forward(self._st(), _abi.LOSS_TRACKING, W, H, self.color.data_ptr(),
                                      self.depth.data_ptr(), self.opacity.data_ptr(), self.gt_rgb.data_ptr(),
                                      _C._ptr(self.gt_depth), _C._ptr(self.mask), _C._ptr(self.grad_mask),
@@ -140,6 +174,10 @@ class TrackingGraph:
                                  p("means2D"), p("colors"), p("opacity"), p("means3D"), None, None, p("scales"),
                                  p("rotations"), None, self.tau.data_ptr(), 0)
         _abi.check(rc, "gsr_backward_l1")
+        # a replay beyond the captured capacity rendered a truncated list: poison its loss and pose gradient
+        torch.gt(self.total_dev, self.capacity, out=self.over)
+        self.terms[0:1].masked_fill_(self.over, float("nan"))
+        self.tau.masked_fill_(self.over, float("nan"))
 
     def _capture(self):
         with torch.cuda.device(self.dev):

@@ -74,11 +74,28 @@ def test_graph_reports_capacity_overflow(built):
     gt_rgb, gt_depth = synth.make_targets(cam, seed=2, device=DEV)
     far = synth.make_camera("tum", trans=(0.0, 0.0, 40.0))      # from 40 m behind: almost nothing on screen
     w2c = far.w2c.to(DEV)
-    tg = tracking.TrackingGraph(ci, sc["means3D"], sc["rotations"], sc["scales"], sc["opacities"], sc["colors"], bg,
-                                gt_rgb, gt_depth, R0=w2c[:3, :3].contiguous(), T0=w2c[:3, 3].contiguous(),
-                                capacity_factor=1.0)
+    args = (ci, sc["means3D"], sc["rotations"], sc["scales"], sc["opacities"], sc["colors"], bg, gt_rgb, gt_depth)
+    tg = tracking.TrackingGraph(*args, R0=w2c[:3, :3].contiguous(), T0=w2c[:3, 3].contiguous(),
+                                capacity_factor=1.0, capacity_slack=0)
+    loss, g_rho, g_theta, _ = tg.step(w2c[:3, :3].contiguous(), w2c[:3, 3].contiguous())
+    assert not tg.overflowed() and bool(torch.isfinite(loss)) and bool(torch.isfinite(g_rho).all())
     near = cam.w2c.to(DEV)
-    tg.step(near[:3, :3].contiguous(), near[:3, 3].contiguous())
-    # the near pose has far more instances than the capacity captured for the far pose (+64 k slack) may hold
-    assert tg.overflowed() == (int(tg.total[0]) > tg.capacity)
+    Rn, Tn = near[:3, :3].contiguous(), near[:3, 3].contiguous()
+    loss, g_rho, g_theta, _ = tg.step(Rn, Tn)
+    # the near pose has far more instances than the capacity captured for the far pose holds: the replay itself
+    # must have poisoned its loss and pose gradient (device side), and overflowed() must say so
+    assert tg.overflowed() and int(tg.total[0]) > tg.capacity
+    assert bool(torch.isnan(loss)) and bool(torch.isnan(g_rho).all()) and bool(torch.isnan(g_theta).all())
+    tg.recapture()                                               # sized for the near pose now
+    loss, g_rho, g_theta, _ = tg.step(Rn, Tn)
+    assert not tg.overflowed() and bool(torch.isfinite(loss)) and bool(torch.isfinite(g_theta).all())
+    ea, eb = torch.zeros(1, device=DEV), torch.zeros(1, device=DEV)
+    ref = _eager(ci, sc, bg, Rn, Tn, gt_rgb, gt_depth, ea, eb)
+    assert abs(float(loss) - float(ref[0])) <= 1e-6 * abs(float(ref[0]))
+    assert rel_inf(g_rho.cpu().numpy(), ref[1].cpu().numpy()) <= 1e-5
+    # map tensors are captured by address: a strided view or another dtype would be frozen as a hidden copy
+    with pytest.raises(RuntimeError, match="contiguous float32"):
+        tracking.TrackingGraph(ci, sc["means3D"].double(), *args[2:])
+    with pytest.raises(RuntimeError, match="contiguous float32"):
+        tracking.TrackingGraph(ci, torch.cat([sc["means3D"], sc["means3D"]], 1)[:, :3], *args[2:])
     torch.cuda.synchronize()
