@@ -55,6 +55,7 @@ extern "C" {
 #define GSR_EPREFILTER (-4) /* prefiltered=1 but a point was culled        */
 #define GSR_EOVERFLOW (-5)  /* num_rendered does not fit the index type    */
 #define GSR_ECAPACITY (-6)  /* gsr_forward: num_rendered > capacity; re-run gsr_forward_render with *num_rendered */
+#define GSR_ESTATICLIMIT (-7) /* a *_static entry point: the size exceeds the fixed scratch built into the library */
 
 /* Library / build identification ("sm_100a", version). */
 const char* gsr_version(void);
@@ -305,6 +306,18 @@ int gsr_select_kth_f32(void* stream, int64_t n, const float* a, const float* b, 
 int gsr_insert_select(void* stream, int width, int height, const float* gt_depth, const float* render_depth,
                       const float* render_opacity, int init, const float* median_err, int32_t* selected,
                       uint32_t* count, void* ws);
+/* gsr_insert_select WITHOUT a workspace argument, for callers that cannot allocate device memory (CUDA graph capture,
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same kernels and same results as gsr_insert_select; the per-block counts live in
+ * a 16 KB `static __device__` array inside the library (held by every GPU that loads it until the process exits),
+ * which bounds the image: width * height <= GSR_INSERT_STATIC_MAX_PIXELS, else GSR_ESTATICLIMIT (nothing launched).
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  The device current at the
+ * call must be the stream's.  All calls on a device share the array: calls on one stream are ordered, calls that
+ * overlap on the GPU (different streams, no dependency) race and give undefined `selected` / `count`. */
+#define GSR_INSERT_STATIC_MAX_PIXELS (4 * 1024 * 1024)
+int gsr_insert_select_static(void* stream, int width, int height, const float* gt_depth, const float* render_depth,
+                             const float* render_opacity, int init, const float* median_err, int32_t* selected,
+                             uint32_t* count);
 int gsr_insert_points(void* stream, int K, const int32_t* selected, const int64_t* pick, int width, int height,
                       const float* rgb, const float* exposure_a, const float* exposure_b, const float* gt_depth,
                       const int32_t* segmentation, const float* R, const float* T, float fx, float fy, float cx,

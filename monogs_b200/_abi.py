@@ -50,6 +50,7 @@ SIGNATURES = {
     "gsr_insert_ws_bytes": (sz, [i32, i32]),
     "gsr_select_kth_f32": (i32, [vp, i64, vp, vp, i64, vp, vp]),
     "gsr_insert_select": (i32, [vp, i32, i32, vp, vp, vp, i32, vp, vp, vp, vp]),
+    "gsr_insert_select_static": (i32, [vp, i32, i32, vp, vp, vp, i32, vp, vp, vp]),
     "gsr_insert_points": (i32, [vp, i32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, f32, f32, f32, f32, vp, vp,
                                 vp]),
     "gsr_insert_finish": (i32, [vp, i32, vp, vp, i32, vp, vp, vp]),
@@ -84,6 +85,8 @@ STAGES = ("preprocess", "depth_sort", "scan", "emit", "tile_sort", "ranges", "re
           "preprocess_bwd")
 
 GSR_ECAPACITY = -6
+GSR_ESTATICLIMIT = -7
+INSERT_STATIC_MAX_PIXELS = 4 * 1024 * 1024
 
 ERRORS = {
     -1: "GSR_EINVAL: bad argument combination or size",
@@ -92,6 +95,8 @@ ERRORS = {
     -4: "GSR_EPREFILTER: point is filtered although prefiltered is set",
     -5: "GSR_EOVERFLOW: num_rendered exceeds 2^30 instances",
     -6: "GSR_ECAPACITY: num_rendered exceeds the capacity passed to gsr_forward",
+    -7: "GSR_ESTATICLIMIT: the size exceeds the fixed scratch array of a *_static entry point "
+        "(gsr_insert_select_static: width * height <= 4 Mi pixels); use the workspace variant",
 }
 
 _lib = None

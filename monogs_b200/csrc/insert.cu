@@ -8,6 +8,7 @@
 //   insert_finish_kernel      log-scale from the kNN distance (:294-306), identity rotation, opacity logit(0.5)
 // with distCUDA2 (knn.cu) in between.  The random subsample (:247-259) stays torch.randperm on the host RNG, like
 // the reference, so that a seeded run selects the same pixels.
+#include <mutex>
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -273,4 +274,53 @@ cudaError_t launch_insert_finish(cudaStream_t st, int K, const float* dist2, con
   return cudaGetLastError();
 }
 
+// ---- gsr_insert_select_static: the same two kernels with their scratch in a file-scope device array ----------
+// For callers that may not allocate device memory (stream capture, serving loops, harnesses that forbid cudaMalloc).
+// The block counts of insert_count_kernel live in g_insert_static_counts (16 KB, held by every GPU that loads the
+// library until the process exits) instead of a caller workspace.  Nothing in it has to start at zero: every word the
+// compaction kernel reads ([0, n_blocks)) was written by the count kernel of the SAME call.  All calls on a device
+// share the array, so two calls that overlap on the GPU (different streams) race; calls on one stream are ordered.
+constexpr int INSERT_STATIC_MAX_BLOCKS = GSR_INSERT_STATIC_MAX_PIXELS / INS_THREADS;
+static_assert(GSR_INSERT_STATIC_MAX_PIXELS % INS_THREADS == 0, "whole blocks");
+static __device__ __align__(256) uint32_t g_insert_static_counts[INSERT_STATIC_MAX_BLOCKS];
+
+namespace {
+constexpr int STATIC_MAX_DEVICES = 64;
+std::mutex g_static_mu;
+uint32_t* g_static_ptr[STATIC_MAX_DEVICES] = {};
+
+// The device address of g_insert_static_counts on the CURRENT device (the name itself is only a host-side handle);
+// looked up once per device.
+cudaError_t insert_static_scratch(uint32_t** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    uint32_t* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_insert_static_counts);
+    if (e != cudaSuccess) return e;
+    if (!p) return cudaErrorInvalidSymbol;
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return cudaSuccess;
+}
+}  // namespace
+
 }  // namespace gsr
+
+extern "C" int gsr_insert_select_static(void* stream, int width, int height, const float* gt_depth,
+                                        const float* render_depth, const float* render_opacity, int init,
+                                        const float* median_err, int32_t* selected, uint32_t* count) {
+  if (width <= 0 || height <= 0 || !gt_depth || !selected || !count) return GSR_EINVAL;
+  if (!init && (!render_depth || !median_err)) return GSR_EINVAL;
+  if ((long long)width * height > (long long)GSR_INSERT_STATIC_MAX_PIXELS) return GSR_ESTATICLIMIT;
+  uint32_t* counts = nullptr;
+  cudaError_t e = gsr::insert_static_scratch(&counts);
+  if (e != cudaSuccess) return (int)e;
+  e = gsr::launch_insert_select((cudaStream_t)stream, width, height, gt_depth, render_depth, render_opacity, init,
+                                median_err, selected, count, counts);
+  return e == cudaSuccess ? GSR_OK : (int)e;
+}
