@@ -410,12 +410,14 @@ int gsr_debug_geom_views(const void* geom_ws, int P, int width, int height, cons
 int gsr_debug_image_views(const void* image_ws, int width, int height,
                           const float** final_T, const uint32_t** n_contrib,
                           const uint32_t** ranges /*uint2[tiles]*/);
-/* 1 when a forward at this image size uses the instance radix sort and therefore needs the binning workspace
- * (gsr_binning_bytes); 0 when the sort-free binning is used: binning_ws may then be NULL. */
+/* 1 when a forward at this image size needs the binning workspace (gsr_binning_bytes): the two-level sort-free
+ * binning (bin lists) and the instance radix sort (keys) do; 0 when binning_ws may be NULL (single-level sort-free
+ * binning, a test mode). */
 int gsr_binning_needed(int width, int height);
-/* Test hook: 0 = automatic choice of the binning implementation (sort-free for images of <= 4096 tiles, instance
- * radix sort above), 1 = radix sort at every size. Both produce the identical point_list / ranges. A forward and
- * the gsr_debug_sorted_keys call that inspects it must run under the same mode. */
+/* Test hook: 0 = automatic choice of the binning implementation (two-level sort-free binning for images of up to
+ * 4096 bins of 4x4 tiles = 65 536 tiles, instance radix sort above), 1 = radix sort at every size, 2 = single-level
+ * sort-free binning where the image has <= 4096 tiles. All produce the identical point_list / ranges. A forward
+ * and the gsr_debug_sorted_keys call that inspects it must run under the same mode. */
 int gsr_debug_set_binning(int mode);
 /* Rebuilds the reference's sorted 64-bit keys (tile << 32 | depth bits, rasterizer_impl.cu:102-104) of the
  * LAST gsr_forward_render call that used these workspaces into keys_sorted[num_rendered] (device). */

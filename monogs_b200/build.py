@@ -19,7 +19,7 @@ OBJ = ROOT / "build"
 LIB = ROOT / "libgsr_b200.so"
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 SOURCES = ["preprocess.cu", "binning.cu", "radix_sort.cu", "render_fwd.cu", "render_bwd.cu",
-           "preprocess_bwd.cu", "knn.cu", "loss.cu", "tile_scatter.cu", "stats.cu", "rows_exchange.cu", "insert.cu", "surgery.cu", "api.cu"]
+           "preprocess_bwd.cu", "knn.cu", "loss.cu", "tile_scatter.cu", "tile_refine.cu", "stats.cu", "rows_exchange.cu", "insert.cu", "surgery.cu", "api.cu"]
 FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

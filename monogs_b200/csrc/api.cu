@@ -131,7 +131,10 @@ const char* gsr_version(void) { return "gsr_b200 0.1 (sm_100a)"; }
 size_t gsr_geom_bytes(int P, int width, int height) { return carve_geom(nullptr, P, width, height, nullptr); }
 size_t gsr_image_bytes(int width, int height) { return carve_image(nullptr, width, height, nullptr); }
 size_t gsr_point_list_bytes(int64_t R) { return align_up(4 * (size_t)(R > 0 ? R : 1)); }
-size_t gsr_binning_bytes(int64_t R) { return carve_binning(nullptr, R, nullptr); }
+size_t gsr_binning_bytes(int64_t R) {  // the larger of the radix-sort and the two-level layouts (any image size)
+  const size_t a = carve_binning(nullptr, R, nullptr), b = carve_refine(nullptr, R, (size_t)TS_MAX_TILES, nullptr);
+  return a > b ? a : b;
+}
 size_t gsr_backward_scratch_bytes(int P) { return carve_backward(nullptr, P, nullptr); }
 size_t gsr_knn_bytes(int P) { return knn_workspace_bytes(P); }
 
@@ -185,18 +188,25 @@ static SortPlan tile_sort_plan(int W, int H) { return make_sort_plan(higher_msb(
 
 // instance emit + tile sort + ranges + render. `cap` bounds the instances written; the actual count is read
 // from n_dev (device) when given, else it IS cap.
-// GSR_BINNING=radix forces the instance radix sort for every image size (A/B measurements, tests).
-// gsr_debug_set_binning overrides it at run time (tests compare the two implementations in one process).
-static std::atomic<int> g_binning_mode{-1};  // -1: not decided yet, 0: automatic, 1: radix everywhere
-static bool use_tile_scatter(int width, int height) {
+// Binning implementation: 2 = two-level sort-free binning (tile_scatter.cu on 4x4-tile bins + tile_refine.cu; the
+// default for images of up to TS_MAX_TILES bins), 1 = single-level sort-free binning (<= TS_MAX_TILES tiles),
+// 0 = instance radix sort (any size).  GSR_BINNING=radix / single forces a mode for every image size that admits it
+// (A/B measurements); gsr_debug_set_binning overrides it at run time (tests compare the implementations in one
+// process).
+enum { BIN_RADIX = 0, BIN_SINGLE = 1, BIN_TWO_LEVEL = 2 };
+static std::atomic<int> g_binning_mode{-1};  // -1: not decided yet, 0: automatic, 1: radix, 2: single-level
+static int binning_impl(int width, int height) {
   int mode = g_binning_mode.load();
   if (mode < 0) {
     const char* e = getenv("GSR_BINNING");
-    mode = (e && strcmp(e, "radix") == 0) ? 1 : 0;
+    mode = (e && strcmp(e, "radix") == 0) ? 1 : (e && strcmp(e, "single") == 0) ? 2 : 0;
     g_binning_mode.store(mode);
   }
-  return mode == 0 && num_tiles(width, height) <= (size_t)TS_MAX_TILES;
+  if (mode == 1) return BIN_RADIX;
+  if (mode == 2 && num_tiles(width, height) <= (size_t)TS_MAX_TILES) return BIN_SINGLE;
+  return num_bins(width, height) <= (size_t)TS_MAX_TILES ? BIN_TWO_LEVEL : BIN_RADIX;
 }
+static bool binning_ws_needed(int width, int height) { return binning_impl(width, height) != BIN_SINGLE; }
 
 static int enqueue_render(cudaStream_t st, int P, int width, int height, const float* background,
                           const GeomViews& g, const ImageViews& im, char* binning_ws, uint32_t* point_list,
@@ -204,7 +214,24 @@ static int enqueue_render(cudaStream_t st, int P, int width, int height, const f
                           float* out_opacity, int* n_touched, int debug) {
   const int tiles_x = (width + TILE_X - 1) / TILE_X;
   const size_t n_tiles = num_tiles(width, height);
-  if (use_tile_scatter(width, height)) {
+  const int impl = binning_impl(width, height);
+  if (impl == BIN_TWO_LEVEL) {
+    // level 1 (tile_scatter.cu on bins of 4x4 tiles) + level 2 (tile_refine.cu)
+    const int bins_x = (tiles_x + TS2_CB - 1) / TS2_CB, n_bins = (int)num_bins(width, height);
+    RefineViews rv;
+    carve_refine(binning_ws, cap, (size_t)n_bins, &rv);
+    {
+      StageTimer tm(st, GSR_STAGE_EMIT);
+      GSR_TRY(check(launch_bin_count(st, P, g, bins_x, n_bins)));
+      GSR_TRY(check(launch_bin_offsets_scatter(st, P, g, bins_x, n_bins, cap, rv)));
+    }
+    GSR_TRY(debug_sync(st, debug));
+    {
+      StageTimer tm(st, GSR_STAGE_TILE_SORT);
+      GSR_TRY(check(launch_refine(st, g, rv, width, height, cap, im.ranges, point_list)));
+    }
+    GSR_TRY(debug_sync(st, debug));
+  } else if (impl == BIN_SINGLE) {
     // sort-free binning (tile_scatter.cu): count matrix -> column scans -> in-order scatter
     {
       StageTimer tm(st, GSR_STAGE_EMIT);
@@ -296,7 +323,7 @@ int gsr_forward_render(void* stream, int P, int width, int height, const float* 
   if (P == 0) return GSR_OK;  // reference returns its zero-filled outputs (rasterize_points.cu:85)
   if (!background || !radii || !geom_ws || !image_ws || !out_color || !out_depth || !out_opacity || !n_touched)
     return GSR_EINVAL;
-  if (num_rendered > 0 && (!point_list || (!binning_ws && !use_tile_scatter(width, height)))) return GSR_EINVAL;
+  if (num_rendered > 0 && (!point_list || (!binning_ws && binning_ws_needed(width, height)))) return GSR_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
@@ -319,7 +346,7 @@ int gsr_forward_enqueue(void* stream, int P, int sh_degree, int sh_coeffs, int w
                              rotations, cov3D_precomp, viewmatrix, projmatrix, campos, radii, geom_ws));
   if (!background || !image_ws || !out_color || !out_depth || !out_opacity || !n_touched || !point_list)
     return GSR_EINVAL;
-  if (!binning_ws && !use_tile_scatter(width, height)) return GSR_EINVAL;
+  if (!binning_ws && binning_ws_needed(width, height)) return GSR_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
@@ -348,7 +375,7 @@ int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs, int width, in
   GSR_TRY(check_forward_args(P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
                              rotations, cov3D_precomp, viewmatrix, projmatrix, campos, radii, geom_ws));
   if (!background || !image_ws || !out_color || !out_depth || !out_opacity || !n_touched) return GSR_EINVAL;
-  if (capacity > 0 && (!point_list || (!binning_ws && !use_tile_scatter(width, height)))) return GSR_EINVAL;
+  if (capacity > 0 && (!point_list || (!binning_ws && binning_ws_needed(width, height)))) return GSR_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
@@ -787,11 +814,11 @@ int gsr_debug_image_views(const void* image_ws, int width, int height, const flo
 
 int gsr_binning_needed(int width, int height) {
   if (width <= 0 || height <= 0) return 0;
-  return use_tile_scatter(width, height) ? 0 : 1;
+  return binning_ws_needed(width, height) ? 1 : 0;
 }
 
 int gsr_debug_set_binning(int mode) {
-  if (mode != 0 && mode != 1) return GSR_EINVAL;
+  if (mode < 0 || mode > 2) return GSR_EINVAL;
   g_binning_mode.store(mode);
   return GSR_OK;
 }
@@ -801,7 +828,7 @@ int gsr_debug_sorted_keys(void* stream, const void* geom_ws, const void* binning
   if (!geom_ws || !keys_sorted || !point_list) return GSR_EINVAL;
   GeomViews g;
   carve_geom((char*)geom_ws, P, width, height, &g);
-  if (use_tile_scatter(width, height))
+  if (binning_impl(width, height) != BIN_RADIX)
     return check(launch_rebuild_keys_from_starts((cudaStream_t)stream, num_rendered, (int)num_tiles(width, height), g,
                                                  point_list, keys_sorted));
   if (!binning_ws) return GSR_EINVAL;

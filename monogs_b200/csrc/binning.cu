@@ -29,26 +29,32 @@ GSR_DEVINL uint32_t rect_count(uint2 r) {  // r.x = x0 | x1 << 16, r.y = y0 | y1
 // Tile rectangles into depth order + instance count of every 256-Gaussian chunk of the depth-ordered list.
 __global__ void __launch_bounds__(256)
 gather_rects_kernel(int P, const uint32_t* __restrict__ order, const uint2* __restrict__ rect,
-                    uint2* __restrict__ rect_sorted, uint32_t* __restrict__ chunk_sums) {
+                    uint2* __restrict__ rect_sorted, uint32_t* __restrict__ chunk_sums,
+                    uint32_t* __restrict__ chunk_sums_c /* bin-level instance counts (two-level binning) or NULL */) {
   pdl_launch_dependents();
   pdl_wait();
-  __shared__ uint32_t s_w[8];
+  __shared__ uint32_t s_w[8], s_c[8];
   const int s = blockIdx.x * 256 + threadIdx.x;
-  uint32_t v = 0;
+  uint32_t v = 0, vc = 0;
   if (s < P) {
     const uint2 r = rect[order[s]];
     rect_sorted[s] = r;
     v = rect_count(r);
+    vc = rect_count(ts_coarse_rect(r));
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
+  for (int o = 16; o > 0; o >>= 1) {
+    v += __shfl_xor_sync(0xffffffffu, v, o);
+    vc += __shfl_xor_sync(0xffffffffu, vc, o);
+  }
+  if ((threadIdx.x & 31) == 0) { s_w[threadIdx.x >> 5] = v; s_c[threadIdx.x >> 5] = vc; }
   __syncthreads();
   if (threadIdx.x == 0) {
-    uint32_t t = 0;
+    uint32_t t = 0, tc = 0;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) t += s_w[w];
+    for (int w = 0; w < 8; ++w) { t += s_w[w]; tc += s_c[w]; }
     chunk_sums[blockIdx.x] = t;
+    if (chunk_sums_c) chunk_sums_c[blockIdx.x] = tc;
   }
 }
 
@@ -162,7 +168,8 @@ rebuild_keys_kernel(long long L, const uint32_t* __restrict__ tkeys_sorted, cons
 }
 
 cudaError_t launch_gather_rects(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g) {
-  count_launch(); launch_k(gather_rects_kernel, num_pre_blocks(P), 256, 0, st, P, order, g.rect, g.rect_sorted, g.chunk_offsets);
+  count_launch(); launch_k(gather_rects_kernel, num_pre_blocks(P), 256, 0, st, P, order, g.rect, g.rect_sorted, g.chunk_offsets,
+           g.chunk_offsets_c);
   return cudaGetLastError();
 }
 

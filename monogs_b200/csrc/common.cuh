@@ -39,6 +39,13 @@ struct GeomViews {
   uint32_t* ts_totals;       // [tiles] instances of every tile
   uint32_t* ts_start;        // [tiles] first list position of every tile
   uint32_t* chunk_offsets;   // [ceil(P/256)+1] exclusive instance offsets of 256-Gaussian chunks, depth order
+  // two-level binning (tile_scatter.cu level 1 on 4x4-tile bins, tile_refine.cu level 2)
+  uint32_t* chunk_offsets_c; // [ceil(P/256)+1] the same for bin-level instances
+  uint32_t* ts_ctotals;      // [bins + 1] bin-level instances of every bin
+  uint32_t* ts_cstart;       // [bins + 1] first bin-list position of every bin
+  uint32_t* ts_seg_prefix;   // [bins + 1] first segment (TS2_SEG bin-list entries) of every bin; [bins] = segment count
+  unsigned long long* total_c; // [1] bin-level instance count
+  uint32_t* refine_ticket;   // [1] (zeroed region)
   // --- small region zeroed at the start of every forward ---
   uint32_t* hist;            // [4*256] depth digit histograms -> exclusive offsets
   uint32_t* tickets;         // [4]
@@ -84,6 +91,15 @@ inline SortPlan make_sort_plan(int total_bits) {
 }
 
 constexpr int TS_MAX_TILES = 4096;   // above this the per-tile shared-memory state no longer fits: radix path
+// Two-level binning: level 1 scatters into bins of TS2_CB x TS2_CB tiles, level 2 splits every bin list into its tiles.
+constexpr int TS2_CSHIFT = 2;
+constexpr int TS2_CB = 1 << TS2_CSHIFT;
+constexpr int TS2_BIN_TILES = TS2_CB * TS2_CB;         // 16 tiles per bin = one bit each of a u16 mask
+constexpr int TS2_SEG = 2048;                          // bin-list entries one level-2 CTA handles
+__host__ __device__ inline size_t num_bins(int W, int H) {
+  const size_t tx = (W + TILE_X - 1) / TILE_X, ty = (H + TILE_Y - 1) / TILE_Y;
+  return ((tx + TS2_CB - 1) / TS2_CB) * ((ty + TS2_CB - 1) / TS2_CB);
+}
 #ifndef TS_ITEMS_PER_THREAD
 #define TS_ITEMS_PER_THREAD 8          // instances per thread and piece of the scatter kernel
 #endif
@@ -100,8 +116,19 @@ __host__ __device__ inline int ts_blocks(size_t n_tiles) {
   occ = occ > TS_MAX_OCC ? TS_MAX_OCC : (occ < 1 ? 1 : occ);
   return 148 * (int)occ;
 }
+#ifndef GSR_TS_COARSE_OCC
+#define GSR_TS_COARSE_OCC TS_MAX_OCC
+#endif
+__host__ __device__ inline int ts_blocks_coarse(size_t n_bins) {  // level 1 of the two-level binning (+ staged masks)
+  const size_t smem = (size_t)TS_GROUP_SMEM + 256 * TS_ITEMS_PER_THREAD * 2 + n_bins * TS_TILE_SMEM + 1024;
+  size_t occ = (size_t)232448 / smem;
+  occ = occ > GSR_TS_COARSE_OCC ? GSR_TS_COARSE_OCC : (occ < 1 ? 1 : occ);
+  return 148 * (int)occ;
+}
 __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, GeomViews* v) {
   const size_t ts_tiles = num_tiles(W, H) <= (size_t)TS_MAX_TILES ? num_tiles(W, H) : 0;
+  const size_t ts_bins = num_bins(W, H) <= (size_t)TS_MAX_TILES ? num_bins(W, H) : 0;
+  const size_t fine_tiles = ts_bins ? num_tiles(W, H) : 0;
   size_t off = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
   char* a = take(sizeof(float4) * 3 * (size_t)P);
@@ -111,9 +138,14 @@ __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, Ge
   char* ka = take(4 * (size_t)P); char* kb = take(4 * (size_t)P);
   char* oa = take(4 * (size_t)P); char* ob = take(4 * (size_t)P);
   char* co = take(sizeof(uint32_t) * (size_t)(num_pre_blocks(P) + 1));
-  char* tc = take(sizeof(uint32_t) * (size_t)ts_blocks(ts_tiles) * ts_tiles);
-  char* tto = take(sizeof(uint32_t) * (ts_tiles + 1));
-  char* tst = take(sizeof(uint32_t) * (ts_tiles + 1));
+  const size_t tc_words = (size_t)ts_blocks(ts_tiles) * ts_tiles, tc_words_c = (size_t)ts_blocks_coarse(ts_bins) * ts_bins;
+  char* tc = take(sizeof(uint32_t) * (tc_words > tc_words_c ? tc_words : tc_words_c));
+  char* tto = take(sizeof(uint32_t) * (fine_tiles + 1));
+  char* tst = take(sizeof(uint32_t) * (fine_tiles + 1));
+  char* coc = take(sizeof(uint32_t) * (size_t)(num_pre_blocks(P) + 1));
+  char* cto = take(sizeof(uint32_t) * (ts_bins + 1));
+  char* cst = take(sizeof(uint32_t) * (ts_bins + 1));
+  char* csp = take(sizeof(uint32_t) * (ts_bins + 1));
   size_t zb = off;
   char* h = take(sizeof(uint32_t) * 4 * 256);
   char* tk = take(sizeof(uint32_t) * 4);
@@ -129,6 +161,10 @@ __host__ __device__ inline size_t carve_geom(char* base, int P, int W, int H, Ge
     v->ts_counts = (uint32_t*)tc; v->ts_totals = (uint32_t*)tto; v->ts_start = (uint32_t*)tst;
     v->hist = (uint32_t*)h; v->tickets = (uint32_t*)tk; v->lookback = (uint32_t*)lb;
     v->total = (unsigned long long*)tot; v->error_flag = (int*)(tot ? tot + 64 : nullptr);
+    v->total_c = (unsigned long long*)(tot ? tot + 128 : nullptr);
+    v->refine_ticket = (uint32_t*)(tot ? tot + 192 : nullptr);
+    v->chunk_offsets_c = (uint32_t*)coc; v->ts_ctotals = (uint32_t*)cto; v->ts_cstart = (uint32_t*)cst;
+    v->ts_seg_prefix = (uint32_t*)csp;
     v->zero_begin = zb; v->zero_end = ze;
   }
   return off;
@@ -190,6 +226,34 @@ __host__ __device__ inline size_t carve_binning(char* base, int64_t R, BinningVi
     v->zero_begin = zb;
     v->lookback_off = (size_t)(lb - base);
     v->lookback_pass_bytes = 4 * sort_blocks(n) * SORT_RADIX;
+  }
+  return off;
+}
+
+// Two-level binning workspace (aliases the same caller buffer as BinningViews; never used together): the bin lists
+// written by level 1 and the per-segment tile counts of level 2.  Sized for `R` = the list capacity (the number of
+// bin-level instances never exceeds the number of tile-level instances).
+struct RefineViews {
+  uint32_t* ids;         // [R] Gaussian ids, bin-major, (depth, id) order inside a bin
+  uint16_t* masks;       // [R] which of the bin's 16 tiles the Gaussian's rectangle covers (bit 4*dy + dx)
+  uint32_t* seg_bin;     // [max_segs] bin of every segment
+  uint32_t* seg_counts;  // [max_segs][16] per-segment tile counts -> exclusive prefixes over the segments of a bin
+  uint32_t* warp_counts; // [max_segs][8][16] the same per warp (256 entries) of the segment
+  size_t max_segs;
+};
+__host__ __device__ inline size_t refine_max_segs(int64_t R, size_t n_bins) {
+  return (size_t)((R > 0 ? R : 0) / TS2_SEG) + n_bins + 1;
+}
+__host__ __device__ inline size_t carve_refine(char* base, int64_t R, size_t n_bins, RefineViews* v) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
+  const size_t n = (size_t)(R > 0 ? R : 1), segs = refine_max_segs(R, n_bins);
+  char* a = take(4 * n); char* b = take(2 * n); char* c = take(4 * segs); char* d = take(4 * segs * TS2_BIN_TILES);
+  char* e = take(4 * segs * TS2_BIN_TILES * (TS2_SEG / 256));
+  if (v) {
+    v->ids = (uint32_t*)a; v->masks = (uint16_t*)b; v->seg_bin = (uint32_t*)c; v->seg_counts = (uint32_t*)d;
+    v->warp_counts = (uint32_t*)e;
+    v->max_segs = segs;
   }
   return off;
 }
@@ -285,6 +349,13 @@ GSR_DEVINL uint32_t warp_peers(uint32_t v) {
 // once (pdl_launch_dependents) and waits for its predecessor's results (pdl_wait) before it touches global memory,
 // so launch latency, CTA scheduling and the shared-memory prologue overlap the predecessor's tail.  Every kernel
 // must execute pdl_wait on every path: completion of a grid then implies completion of all earlier grids.
+// Tile rectangle (x0 | x1 << 16, y0 | y1 << 16, exclusive ends) -> rectangle of TS2_CB x TS2_CB-tile bins.
+GSR_DEVINL uint2 ts_coarse_rect(uint2 r) {
+  const uint32_t x0 = r.x & 0xffffu, x1 = r.x >> 16, y0 = r.y & 0xffffu, y1 = r.y >> 16;
+  if (x1 <= x0 || y1 <= y0) return make_uint2(0u, 0u);
+  return make_uint2((x0 >> TS2_CSHIFT) | (((x1 + TS2_CB - 1) >> TS2_CSHIFT) << 16),
+                    (y0 >> TS2_CSHIFT) | (((y1 + TS2_CB - 1) >> TS2_CSHIFT) << 16));
+}
 GSR_DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 GSR_DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 

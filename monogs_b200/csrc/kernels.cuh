@@ -32,6 +32,12 @@ cudaError_t launch_rebuild_keys(cudaStream_t st, long long L, const uint32_t* tk
 cudaError_t launch_tile_count(cudaStream_t st, int P, const GeomViews& g, int tiles_x, int n_tiles);
 cudaError_t launch_tile_offsets_scatter(cudaStream_t st, int P, const GeomViews& g, int tiles_x, int n_tiles,
                                         long long cap, uint2* ranges, uint32_t* point_list);
+// two-level binning: level 1 on bins of TS2_CB x TS2_CB tiles (tile_scatter.cu), level 2 = tile_refine.cu
+cudaError_t launch_bin_count(cudaStream_t st, int P, const GeomViews& g, int bins_x, int n_bins);
+cudaError_t launch_bin_offsets_scatter(cudaStream_t st, int P, const GeomViews& g, int bins_x, int n_bins,
+                                       long long cap, const RefineViews& rv);
+cudaError_t launch_refine(cudaStream_t st, const GeomViews& g, const RefineViews& rv, int width, int height,
+                          long long cap, uint2* ranges, uint32_t* point_list);
 cudaError_t launch_rebuild_keys_from_starts(cudaStream_t st, long long L, int n_tiles, const GeomViews& g,
                                             const uint32_t* point_list, uint64_t* keys);
 

@@ -382,9 +382,11 @@ GSR_DEVINL uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp, uint
 // chunk sums -> exclusive chunk offsets (in place) + total = num_rendered (cub InclusiveSum, rasterizer_impl.cu:280).
 // One block; 4 consecutive chunks per thread and round (one 16-byte load), so 1M Gaussians are a single round.
 __global__ void __launch_bounds__(SCAN_THREADS)
-chunk_scan_kernel(int n_chunks, uint32_t* __restrict__ chunk_sums, unsigned long long* __restrict__ total) {
+chunk_scan_kernel(int n_chunks, uint32_t* __restrict__ chunk_sums, unsigned long long* __restrict__ total,
+                  uint32_t* __restrict__ chunk_sums_c, unsigned long long* __restrict__ total_c) {
   pdl_launch_dependents();
   pdl_wait();
+  if (blockIdx.x == 1) { chunk_sums = chunk_sums_c; total = total_c; }  // CTA 1: the bin-level counts
   __shared__ uint32_t s_warp[33];
   unsigned long long carry = 0;
   for (int base = 0; base < n_chunks; base += SCAN_THREADS * 4) {
@@ -484,7 +486,7 @@ cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, con
   const int nc = num_pre_blocks(P);
   cudaError_t e = launch_gather_rects(st, P, order, g);
   if (e != cudaSuccess) return e;
-  count_launch(); launch_k(chunk_scan_kernel, 1, SCAN_THREADS, 0, st, nc, g.chunk_offsets, g.total);
+  count_launch(); launch_k(chunk_scan_kernel, 2, SCAN_THREADS, 0, st, nc, g.chunk_offsets, g.total, g.chunk_offsets_c, g.total_c);
   return cudaGetLastError();
 }
 

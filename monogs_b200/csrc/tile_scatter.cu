@@ -14,6 +14,12 @@
 //                        tile counters, like one radix-sort CTA step but over the whole tile id) and writes the
 //                        Gaussian ids straight to their final slots                               (4 B/instance)
 // Instance keys are never written or read; traffic is ~4 B per instance instead of ~44 B.
+//
+// Two-level binning (COARSE = true; the default path for images of up to TS_MAX_TILES bins = 65 536 tiles): the same
+// three kernels run on BINS of 4x4 tiles -- a Gaussian of the headline scene covers 4.9 tiles but only 1.7 bins, and
+// with 80 instead of 1200 destinations the per-piece bookkeeping and the rank's vote count shrink -- and write, per
+// bin-level instance, the Gaussian id and a 16-bit mask of the bin's tiles its rectangle covers.  tile_refine.cu then
+// splits every bin list into its 16 tile lists with warp ballots (one vote ranks ~6 instances of one tile).
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -36,12 +42,18 @@ GSR_DEVINL void ts_block_range(const uint32_t* __restrict__ chunk_offsets, int n
                                int b, int nb, unsigned long long& k_lo, unsigned long long& k_hi, int& c0) {
   k_lo = total * (unsigned long long)b / nb;
   k_hi = total * (unsigned long long)(b + 1) / nb;
-  int l = 0, h = n_chunks - 1;  // last chunk whose first instance index is <= k_lo
-  while (l < h) {
-    const int m = (l + h + 1) >> 1;
-    if ((unsigned long long)chunk_offsets[m] <= k_lo) l = m; else h = m - 1;
+  // last chunk whose first instance index is <= k_lo, by a block-wide 256-ary search (two rounds of one load each
+  // for 1 M Gaussians, where a per-thread binary search is a chain of 12 dependent loads from L2)
+  int lo = 0, n = n_chunks;  // the answer lies in [lo, lo + n); chunk_offsets[lo] <= k_lo
+  while (n > 1) {
+    const int step = (n + TS_THREADS - 1) / TS_THREADS;
+    const int idx = lo + (int)threadIdx.x * step;
+    const int cnt = __syncthreads_count(idx < lo + n && (unsigned long long)chunk_offsets[idx] <= k_lo);
+    const int nlo = lo + (cnt > 0 ? cnt - 1 : 0) * step;
+    n = min(step, lo + n - nlo);
+    lo = nlo;
   }
-  c0 = l;
+  c0 = lo;
 }
 
 // Last chunk >= c whose first instance index is <= k (the chunk that contains instance k). Block-wide: every thread
@@ -67,7 +79,7 @@ GSR_DEVINL uint32_t ts_rect_count(uint2 r) { return ((r.x >> 16) - (r.x & 0xffff
 
 // Loads the window of TS_GROUP Gaussians that starts at chunk c (rectangles in depth order) and builds its instance
 // prefix. Returns the window's instance count.
-template <bool WITH_IDS>
+template <bool WITH_IDS, bool COARSE>
 GSR_DEVINL uint32_t ts_load_group(TsGroup& sg, int c, int P, const uint2* __restrict__ rect_sorted,
                                   const uint32_t* __restrict__ order) {
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -91,7 +103,7 @@ GSR_DEVINL uint32_t ts_load_group(TsGroup& sg, int c, int P, const uint2* __rest
   }
   uint32_t n[TS_GPT], mine = 0;
 #pragma unroll
-  for (int j = 0; j < TS_GPT; ++j) { n[j] = ts_rect_count(r[j]); mine += n[j]; }
+  for (int j = 0; j < TS_GPT; ++j) { n[j] = ts_rect_count(COARSE ? ts_coarse_rect(r[j]) : r[j]); mine += n[j]; }
   uint32_t inc = mine;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -118,10 +130,16 @@ GSR_DEVINL uint32_t ts_load_group(TsGroup& sg, int c, int P, const uint2* __rest
 
 // Walks a run of consecutive instances of the staged group: one binary search for the first instance, then
 // x/y/slot increments (row-major tile order inside a rectangle like rasterizer_impl.cu:98-109).
+template <bool COARSE>
 struct TsWalker {
   uint32_t slot, x, y, x0, x1, y1;
+  uint32_t fx0, fx1, fy0, fy1;  // COARSE: the tile rectangle (x, y, ... then walk its bins)
   GSR_DEVINL void load_rect(const TsGroup& sg) {
-    const uint2 r = sg.rect[slot];
+    uint2 r = sg.rect[slot];
+    if (COARSE) {
+      fx0 = r.x & 0xffffu; fx1 = r.x >> 16; fy0 = r.y & 0xffffu; fy1 = r.y >> 16;
+      r = ts_coarse_rect(r);
+    }
     x0 = r.x & 0xffffu; x1 = r.x >> 16; y = r.y & 0xffffu; y1 = r.y >> 16; x = x0;
   }
   GSR_DEVINL void seek(const TsGroup& sg, uint32_t k) {  // k < instance count of the group
@@ -135,6 +153,15 @@ struct TsWalker {
     y += row; x += j - row * wdt;
   }
   GSR_DEVINL uint32_t tile(int tiles_x) const { return y * (uint32_t)tiles_x + x; }
+  // COARSE: which of the 16 tiles of bin (x, y) the tile rectangle covers, bit 4 * dy + dx
+  GSR_DEVINL uint32_t mask() const {
+    const uint32_t bx = x << TS2_CSHIFT, by = y << TS2_CSHIFT;
+    const uint32_t lx0 = max(fx0, bx) - bx, lx1 = min(fx1, bx + TS2_CB) - bx;
+    const uint32_t ly0 = max(fy0, by) - by, ly1 = min(fy1, by + TS2_CB) - by;
+    const uint32_t row = (1u << lx1) - (1u << lx0);
+    const uint32_t rows = ((1u << (4u * ly1)) - (1u << (4u * ly0))) & 0x1111u;
+    return row * rows;
+  }
   GSR_DEVINL void next(const TsGroup& sg, uint32_t k_next) {  // k_next = index of the instance stepped to
     if (++x == x1) {
       x = x0;
@@ -147,6 +174,7 @@ struct TsWalker {
   }
 };
 
+template <bool COARSE>
 __global__ void __launch_bounds__(TS_THREADS)
 tile_count_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* __restrict__ chunk_offsets,
                   const unsigned long long* __restrict__ total_dev, int tiles_x, int n_tiles,
@@ -165,7 +193,7 @@ tile_count_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* 
   for (unsigned long long kk = k_lo; kk < k_hi;) {
     c = ts_advance_chunk(chunk_offsets, n_chunks, c, kk);
     const unsigned long long off = chunk_offsets[c];
-    const uint32_t n = ts_load_group<false>(sg, c, P, rect_sorted, nullptr);
+    const uint32_t n = ts_load_group<false, COARSE>(sg, c, P, rect_sorted, nullptr);
     const uint32_t b = (uint32_t)(kk - off);
     const uint32_t e = (uint32_t)min((unsigned long long)n, k_hi - off);
     if (e <= b) break;  // cannot happen (chunk c holds instance kk); never spin on inconsistent inputs
@@ -175,7 +203,7 @@ tile_count_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* 
       uint32_t k = b + tid * per;
       const uint32_t k_end = min(e, k + per);
       if (k < k_end) {
-        TsWalker wk;
+        TsWalker<COARSE> wk;
         wk.seek(sg, k);
         for (;;) {
           atomicAdd(&hist[wk.tile(tiles_x)], 1u);
@@ -234,12 +262,46 @@ constexpr int TS_STAGE_WORDS = TS_PIECE + TS_PIECE / 32;
 static_assert(sizeof(TsGroup) + TS_STAGE_WORDS * 4 <= TS_GROUP_SMEM, "ts_blocks() budgets TS_GROUP_SMEM bytes");
 static_assert(TS_GROUP <= 1024 && TS_MAX_TILES <= (1 << 12), "stage word = tile << 10 | slot; 13-bit peer masks");
 
+// a[0..n) (shared memory) -> its exclusive prefix, in place; returns the total. Block-wide (TS_THREADS threads).
+GSR_DEVINL uint32_t ts_block_scan(uint32_t* a, int n, uint32_t* warp_sum) {
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int per = (n + TS_THREADS - 1) / TS_THREADS;
+  const int t0 = min(n, tid * per), t1 = min(n, t0 + per);
+  uint32_t mine = 0u;
+  for (int t = t0; t < t1; ++t) mine += a[t];
+  uint32_t inc = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  __syncthreads();  // warp_sum free
+  if (lane == 31) warp_sum[w] = inc;
+  __syncthreads();
+  uint32_t run = inc - mine, all = 0u;
+#pragma unroll
+  for (int ww = 0; ww < TS_WARPS; ++ww) { run += (ww < w) ? warp_sum[ww] : 0u; all += warp_sum[ww]; }
+  for (int t = t0; t < t1; ++t) {
+    const uint32_t c = a[t];
+    a[t] = run;
+    run += c;
+  }
+  __syncthreads();
+  return all;
+}
+
+// COARSE = false: destinations are tiles, `list` = point_list (Gaussian ids), CTA 0 writes starts and ranges.
+// COARSE = true : destinations are bins (tiles_x = bins per row, n_tiles = bins), `list` = the bin lists' ids and
+//                 `masks` their tile masks; CTA 0 writes the bin starts and the segment table of level 2
+//                 (seg_prefix[bin] = first segment of the bin, seg_bin[segment] = its bin).
+template <bool COARSE>
 __global__ void __launch_bounds__(TS_THREADS, TS_MAX_OCC)
 tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t* __restrict__ order,
                     const uint32_t* __restrict__ chunk_offsets, const unsigned long long* __restrict__ total_dev,
                     int tiles_x, int n_tiles, const uint32_t* __restrict__ counts /*exclusive over chunks*/,
                     const uint32_t* __restrict__ totals, long long cap, uint32_t* __restrict__ start_out,
-                    uint2* __restrict__ ranges, uint32_t* __restrict__ point_list) {
+                    uint2* __restrict__ ranges, uint32_t* __restrict__ list, uint16_t* __restrict__ masks,
+                    uint32_t* __restrict__ seg_prefix, uint32_t* __restrict__ seg_bin, uint32_t max_segs) {
   pdl_launch_dependents();
   pdl_wait();
   extern __shared__ __align__(16) unsigned char ts_smem[];
@@ -248,42 +310,37 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
   uint32_t* pbase = cur + n_tiles;                                          // the same, at the start of the piece
   uint32_t* stage = pbase + n_tiles;                                        // piece: tile << 10 | slot, padded
   uint16_t* whist = reinterpret_cast<uint16_t*>(stage + TS_STAGE_WORDS);    // [TS_WARPS][n_tiles]
+  uint16_t* mstage = whist + (size_t)TS_WARPS * n_tiles + 2;                // COARSE: tile mask of every staged instance
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
 
   // ---- tile starts = exclusive scan of the tile totals (every CTA; CTA 0 publishes starts and ranges) ----
-  for (int t = tid; t < n_tiles; t += TS_THREADS) pbase[t] = totals[t];
+  for (int t = tid; t < n_tiles; t += TS_THREADS) { const uint32_t c = totals[t]; pbase[t] = c; cur[t] = c; }
   __syncthreads();
-  {
-    const int per = (n_tiles + TS_THREADS - 1) / TS_THREADS;
-    const int t0 = min(n_tiles, tid * per), t1 = min(n_tiles, t0 + per);
-    uint32_t mine = 0u;
-    for (int t = t0; t < t1; ++t) mine += pbase[t];
-    uint32_t inc = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += v;
-    }
-    if (lane == 31) sg.warp_sum[w] = inc;
-    __syncthreads();
-    uint32_t run = inc - mine;
-#pragma unroll
-    for (int ww = 0; ww < TS_WARPS; ++ww) run += (ww < w) ? sg.warp_sum[ww] : 0u;
-    for (int t = t0; t < t1; ++t) {
-      const uint32_t c = pbase[t];
-      cur[t] = run;
-      run += c;
-    }
-    __syncthreads();
-  }
+  ts_block_scan(cur, n_tiles, sg.warp_sum);
   if (blockIdx.x == 0) {
     for (int t = tid; t < n_tiles; t += TS_THREADS) {
       const uint32_t st = cur[t], n = pbase[t];
       start_out[t] = st;
-      // clipped to the list capacity: an undersized list (GSR_ECAPACITY) must not send the renderer out of bounds;
-      // (0,0) for empty tiles like the reference's memset (rasterizer_impl.cu:313)
-      const uint32_t lo = (uint32_t)min((long long)st, cap), hi = (uint32_t)min((long long)st + n, cap);
-      ranges[t] = hi > lo ? make_uint2(lo, hi) : make_uint2(0u, 0u);
+      if (!COARSE) {
+        // clipped to the list capacity: an undersized list (GSR_ECAPACITY) must not send the renderer out of
+        // bounds; (0,0) for empty tiles like the reference's memset (rasterizer_impl.cu:313)
+        const uint32_t lo = (uint32_t)min((long long)st, cap), hi = (uint32_t)min((long long)st + n, cap);
+        ranges[t] = hi > lo ? make_uint2(lo, hi) : make_uint2(0u, 0u);
+      }
+    }
+    if (COARSE) {
+      uint32_t* nseg = reinterpret_cast<uint32_t*>(whist);  // [n_tiles] (whist holds 4 words per tile)
+      for (int t = tid; t < n_tiles; t += TS_THREADS) nseg[t] = (pbase[t] + TS2_SEG - 1) / TS2_SEG;
+      __syncthreads();
+      const uint32_t all = ts_block_scan(nseg, n_tiles, sg.warp_sum);
+      for (int t = tid; t < n_tiles; t += TS_THREADS) {
+        const uint32_t first = nseg[t], n = (pbase[t] + TS2_SEG - 1) / TS2_SEG;
+        seg_prefix[t] = first;
+        for (uint32_t q = 0; q < n; ++q)
+          if (first + q < max_segs) seg_bin[first + q] = (uint32_t)t;
+      }
+      if (tid == 0) seg_prefix[n_tiles] = min(all, max_segs);
+      __syncthreads();
     }
   }
   for (int t = tid; t < n_tiles; t += TS_THREADS) cur[t] += counts[(size_t)blockIdx.x * n_tiles + t];
@@ -302,7 +359,7 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
   uint32_t n_all = 0;
   for (unsigned long long kk = k_lo; kk < k_hi;) {
     c = ts_advance_chunk(chunk_offsets, n_chunks, c, kk);
-    if (c != loaded) { n_all = ts_load_group<true>(sg, c, P, rect_sorted, order); loaded = c; }
+    if (c != loaded) { n_all = ts_load_group<true, COARSE>(sg, c, P, rect_sorted, order); loaded = c; }
     const unsigned long long off = chunk_offsets[c];
     const uint32_t piece = (uint32_t)(kk - off);
     const uint32_t n = (uint32_t)min((unsigned long long)n_all, k_hi - off);
@@ -321,10 +378,11 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
         uint32_t local = (uint32_t)(tid * rounds);
         const uint32_t local_end = min(piece_n, local + (uint32_t)rounds);
         if (local < local_end) {
-          TsWalker wk;
+          TsWalker<COARSE> wk;
           wk.seek(sg, piece + local);
           for (;;) {
             stage[local + (local >> 5)] = wk.tile(tiles_x) << 10 | wk.slot;
+            if (COARSE) mstage[local] = (uint16_t)wk.mask();
             if (++local == local_end) break;
             wk.next(sg, piece + local);
           }
@@ -353,7 +411,8 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
           const int i = i0 + j;
           peers[j] = 0u;
           // 13 bits: tile ids < TS_MAX_TILES = 2^12, bit 12 of the invalid marker 0xFFFFFFFF separates idle lanes
-          if (i < rounds && wbase + i * 32 < piece_n) peers[j] = warp_peers<13>(tile[i]);  // warp-uniform branch
+          if (i < rounds && wbase + i * 32 < piece_n)  // warp-uniform branch
+            peers[j] = (COARSE && n_tiles <= 128) ? warp_peers<8>(tile[i]) : warp_peers<13>(tile[i]);
         }
 #pragma unroll
         for (int j = 0; j < TS_MATCH_BATCH; ++j) {
@@ -393,7 +452,10 @@ tile_scatter_kernel(int P, const uint2* __restrict__ rect_sorted, const uint32_t
       for (int i = 0; i < TS_ITEMS; ++i) {
         if (tile[i] != 0xFFFFFFFFu) {
           const long long pos = (long long)pbase[tile[i]] + my_hist[tile[i]] + (sr[i] & 0xffffu);
-          if (pos < cap) point_list[pos] = sg.id[sr[i] >> 16];
+          if (pos < cap) {
+            list[pos] = sg.id[sr[i] >> 16];
+            if (COARSE) masks[pos] = mstage[wbase + i * 32 + lane];
+          }
         }
       }
       __syncthreads();
@@ -418,24 +480,35 @@ rebuild_keys_from_starts_kernel(long long L, int n_tiles, const uint32_t* __rest
   keys[i] = ((uint64_t)(uint32_t)l << 32) | __float_as_uint(rec[3 * (size_t)point_list[i]].z);
 }
 
-static size_t ts_scatter_smem(int n_tiles) {
-  return sizeof(TsGroup) + TS_STAGE_WORDS * 4 + (size_t)n_tiles * TS_TILE_SMEM + 8;
+static size_t ts_scatter_smem(int n_tiles, bool coarse) {
+  return sizeof(TsGroup) + TS_STAGE_WORDS * 4 + (size_t)n_tiles * TS_TILE_SMEM + 8 + (coarse ? TS_PIECE * 2 : 0);
 }
 static size_t ts_count_smem(int n_tiles) { return sizeof(TsGroup) + (size_t)n_tiles * 4; }
 
-cudaError_t launch_tile_count(cudaStream_t st, int P, const GeomViews& g, int tiles_x, int n_tiles) {
+static cudaError_t ts_set_attributes() {
   static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(tile_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)ts_count_smem(TS_MAX_TILES));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(tile_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)ts_scatter_smem(TS_MAX_TILES));
-    if (e != cudaSuccess) return e;
-    attr = true;
-  }
+  if (attr) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(tile_count_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)ts_count_smem(TS_MAX_TILES));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(tile_count_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)ts_count_smem(TS_MAX_TILES));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(tile_scatter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)ts_scatter_smem(TS_MAX_TILES, false));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(tile_scatter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)ts_scatter_smem(TS_MAX_TILES, true));
+  if (e != cudaSuccess) return e;
+  attr = true;
+  return cudaSuccess;
+}
+
+cudaError_t launch_tile_count(cudaStream_t st, int P, const GeomViews& g, int tiles_x, int n_tiles) {
+  cudaError_t e = ts_set_attributes();
+  if (e != cudaSuccess) return e;
   count_launch();
-  launch_k(tile_count_kernel, ts_blocks(n_tiles), TS_THREADS, ts_count_smem(n_tiles), st, 
+  launch_k(tile_count_kernel<false>, ts_blocks(n_tiles), TS_THREADS, ts_count_smem(n_tiles), st,
       P, g.rect_sorted, g.chunk_offsets, g.total, tiles_x, n_tiles, g.ts_counts);
   return cudaGetLastError();
 }
@@ -446,9 +519,31 @@ cudaError_t launch_tile_offsets_scatter(cudaStream_t st, int P, const GeomViews&
   count_launch();
   launch_k(tile_offsets_kernel, (n_tiles + 31) / 32, TS_OFF_WARPS * 32, 0, st, nb, n_tiles, g.ts_counts, g.ts_totals);
   count_launch();
-  launch_k(tile_scatter_kernel, nb, TS_THREADS, ts_scatter_smem(n_tiles), st, 
+  launch_k(tile_scatter_kernel<false>, nb, TS_THREADS, ts_scatter_smem(n_tiles, false), st,
       P, g.rect_sorted, g.order_a, g.chunk_offsets, g.total, tiles_x, n_tiles, g.ts_counts, g.ts_totals, cap,
-      g.ts_start, ranges, point_list);
+      g.ts_start, ranges, point_list, nullptr, nullptr, nullptr, 0u);
+  return cudaGetLastError();
+}
+
+// Level 1 of the two-level binning: the same kernels on bins of TS2_CB x TS2_CB tiles.
+cudaError_t launch_bin_count(cudaStream_t st, int P, const GeomViews& g, int bins_x, int n_bins) {
+  cudaError_t e = ts_set_attributes();
+  if (e != cudaSuccess) return e;
+  count_launch();
+  launch_k(tile_count_kernel<true>, ts_blocks_coarse(n_bins), TS_THREADS, ts_count_smem(n_bins), st,
+      P, g.rect_sorted, g.chunk_offsets_c, g.total_c, bins_x, n_bins, g.ts_counts);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_bin_offsets_scatter(cudaStream_t st, int P, const GeomViews& g, int bins_x, int n_bins,
+                                       long long cap, const RefineViews& rv) {
+  const int nb = ts_blocks_coarse(n_bins);
+  count_launch();
+  launch_k(tile_offsets_kernel, (n_bins + 31) / 32, TS_OFF_WARPS * 32, 0, st, nb, n_bins, g.ts_counts, g.ts_ctotals);
+  count_launch();
+  launch_k(tile_scatter_kernel<true>, nb, TS_THREADS, ts_scatter_smem(n_bins, true), st,
+      P, g.rect_sorted, g.order_a, g.chunk_offsets_c, g.total_c, bins_x, n_bins, g.ts_counts, g.ts_ctotals, cap,
+      g.ts_cstart, nullptr, rv.ids, rv.masks, g.ts_seg_prefix, rv.seg_bin, (uint32_t)rv.max_segs);
   return cudaGetLastError();
 }
 

@@ -530,25 +530,29 @@ np.savez(sys.argv[2], R=o["R"], plist=o["plist"].cpu().numpy()[:o["R"]], keys=o[
 def test_radix_and_sort_free_binning_agree(built, tmp_path):
     import os, subprocess, sys
     outs = {}
-    for mode in ("radix", "scatter"):
+    for mode in ("radix", "single", "scatter"):     # "scatter" (any other value) = the default two-level binning
         env = dict(os.environ, GSR_BINNING=mode)
         f = tmp_path / f"{mode}.npz"
         r = subprocess.run([sys.executable, "-c", _BINNING_CHILD, str(ROOT), str(f)], env=env, capture_output=True,
                            text=True, timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
         outs[mode] = np.load(f)
-    a, b = outs["radix"], outs["scatter"]
-    assert int(a["R"]) == int(b["R"]) > 0
-    for k in ("plist", "keys", "ranges", "n_contrib", "n_touched", "color"):
-        assert np.array_equal(a[k], b[k]), k
+    a = outs["radix"]
+    for other in ("single", "scatter"):
+        b = outs[other]
+        assert int(a["R"]) == int(b["R"]) > 0
+        for k in ("plist", "keys", "ranges", "n_contrib", "n_touched", "color"):
+            assert np.array_equal(a[k], b[k]), (other, k)
 
 
 def test_binning_implementations_agree_in_process_and_are_deterministic(built):
-    """Random scenes / image shapes: the sort-free binning equals the instance radix sort bit for bit, and 10 repeats
-    of it give identical lists (a shared-memory race in the scatter kernel would show up as run-to-run variation)."""
+    """Random scenes / image shapes: the two-level (mode 0) and the single-level (mode 2) sort-free binning equal the
+    instance radix sort (mode 1) bit for bit, and 10 repeats of each give identical lists (a shared-memory race in
+    the scatter kernels would show up as run-to-run variation)."""
     lib = _abi.load()
     cases = [(20_000, "tum_half", 21, False, False), (80_000, "tum", 22, True, True), (150_000, "replica", 23, False, False),
-             (257, "tum_half", 24, False, False), (40_000, "tum", 25, False, True)]
+             (257, "tum_half", 24, False, False), (40_000, "tum", 25, False, True), (300_000, "hd", 26, True, True),
+             (3_000, "hd", 27, False, False)]
     try:
         for P, kind, seed, aniso, layered in cases:
             cam = synth.make_camera(kind, rot=(0.003, 0.004, -0.002), trans=(0.01, 0.02, -0.01))
@@ -556,10 +560,11 @@ def test_binning_implementations_agree_in_process_and_are_deterministic(built):
             bg = torch.tensor([0.1, 0.2, 0.3], device=DEV)
             fa = _fargs(cam, sc, bg, debug=False)
             outs = {}
-            for mode in (1, 0):
+            modes = (1, 0, 2) if lib.gsr_debug_set_binning(2) == 0 and cam.W * cam.H <= 4096 * 256 else (1, 0)
+            for mode in modes:
                 assert lib.gsr_debug_set_binning(mode) == 0
                 reps = []
-                for _ in range(10 if mode == 0 else 1):
+                for _ in range(10 if mode != 1 else 1):
                     R, col, radii, geom, plist, img, dep, opa, nt = ours.rasterize_gaussians(*fa)
                     # (sorted keys are compared in the two-phase tests above: the key hook follows gsr_forward_render)
                     _, n_contrib, ranges = _image_state(img, cam.W, cam.H)
@@ -568,9 +573,11 @@ def test_binning_implementations_agree_in_process_and_are_deterministic(built):
                 for r in reps[1:]:
                     assert r[0] == reps[0][0] and torch.equal(r[1], reps[0][1]) and torch.equal(r[5], reps[0][5])
                 outs[mode] = reps[0]
-            a, b = outs[1], outs[0]
-            assert a[0] == b[0] > 0
-            assert torch.equal(a[1], b[1]) and torch.equal(a[5], b[5])
-            assert (a[3] == b[3]).all() and (a[4] == b[4]).all()
+            a = outs[1]
+            for mode in modes[1:]:
+                b = outs[mode]
+                assert a[0] == b[0] > 0, mode
+                assert torch.equal(a[1], b[1]) and torch.equal(a[5], b[5]), mode
+                assert (a[3] == b[3]).all() and (a[4] == b[4]).all(), mode
     finally:
         lib.gsr_debug_set_binning(0)
