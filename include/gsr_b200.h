@@ -414,10 +414,11 @@ int gsr_debug_image_views(const void* image_ws, int width, int height,
  * binning (bin lists) and the instance radix sort (keys) do; 0 when binning_ws may be NULL (single-level sort-free
  * binning, a test mode). */
 int gsr_binning_needed(int width, int height);
-/* Test hook: 0 = automatic choice of the binning implementation (two-level sort-free binning for images of up to
- * 4096 bins of 4x4 tiles = 65 536 tiles, instance radix sort above), 1 = radix sort at every size, 2 = single-level
- * sort-free binning where the image has <= 4096 tiles. All produce the identical point_list / ranges. A forward
- * and the gsr_debug_sorted_keys call that inspects it must run under the same mode. */
+/* Test hook: 0 = automatic choice of the binning implementation (single-level sort-free binning for lists of fewer
+ * than 2 Mi instances on images of <= 4096 tiles, else two-level sort-free binning for images of up to 4096 bins of
+ * 4x4 tiles = 65 536 tiles, instance radix sort above), 1 = radix sort at every size, 2 = single-level and
+ * 3 = two-level wherever the image admits them. All produce the identical point_list / ranges. A forward and the
+ * gsr_debug_sorted_keys call that inspects it must run under the same mode. */
 int gsr_debug_set_binning(int mode);
 /* Rebuilds the reference's sorted 64-bit keys (tile << 32 | depth bits, rasterizer_impl.cu:102-104) of the
  * LAST gsr_forward_render call that used these workspaces into keys_sorted[num_rendered] (device). */

@@ -530,7 +530,7 @@ np.savez(sys.argv[2], R=o["R"], plist=o["plist"].cpu().numpy()[:o["R"]], keys=o[
 def test_radix_and_sort_free_binning_agree(built, tmp_path):
     import os, subprocess, sys
     outs = {}
-    for mode in ("radix", "single", "scatter"):     # "scatter" (any other value) = the default two-level binning
+    for mode in ("radix", "single", "twolevel", "scatter"):     # "scatter" (any other value) = the automatic choice
         env = dict(os.environ, GSR_BINNING=mode)
         f = tmp_path / f"{mode}.npz"
         r = subprocess.run([sys.executable, "-c", _BINNING_CHILD, str(ROOT), str(f)], env=env, capture_output=True,
@@ -538,7 +538,7 @@ def test_radix_and_sort_free_binning_agree(built, tmp_path):
         assert r.returncode == 0, r.stderr[-2000:]
         outs[mode] = np.load(f)
     a = outs["radix"]
-    for other in ("single", "scatter"):
+    for other in ("single", "twolevel", "scatter"):
         b = outs[other]
         assert int(a["R"]) == int(b["R"]) > 0
         for k in ("plist", "keys", "ranges", "n_contrib", "n_touched", "color"):
@@ -546,8 +546,8 @@ def test_radix_and_sort_free_binning_agree(built, tmp_path):
 
 
 def test_binning_implementations_agree_in_process_and_are_deterministic(built):
-    """Random scenes / image shapes: the two-level (mode 0) and the single-level (mode 2) sort-free binning equal the
-    instance radix sort (mode 1) bit for bit, and 10 repeats of each give identical lists (a shared-memory race in
+    """Random scenes / image shapes: the two-level (mode 3), the single-level (mode 2) sort-free binning and the
+    automatic choice (mode 0) equal the instance radix sort (mode 1) bit for bit, and 10 repeats of each give identical lists (a shared-memory race in
     the scatter kernels would show up as run-to-run variation)."""
     lib = _abi.load()
     cases = [(20_000, "tum_half", 21, False, False), (80_000, "tum", 22, True, True), (150_000, "replica", 23, False, False),
@@ -560,7 +560,7 @@ def test_binning_implementations_agree_in_process_and_are_deterministic(built):
             bg = torch.tensor([0.1, 0.2, 0.3], device=DEV)
             fa = _fargs(cam, sc, bg, debug=False)
             outs = {}
-            modes = (1, 0, 2) if lib.gsr_debug_set_binning(2) == 0 and cam.W * cam.H <= 4096 * 256 else (1, 0)
+            modes = (1, 3, 0, 2) if cam.W * cam.H <= 4096 * 256 else (1, 3, 0)
             for mode in modes:
                 assert lib.gsr_debug_set_binning(mode) == 0
                 reps = []
