@@ -115,14 +115,14 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const float4 q1 = sg.rec[3 * (valid ? jj : c0) + 1];
         const bool hit = valid && cull_hit(cull_gauss(q0, q1), rx0, rx1, ry0, ry1);
         const uint32_t m = __ballot_sync(0xffffffffu, hit);
-        if (hit) my_queue[qn + __popc(m & lt_mask)] = (uint8_t)(jj - c0);
+        if (hit) my_queue[qn + __popc(m & lt_mask)] = (uint8_t)jj;   // batch index < RENDER_BATCH = 256
         qn += __popc(m);
       }
       __syncwarp();
       // ---- blend the queued Gaussians in list order (prefetching Gaussian i+1's record one iteration ahead was
       //      measured SLOWER here: 0.094 vs 0.081 ms; it pays in the backward kernel) ----
       for (int i = 0; i < qn; ++i) {
-        const int j = c0 + (int)my_queue[i];
+        const int j = (int)my_queue[i];
         const float4 a = sg.rec[3 * j];
         const float4 co = sg.rec[3 * j + 1];
         const float dx = fsub(a.x, pixx), dy = fsub(a.y, pixy);
@@ -144,8 +144,11 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         // once no pixel of the warp has T > 0.5 the vote can never fire again and is skipped for the rest of the tile.
         if (touch_live) {
           const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
-          if (tv != 0 && lane == 0) atomicAdd(&n_touched[sg.id[j]], __popc(tv));
-          touch_live = __any_sync(0xffffffffu, !done && T > 0.5f);
+          if (tv != 0) {   // (a pixel that fired has T > 0.5: still live, no second vote needed)
+            if (lane == 0) atomicAdd(&n_touched[sg.id[j]], __popc(tv));
+          } else {
+            touch_live = __any_sync(0xffffffffu, !done && T > 0.5f);
+          }
         }
         if (__all_sync(0xffffffffu, done)) break;
       }
