@@ -33,8 +33,12 @@ constexpr int RF_CHUNK = GSR_RF_CHUNK;   // staged Gaussians queued at a time (e
 static_assert(RF_CHUNK % 32 == 0 && RENDER_BATCH % RF_CHUNK == 0 && RF_CHUNK <= 256, "RF_CHUNK");
 
 #ifndef GSR_RF_MIN_CTAS
-#define GSR_RF_MIN_CTAS 1
+#define GSR_RF_MIN_CTAS 4
 #endif
+#ifndef GSR_RF_UNROLL
+#define GSR_RF_UNROLL 4
+#endif
+constexpr int RF_UNROLL = GSR_RF_UNROLL;   // queued Gaussians blended per loop round
 __global__ void __launch_bounds__(RENDER_THREADS, GSR_RF_MIN_CTAS)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                   int tiles_x, const float4* __restrict__ rec, const float* __restrict__ bg,
@@ -121,17 +125,22 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       __syncwarp();
       // ---- blend the queued Gaussians in list order (prefetching Gaussian i+1's record one iteration ahead was
       //      measured SLOWER here: 0.094 vs 0.081 ms; it pays in the backward kernel) ----
-      for (int i = 0; i < qn; ++i) {
-        const int j = (int)my_queue[i];
+      // One queued Gaussian: alpha for this lane's pixel (independent of the pixel's running state) ...
+      auto pair_alpha = [&](int j, float& alpha, bool& ok) {
         const float4 a = sg.rec[3 * j];
         const float4 co = sg.rec[3 * j + 1];
         const float dx = fsub(a.x, pixx), dy = fsub(a.y, pixy);
         const float power = gauss_power(dx, dy, co.x, co.y, co.z);
-        const float alpha = fminf(fmul(co.w, expf(power)), 0.99f);
+        alpha = fminf(fmul(co.w, expf(power)), 0.99f);
+        ok = !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+      };
+      // ... and its blend into the running state, in list order (forward.cu:352-371)
+      auto blend = [&](int j, float alpha, bool ok) {
         const float test_T = fmul(T, fsub(1.0f, alpha));
-        bool act = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+        bool act = !done && ok;
         if (act && test_T < 0.0001f) { done = true; act = false; }
         if (act) {
+          const float4 a = sg.rec[3 * j];
           const float4 c = sg.rec[3 * j + 2];
           Cr = ffma(T, fmul(alpha, c.x), Cr);
           Cg = ffma(T, fmul(alpha, c.y), Cg);
@@ -150,7 +159,29 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
             touch_live = __any_sync(0xffffffffu, !done && T > 0.5f);
           }
         }
+      };
+      // RF_UNROLL queued Gaussians per round: their alphas are independent (several exp chains in flight), only the
+      // short T / colour updates are ordered; the all-done vote and the loop bookkeeping are paid once per round
+      int i = 0;
+      for (; i + RF_UNROLL <= qn; i += RF_UNROLL) {
+        int j[RF_UNROLL];
+        float al[RF_UNROLL];
+        bool ok[RF_UNROLL];
+#pragma unroll
+        for (int u = 0; u < RF_UNROLL; ++u) { j[u] = (int)my_queue[i + u]; pair_alpha(j[u], al[u], ok[u]); }
+#pragma unroll
+        for (int u = 0; u < RF_UNROLL; ++u) blend(j[u], al[u], ok[u]);
         if (__all_sync(0xffffffffu, done)) break;
+      }
+      if (i + RF_UNROLL > qn) {   // (not taken after the break above: there i + RF_UNROLL <= qn)
+        for (; i < qn; ++i) {
+          if (__all_sync(0xffffffffu, done)) break;
+          const int j0 = (int)my_queue[i];
+          float al0;
+          bool ok0;
+          pair_alpha(j0, al0, ok0);
+          blend(j0, al0, ok0);
+        }
       }
       __syncwarp();   // the queue is rewritten by the next chunk
     }
