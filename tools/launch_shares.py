@@ -13,7 +13,7 @@ def main(path):
         agg.setdefault(r[ki], []).append(v)
     tot = sum(sum(v) for v in agg.values())
     print("# ncu --metrics gpu__time_duration.sum --clock-control none, command: python bench.py --steps 2 --warmup 1 "
-          "--no-e2e --no-cpu-baseline")
+          "--no-e2e --no-cpu-baseline --no-window-c4")
     print("# (cold-cache, serialised launches: compare SHARES with bench.py's live CUDA-event stage times, not absolutes)")
     for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
         print(f"{k[:70]:70s} n={len(v):3d} mean_us={sum(v)/len(v):8.1f} share={100*sum(v)/tot:5.1f}%")
