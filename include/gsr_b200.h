@@ -374,14 +374,16 @@ int gsr_knn_dist2(void* stream, int P, const float* points, float* mean_dist2,
 
 /* ---- measurement hook ------------------------------------------------------
  * Per-stage device timing with CUDA events recorded on the CALLER's stream around each kernel group
- * (bench.py's roofline leg). gsr_profile_enable(1) starts recording; gsr_profile_collect waits for the
- * recorded events, writes ms_sum[GSR_NUM_STAGES] (total device milliseconds per stage since the last
- * collect) and launches[GSR_NUM_STAGES] (how many times each stage ran) and clears the record. */
+ * (bench.py's roofline leg). gsr_profile_enable(1) starts recording every stage, gsr_profile_enable(1 | mask << 8)
+ * only the stages whose bit (1 << GSR_STAGE_x) is set in mask -- an event record between two kernels takes away their
+ * programmatic-dependent-launch overlap, so timing all nine stages costs the step ~3 %; gsr_profile_enable(0) stops.
+ * gsr_profile_collect waits for the recorded events, writes ms_sum[GSR_NUM_STAGES] (total device milliseconds per
+ * stage since the last collect) and launches[GSR_NUM_STAGES] (how many times each stage ran) and clears the record. */
 #define GSR_STAGE_PREPROCESS 0      /* preprocess_fwd_kernel (+ digit offsets)            */
 #define GSR_STAGE_DEPTH_SORT 1      /* 4 onesweep passes over P (depth bits, id)           */
 #define GSR_STAGE_SCAN 2            /* chunk sums + scan -> num_rendered                   */
-#define GSR_STAGE_EMIT 3            /* emit_instances_kernel                               */
-#define GSR_STAGE_TILE_SORT 4       /* tile-digit histogram + 1-2 onesweep passes over R   */
+#define GSR_STAGE_EMIT 3            /* binning, first half: bin lists (two-level) / tile counts / instance emission */
+#define GSR_STAGE_TILE_SORT 4       /* binning, second half: refine / offsets + scatter / onesweep passes over R   */
 #define GSR_STAGE_RANGES 5          /* tile_ranges_kernel                                  */
 #define GSR_STAGE_RENDER_FWD 6      /* render_fwd_kernel                                   */
 #define GSR_STAGE_RENDER_BWD 7      /* render_bwd_kernel                                   */

@@ -91,6 +91,7 @@ int debug_sync(cudaStream_t st, int debug) {
 struct StageSpan { int stage; cudaEvent_t a, b; };
 std::mutex g_prof_mu;
 bool g_prof_on = false;
+unsigned g_prof_mask = 0;   // stages to time (bit = GSR_STAGE_*); 0 = all
 std::vector<StageSpan> g_spans;
 std::vector<cudaEvent_t> g_free_events;
 cudaEvent_t prof_event() {
@@ -103,7 +104,7 @@ struct StageTimer {
   cudaStream_t st; int idx = -1;
   StageTimer(cudaStream_t s, int stage) : st(s) {
     std::lock_guard<std::mutex> lk(g_prof_mu);
-    if (!g_prof_on) return;
+    if (!g_prof_on || (g_prof_mask && !(g_prof_mask >> stage & 1u))) return;
     StageSpan sp{stage, prof_event(), prof_event()};
     cudaEventRecord(sp.a, st);
     g_spans.push_back(sp);
@@ -773,7 +774,8 @@ int gsr_sort_pairs_u64(void* stream, int64_t n, const uint64_t* keys_in, const u
 
 int gsr_profile_enable(int on) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
-  g_prof_on = on != 0;
+  g_prof_on = (on & 1) != 0;
+  g_prof_mask = (unsigned)on >> 8;   // optional stage selection: on = 1 | (1 << (8 + GSR_STAGE_x)) | ...
   return GSR_OK;
 }
 
