@@ -265,6 +265,56 @@ def test_huge_and_near_degenerate_gaussians_against_reference(built):
 
 
 @needs_ref
+@pytest.mark.parametrize("case", ["planes", "one_depth", "far_and_near", "tiny"])
+def test_depth_order_with_equal_and_crowded_depths_against_reference(built, case):
+    """The depth order of the Gaussians must be the reference's -- depth bits, ties by Gaussian id (its stable sort of
+    keys emitted in id order) -- also in degenerate scenes: tens of thousands of EQUAL depths (five planes, or every
+    Gaussian at one depth), depths of 2e4 .. 3e6 m and just above the 0.2 m near plane with ties there too, and a
+    map of 37 Gaussians. Identity camera, so view depth = z exactly."""
+    cam = synth.make_camera("tum_half")
+    P = {"planes": 120_000, "one_depth": 60_000, "far_and_near": 40_000, "tiny": 37}[case]
+    sc = synth.make_scene(P, cam, seed=41, device=DEV)
+    g = torch.Generator().manual_seed(42)
+    m = sc["means3D"].clone()
+    z = m[:, 2].clone()
+    front = z > 0.2
+    if case == "planes":          # five planes of ~20 k Gaussians each + 30 short runs + the rest random
+        sel = torch.rand(P, generator=g).to(DEV)
+        planes = torch.tensor([0.75, 1.5, 1.5000001, 2.25, 4.0], device=DEV)
+        pick = (sel * 6).long().clamp_max(5)
+        znew = torch.where(pick < 5, planes[pick.clamp_max(4)], z)
+        runs = (sel * 4000).long() % 130
+        znew = torch.where((pick == 5) & (runs < 30), 3.0 + 0.001 * runs.float(), znew)
+    elif case == "one_depth":
+        znew = torch.full_like(z, 2.0)
+    elif case == "far_and_near":  # beyond both ends of the binned range, with ties there too
+        sel = torch.rand(P, generator=g).to(DEV)
+        znew = torch.where(sel < 0.3, 20000.0 + 5000.0 * (sel * 1000).floor() / 300.0, z)
+        znew = torch.where(sel > 0.9, torch.full_like(z, 0.2000001), znew)
+        znew = torch.where((sel > 0.8) & (sel <= 0.9), torch.full_like(z, 3.0e6), znew)
+    else:
+        znew = z
+    scale = torch.where(front, znew / z.clamp_min(1e-6), torch.ones_like(z))
+    m[:, 0] = torch.where(front, m[:, 0] * scale, m[:, 0])      # keep the pixel, move along the ray
+    m[:, 1] = torch.where(front, m[:, 1] * scale, m[:, 1])
+    m[:, 2] = torch.where(front, znew, z)
+    sc["means3D"] = m.contiguous()
+    sc["scales"] = (sc["scales"] * scale[:, None].clamp(1e-3, 1e3)).contiguous()
+    bg = torch.tensor([0.1, 0.2, 0.3], device=DEV)
+    dcol = (torch.randn(3, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
+    ddep = (torch.randn(1, cam.H, cam.W, generator=g) / (cam.H * cam.W)).to(DEV)
+    o = _compare_with_reference(cam, sc, bg, dcol, ddep)
+    if case != "tiny":
+        keys = o["keys"].cpu().numpy().astype(np.int64)
+        depth_bits = keys & 0xFFFFFFFF
+        tile = keys >> 32
+        same = (tile[1:] == tile[:-1]) & (depth_bits[1:] == depth_bits[:-1])
+        assert same.sum() > 1000                                   # the scene really has ties inside tiles ...
+        pl = o["plist"].view(torch.int32).cpu().numpy()[:len(keys)].astype(np.int64)
+        assert (pl[1:][same] > pl[:-1][same]).all()                # ... and they are in id order
+
+
+@needs_ref
 def test_sh_and_cov3d_precomp_paths_against_reference(built):
     """shs (degree 3) instead of precomputed colours, and cov3D_precomp instead of scale/rotation."""
     P = 20_000
