@@ -31,7 +31,7 @@ GSR_DEVINL unsigned trace_smid() { unsigned s; asm volatile("mov.u32 %0, %smid;"
 #endif
 
 #ifndef GSR_RB_UNROLL
-#define GSR_RB_UNROLL 4
+#define GSR_RB_UNROLL 8
 #endif
 constexpr int RB_UNROLL = GSR_RB_UNROLL;   // unroll of the phase-2 pixel loop (register budget: 3 CTAs per SM)
 constexpr int RB_GROUP = 16;              // queued Gaussians per transposed-reduction round
@@ -93,13 +93,19 @@ tile_order_kernel(int n_tiles, const uint32_t* __restrict__ tile_work, uint32_t*
 }
 
 // Dynamic shared memory of the backward renderer (65 KB: above the 48 KB static limit; 3 CTAs per SM fit).
+#ifndef GSR_RB_BATCH
+#define GSR_RB_BATCH 256
+#endif
+constexpr int RB_BATCH = GSR_RB_BATCH;    // list entries staged per round (<= one per thread; queue indices are u8)
+static_assert(RB_BATCH <= RENDER_THREADS && RB_BATCH <= 256 && RB_BATCH % 32 == 0, "RB_BATCH");
+using RbStage = RenderStageT<RB_BATCH>;
 struct RbShared {
-  RenderStage stage[2];
+  RbStage stage[2];
   float4 dp[RENDER_WARPS][32];                 // dL/d(r, g, b, depth) of every warp's pixels
   float S[RENDER_WARPS][RB_GROUP * RB_PITCH];  // [Gaussian of the round][pixel]
   float A[RENDER_WARPS][RB_GROUP * RB_PITCH];
   uint32_t max_contrib[RENDER_WARPS];
-  uint8_t queue[RENDER_WARPS][RENDER_BATCH];
+  uint8_t queue[RENDER_WARPS][RB_BATCH];
 };
 
 #ifndef GSR_RB_MIN_CTAS
@@ -121,7 +127,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 #endif
   extern __shared__ __align__(16) unsigned char rb_smem_raw[];
   RbShared& sh = *reinterpret_cast<RbShared*>(rb_smem_raw);
-  RenderStage* const stage = sh.stage;
+  RbStage* const stage = sh.stage;
   uint32_t* const s_max = sh.max_contrib;
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -166,7 +172,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 #pragma unroll
   for (int i = 0; i < RENDER_WARPS; ++i) tile_last = max(tile_last, s_max[i]);
   const int total = (int)tile_last;  // list positions [0, total) are replayed, from the back
-  const int n_batches = (total + RENDER_BATCH - 1) / RENDER_BATCH;
+  const int n_batches = (total + RB_BATCH - 1) / RB_BATCH;
 
   float T = T_final;
   float acc_w = 0.f, last_w = 0.f, last_alpha = 0.f;
@@ -175,39 +181,39 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int g2 = lane & (RB_GROUP - 1), h2 = lane >> 4;
   const float py2 = (float)(wy0 + 2 * h2);
 
-  // batch k covers list positions pos = total-1 - (k*RENDER_BATCH + t), t = 0..255 (descending)
+  // batch k covers list positions pos = total-1 - (k*RB_BATCH + t), t = 0..255 (descending)
   uint32_t id_next = 0;
   if (n_batches > 0) {
-    if (tid < total) stage_record(stage[0], tid, point_list[range.x + (total - 1 - tid)], rec);
+    if (tid < RB_BATCH && tid < total) stage_record(stage[0], tid, point_list[range.x + (total - 1 - tid)], rec);
     cp_async_commit();
-    if (RENDER_BATCH + tid < total) id_next = point_list[range.x + (total - 1 - RENDER_BATCH - tid)];
+    if (tid < RB_BATCH && RB_BATCH + tid < total) id_next = point_list[range.x + (total - 1 - RB_BATCH - tid)];
   }
 
   for (int b = 0; b < n_batches; ++b) {
     const int cur = b & 1;
     if (b + 1 < n_batches) {
-      if ((b + 1) * RENDER_BATCH + tid < total) stage_record(stage[cur ^ 1], tid, id_next, rec);
+      if (tid < RB_BATCH && (b + 1) * RB_BATCH + tid < total) stage_record(stage[cur ^ 1], tid, id_next, rec);
       cp_async_commit();
-      const int e2 = (b + 2) * RENDER_BATCH + tid;
-      if (e2 < total) id_next = point_list[range.x + (total - 1 - e2)];
+      const int e2 = (b + 2) * RB_BATCH + tid;
+      if (tid < RB_BATCH && e2 < total) id_next = point_list[range.x + (total - 1 - e2)];
       cp_async_wait<1>();
     } else {
       cp_async_wait<0>();
     }
     __syncthreads();
 
-    const RenderStage& sg = stage[cur];
-    const int count = min(RENDER_BATCH, total - b * RENDER_BATCH);
+    const RbStage& sg = stage[cur];
+    const int count = min(RB_BATCH, total - b * RB_BATCH);
     // ---- queue the batch's Gaussians that can reach this warp's rectangle and lie in front of its last
     //      contributor (the walk starts at the TILE's largest n_contrib) ----
     int qn = 0;
-    if ((uint32_t)(total - b * RENDER_BATCH - count) < wm) {   // else: the whole batch lies behind this warp's pixels
+    if ((uint32_t)(total - b * RB_BATCH - count) < wm) {   // else: the whole batch lies behind this warp's pixels
       for (int g0 = 0; g0 < count; g0 += 32) {
         const int jj = g0 + lane;
         const bool valid = jj < count;
         const float4 q0 = sg.rec[3 * (valid ? jj : 0)];
         const float4 q1 = sg.rec[3 * (valid ? jj : 0) + 1];
-        const uint32_t posj = (uint32_t)(total - 1 - (b * RENDER_BATCH + jj));
+        const uint32_t posj = (uint32_t)(total - 1 - (b * RB_BATCH + jj));
         const bool hit = valid && posj < wm && cull_hit(cull_gauss(q0, q1), rx0, rx1, ry0, ry1);
         const uint32_t m = __ballot_sync(0xffffffffu, hit);
         if (hit) my_queue[qn + __popc(m & lt_mask)] = (uint8_t)jj;
@@ -223,7 +229,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       int j = (int)my_queue[i0];
       float4 a = sg.rec[3 * j], co = sg.rec[3 * j + 1], c = sg.rec[3 * j + 2];
       for (int k = 0; k < gn; ++k) {
-        const uint32_t pos = (uint32_t)(total - 1 - (b * RENDER_BATCH + j));  // 0-based list position
+        const uint32_t pos = (uint32_t)(total - 1 - (b * RB_BATCH + j));  // 0-based list position
         const float4 a_k = a, co_k = co, c_k = c;
         if (k + 1 < gn) {
           j = (int)my_queue[i0 + k + 1];

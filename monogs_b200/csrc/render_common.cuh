@@ -36,11 +36,13 @@ constexpr int RENDER_BATCH = GSR_RENDER_BATCH;  // list entries staged per round
 static_assert(RENDER_BATCH == RENDER_THREADS, "one staged record per thread");
 constexpr int WARP_RECT_W = 8, WARP_RECT_H = 4;
 
-// One staged batch: the 48-byte records (3 x float4, see GeomViews::rec) + the Gaussian ids.
-struct RenderStage {
-  float4 rec[3 * RENDER_BATCH];
-  uint32_t id[RENDER_BATCH];
+// One staged batch of B list entries: the 48-byte records (3 x float4, see GeomViews::rec) + the Gaussian ids.
+template <int B>
+struct RenderStageT {
+  float4 rec[3 * B];
+  uint32_t id[B];
 };
+using RenderStage = RenderStageT<RENDER_BATCH>;
 
 GSR_DEVINL void cp_async16(void* smem_dst, const void* gmem_src) {
   const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
@@ -51,7 +53,8 @@ template <int N>
 GSR_DEVINL void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // Gather record `id` into slot t of a stage: three 16-byte LDGSTS from ONE 48-byte location (two 32-byte sectors).
-GSR_DEVINL void stage_record(RenderStage& st, int t, uint32_t id, const float4* __restrict__ rec) {
+template <int B>
+GSR_DEVINL void stage_record(RenderStageT<B>& st, int t, uint32_t id, const float4* __restrict__ rec) {
   st.id[t] = id;
   const float4* src = rec + 3 * (size_t)id;
   cp_async16(&st.rec[3 * t + 0], src + 0);
