@@ -161,7 +161,9 @@ static int enqueue_plan(cudaStream_t st, int P, int sh_degree, int sh_coeffs, in
                         const float* scales, float scale_modifier, const float* rotations,
                         const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
                         const float* campos, float tan_fovx, float tan_fovy, int prefiltered, int* radii,
-                        char* geom_ws, const GeomViews& g, int debug) {
+                        char* geom_ws, const GeomViews& g, int debug, const ImageViews* im = nullptr) {
+  // im (the single-call forwards): the forward renderer's tile order is sorted by an extra CTA of the chunk scan --
+  // one launch less than a separate sort kernel in front of the renderer
   GSR_TRY(check(cudaMemsetAsync(geom_ws + g.zero_begin, 0, g.zero_end - g.zero_begin, st)));
   {
     StageTimer tm(st, GSR_STAGE_PREPROCESS);
@@ -180,7 +182,8 @@ static int enqueue_plan(cudaStream_t st, int P, int sh_degree, int sh_coeffs, in
   GSR_TRY(debug_sync(st, debug));
   {
     StageTimer tm(st, GSR_STAGE_SCAN);
-    GSR_TRY(check(launch_chunk_scan(st, P, g.order_a, g)));
+    GSR_TRY(check(launch_chunk_scan(st, P, g.order_a, g, (int)num_tiles(width, height), im ? im->tile_work : nullptr,
+                                    im ? im->tile_order_fwd : nullptr)));
   }
   return GSR_OK;
 }
@@ -221,7 +224,7 @@ static bool binning_ws_needed(int width, int height, long long cap = -1) {
 static int enqueue_render(cudaStream_t st, int P, int width, int height, const float* background,
                           const GeomViews& g, const ImageViews& im, char* binning_ws, uint32_t* point_list,
                           long long cap, const unsigned long long* n_dev, float* out_color, float* out_depth,
-                          float* out_opacity, int* n_touched, int debug) {
+                          float* out_opacity, int* n_touched, int debug, bool tile_order_ready = false) {
   const int tiles_x = (width + TILE_X - 1) / TILE_X;
   const size_t n_tiles = num_tiles(width, height);
   const int impl = binning_impl(width, height, cap);
@@ -280,7 +283,7 @@ static int enqueue_render(cudaStream_t st, int P, int width, int height, const f
   {
     StageTimer tm(st, GSR_STAGE_RENDER_FWD);
     GSR_TRY(check(launch_render_fwd(st, width, height, im, point_list, g, background, out_color, out_depth,
-                                    out_opacity, n_touched)));
+                                    out_opacity, n_touched, tile_order_ready)));
   }
   return debug_sync(st, debug);
 }
@@ -364,11 +367,11 @@ int gsr_forward_enqueue(void* stream, int P, int sh_degree, int sh_coeffs, int w
   carve_image((char*)image_ws, width, height, &im);
   GSR_TRY(enqueue_plan(st, P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
                        scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy,
-                       prefiltered, radii, (char*)geom_ws, g, 0));
+                       prefiltered, radii, (char*)geom_ws, g, 0, &im));
   if (total_out)
     GSR_TRY(check(cudaMemcpyAsync(total_out, g.total, sizeof(unsigned long long), cudaMemcpyDefault, st)));
   return enqueue_render(st, P, width, height, background, g, im, (char*)binning_ws, point_list, capacity, g.total,
-                        out_color, out_depth, out_opacity, n_touched, 0);
+                        out_color, out_depth, out_opacity, n_touched, 0, true);
 }
 
 int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs, int width, int height, const float* background,
@@ -393,13 +396,13 @@ int gsr_forward(void* stream, int P, int sh_degree, int sh_coeffs, int width, in
   carve_image((char*)image_ws, width, height, &im);
   GSR_TRY(enqueue_plan(st, P, sh_degree, sh_coeffs, width, height, means3D, shs, colors_precomp, opacities, scales,
                        scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy,
-                       prefiltered, radii, (char*)geom_ws, g, debug));
+                       prefiltered, radii, (char*)geom_ws, g, debug, &im));
   ReadSlotGuard rs;
   GSR_TRY(acquire_read_slot(&rs.s));
   GSR_TRY(enqueue_total_read(st, g, rs.s));
   // everything downstream is enqueued BEFORE the host waits for num_rendered: the GPU never idles on the read
   GSR_TRY(enqueue_render(st, P, width, height, background, g, im, (char*)binning_ws, point_list, capacity, g.total,
-                         out_color, out_depth, out_opacity, n_touched, debug));
+                         out_color, out_depth, out_opacity, n_touched, debug, true));
   GSR_TRY(finish_total_read(rs.s, num_rendered));
   return *num_rendered > capacity ? GSR_ECAPACITY : GSR_OK;
 }

@@ -349,6 +349,46 @@ GSR_DEVINL uint32_t warp_peers(uint32_t v) {
 // once (pdl_launch_dependents) and waits for its predecessor's results (pdl_wait) before it touches global memory,
 // so launch latency, CTA scheduling and the shared-memory prologue overlap the predecessor's tail.  Every kernel
 // must execute pdl_wait on every path: completion of a grid then implies completion of all earlier grids.
+// Tiles by descending replay length (counting sort on tile_work / 4) by ONE CTA of TILE_ORDER_THREADS threads: the
+// body of tile_order_kernel (render_bwd.cu), also run by an extra CTA of chunk_scan_kernel for the forward renderer.
+constexpr int TILE_ORDER_THREADS = 1024;
+GSR_DEVINL void tile_order_body(int n_tiles, const uint32_t* __restrict__ tile_work, uint32_t* __restrict__ tile_order) {
+  __shared__ uint32_t s_bin[TILE_ORDER_THREADS];
+  __shared__ uint32_t s_warp[TILE_ORDER_THREADS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  s_bin[tid] = 0;
+  __syncthreads();
+  for (int t = tid; t < n_tiles; t += TILE_ORDER_THREADS)
+    atomicAdd(&s_bin[TILE_ORDER_THREADS - 1 - min(tile_work[t] >> 2, (uint32_t)TILE_ORDER_THREADS - 1)], 1u);
+  __syncthreads();
+  // exclusive scan of the 1024 bins (bin 0 = heaviest)
+  const uint32_t c = s_bin[tid];
+  uint32_t inc = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = s_warp[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += v;
+    }
+    s_warp[lane] = w;
+  }
+  __syncthreads();
+  s_bin[tid] = inc - c + (warp ? s_warp[warp - 1] : 0u);
+  __syncthreads();
+  for (int t = tid; t < n_tiles; t += TILE_ORDER_THREADS) {
+    const uint32_t pos = atomicAdd(&s_bin[TILE_ORDER_THREADS - 1 - min(tile_work[t] >> 2, (uint32_t)TILE_ORDER_THREADS - 1)], 1u);
+    tile_order[pos] = (uint32_t)t;
+  }
+}
+
 // Tile rectangle (x0 | x1 << 16, y0 | y1 << 16, exclusive ends) -> rectangle of TS2_CB x TS2_CB-tile bins.
 GSR_DEVINL uint2 ts_coarse_rect(uint2 r) {
   const uint32_t x0 = r.x & 0xffffu, x1 = r.x >> 16, y0 = r.y & 0xffffu, y1 = r.y >> 16;

@@ -11,7 +11,9 @@ cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const fl
                                   const float* viewmatrix, const float* projmatrix, const float* campos, int W,
                                   int H, float tan_fovx, float tan_fovy, int prefiltered, int* radii,
                                   const GeomViews& g);
-cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g);
+// tile_order_fwd != NULL: an extra CTA also sorts the tiles by the previous forward's tile_work (the forward renderer's map)
+cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g, int n_tiles,
+                              const uint32_t* tile_work, uint32_t* tile_order_fwd);
 cudaError_t launch_mark_visible(cudaStream_t st, int P, const float* means3D, const float* viewmatrix,
                                 uint8_t* present);
 cudaError_t launch_camera_setup(cudaStream_t st, const float* R, int rs, int cs, const float* T, int ts,
@@ -59,7 +61,7 @@ cudaError_t launch_digit_offsets(cudaStream_t st, uint32_t* hist, int n_passes);
 // render_fwd.cu
 cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, float* out_color, float* out_depth,
-                              float* out_opacity, int* n_touched);
+                              float* out_opacity, int* n_touched, bool tile_order_ready = false);
 
 // render_bwd.cu
 // tile_order[0..n_tiles) = tiles by descending tile_work (any content of tile_work gives a valid permutation)

@@ -351,6 +351,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
 }
 
 constexpr int SCAN_THREADS = 1024;
+static_assert(SCAN_THREADS == TILE_ORDER_THREADS, "chunk_scan_kernel's extra CTA runs tile_order_body");
 
 GSR_DEVINL uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp, uint32_t& block_total) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -383,9 +384,14 @@ GSR_DEVINL uint32_t block_exclusive_scan_1024(uint32_t v, uint32_t* s_warp, uint
 // One block; 4 consecutive chunks per thread and round (one 16-byte load), so 1M Gaussians are a single round.
 __global__ void __launch_bounds__(SCAN_THREADS)
 chunk_scan_kernel(int n_chunks, uint32_t* __restrict__ chunk_sums, unsigned long long* __restrict__ total,
-                  uint32_t* __restrict__ chunk_sums_c, unsigned long long* __restrict__ total_c) {
+                  uint32_t* __restrict__ chunk_sums_c, unsigned long long* __restrict__ total_c, int n_tiles,
+                  const uint32_t* __restrict__ tile_work, uint32_t* __restrict__ tile_order) {
   pdl_launch_dependents();
   pdl_wait();
+  if (blockIdx.x == 2) {   // optional CTA 2: the forward renderer's tile order (independent work, saves a launch)
+    tile_order_body(n_tiles, tile_work, tile_order);
+    return;
+  }
   if (blockIdx.x == 1) { chunk_sums = chunk_sums_c; total = total_c; }  // CTA 1: the bin-level counts
   __shared__ uint32_t s_warp[33];
   unsigned long long carry = 0;
@@ -482,11 +488,13 @@ cudaError_t launch_preprocess_fwd(cudaStream_t st, int P, int D, int M, const fl
 }
 
 // offsets of the depth-ordered chunks + total; `order` = Gaussian ids in depth order
-cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g) {
+cudaError_t launch_chunk_scan(cudaStream_t st, int P, const uint32_t* order, const GeomViews& g, int n_tiles,
+                              const uint32_t* tile_work, uint32_t* tile_order_fwd) {
   const int nc = num_pre_blocks(P);
   cudaError_t e = launch_gather_rects(st, P, order, g);
   if (e != cudaSuccess) return e;
-  count_launch(); launch_k(chunk_scan_kernel, 2, SCAN_THREADS, 0, st, nc, g.chunk_offsets, g.total, g.chunk_offsets_c, g.total_c);
+  count_launch(); launch_k(chunk_scan_kernel, tile_order_fwd ? 3 : 2, SCAN_THREADS, 0, st, nc, g.chunk_offsets, g.total, g.chunk_offsets_c,
+           g.total_c, n_tiles, tile_work, tile_order_fwd);
   return cudaGetLastError();
 }
 

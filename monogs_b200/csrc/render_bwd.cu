@@ -41,7 +41,7 @@ constexpr int RB_PITCH = 33;              // floats per Gaussian row of the S / 
 // linear order, so with this map the long tiles run first and the kernel's tail consists of the shortest ones
 // (measured on the headline scene: the backward renderer's last CTA started at 54 % of the kernel's span and ran
 // for up to half of it). Order inside a bin is arbitrary -- it only affects scheduling.
-constexpr int TO_THREADS = 1024;
+constexpr int TO_THREADS = TILE_ORDER_THREADS;
 // zero_ptr / zero_n16: optional buffer (the backward's partial-gradient scratch) cleared by the OTHER CTAs of the
 // launch while CTA 0 sorts -- one launch instead of a memset node (which also breaks the PDL chain) + a 1-CTA kernel.
 __global__ void __launch_bounds__(TO_THREADS)
@@ -56,40 +56,7 @@ tile_order_kernel(int n_tiles, const uint32_t* __restrict__ tile_work, uint32_t*
       zero_ptr[i] = z;
     return;
   }
-  __shared__ uint32_t s_bin[TO_THREADS];
-  __shared__ uint32_t s_warp[TO_THREADS / 32];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  s_bin[tid] = 0;
-  __syncthreads();
-  for (int t = tid; t < n_tiles; t += TO_THREADS)
-    atomicAdd(&s_bin[TO_THREADS - 1 - min(tile_work[t] >> 2, (uint32_t)TO_THREADS - 1)], 1u);
-  __syncthreads();
-  // exclusive scan of the 1024 bins (bin 0 = heaviest)
-  const uint32_t c = s_bin[tid];
-  uint32_t inc = c;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o) inc += v;
-  }
-  if (lane == 31) s_warp[warp] = inc;
-  __syncthreads();
-  if (warp == 0) {
-    uint32_t w = s_warp[lane];
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t v = __shfl_up_sync(0xffffffffu, w, o);
-      if (lane >= o) w += v;
-    }
-    s_warp[lane] = w;
-  }
-  __syncthreads();
-  s_bin[tid] = inc - c + (warp ? s_warp[warp - 1] : 0u);
-  __syncthreads();
-  for (int t = tid; t < n_tiles; t += TO_THREADS) {
-    const uint32_t pos = atomicAdd(&s_bin[TO_THREADS - 1 - min(tile_work[t] >> 2, (uint32_t)TO_THREADS - 1)], 1u);
-    tile_order[pos] = (uint32_t)t;
-  }
+  tile_order_body(n_tiles, tile_work, tile_order);
 }
 
 // Dynamic shared memory of the backward renderer (65 KB: above the 48 KB static limit; 3 CTAs per SM fit).

@@ -229,7 +229,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 
 cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, float* out_color, float* out_depth,
-                              float* out_opacity, int* n_touched) {
+                              float* out_opacity, int* n_touched, bool tile_order_ready) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y);
   // The forward renderer starts the tiles that were heaviest in the PREVIOUS forward on this image workspace first
@@ -239,8 +239,10 @@ cudaError_t launch_render_fwd(cudaStream_t st, int W, int H, const ImageViews& i
   static const bool fwd_order = [] { const char* e = getenv("GSR_FWD_TILE_ORDER"); return !(e && e[0] == '0'); }();
   const uint32_t* order = nullptr;
   if (fwd_order && tiles_x * tiles_y > 2 * 148) {
-    cudaError_t e = launch_tile_order(st, tiles_x * tiles_y, im.tile_work, im.tile_order_fwd);
-    if (e != cudaSuccess) return e;
+    if (!tile_order_ready) {   // (gsr_forward / gsr_forward_enqueue: already sorted by chunk_scan_kernel's extra CTA)
+      cudaError_t e = launch_tile_order(st, tiles_x * tiles_y, im.tile_work, im.tile_order_fwd);
+      if (e != cudaSuccess) return e;
+    }
     order = im.tile_order_fwd;
   }
   count_launch(); launch_k(render_fwd_kernel, grid, RENDER_THREADS, 0, st, im.ranges, point_list, W, H, tiles_x, g.rec,
