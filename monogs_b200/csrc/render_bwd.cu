@@ -34,6 +34,10 @@ GSR_DEVINL unsigned trace_smid() { unsigned s; asm volatile("mov.u32 %0, %smid;"
 #define GSR_RB_UNROLL 8
 #endif
 constexpr int RB_UNROLL = GSR_RB_UNROLL;   // unroll of the phase-2 pixel loop (register budget: 3 CTAs per SM)
+#ifndef GSR_RB_P1
+#define GSR_RB_P1 2
+#endif
+constexpr int RB_P1 = GSR_RB_P1;          // queued Gaussians replayed per phase-1 loop round
 constexpr int RB_GROUP = 16;              // queued Gaussians per transposed-reduction round
 constexpr int RB_PITCH = 33;              // floats per Gaussian row of the S / A tiles: 32 pixels + 1 (conflict-free both ways)
 
@@ -192,22 +196,24 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     for (int i0 = 0; i0 < qn; i0 += RB_GROUP) {
       const int gn = min(RB_GROUP, qn - i0);
       // ---- phase 1 (lane = pixel): replay gn Gaussians, park S = G dL/dalpha and A = alpha T per (Gaussian, pixel).
-      //      The records of Gaussian k+1 are fetched from shared memory while k is computed.
-      int j = (int)my_queue[i0];
-      float4 a = sg.rec[3 * j], co = sg.rec[3 * j + 1], c = sg.rec[3 * j + 2];
-      for (int k = 0; k < gn; ++k) {
+      //      RB_P1 queued Gaussians per round: their records, exp chains and colour dot products are independent
+      //      (issued together), only the short transmittance / accumulator recurrences are ordered.
+      auto p1_front = [&](int q, float& G, float& alpha, float& wk, bool& skip) {
+        const int j = (int)my_queue[q];
+        const float4 a = sg.rec[3 * j], co = sg.rec[3 * j + 1], c = sg.rec[3 * j + 2];
         const uint32_t pos = (uint32_t)(total - 1 - (b * RB_BATCH + j));  // 0-based list position
-        const float4 a_k = a, co_k = co, c_k = c;
-        if (k + 1 < gn) {
-          j = (int)my_queue[i0 + k + 1];
-          a = sg.rec[3 * j]; co = sg.rec[3 * j + 1]; c = sg.rec[3 * j + 2];
-        }
-        const float dx = fsub(a_k.x, pixx), dy = fsub(a_k.y, pixy);
-        const float power = gauss_power(dx, dy, co_k.x, co_k.y, co_k.z);
-        const float G = expf(power);
-        const float alpha = fminf(fmul(co_k.w, G), 0.99f);
+        const float dx = fsub(a.x, pixx), dy = fsub(a.y, pixy);
+        const float power = gauss_power(dx, dy, co.x, co.y, co.z);
+        G = expf(power);
+        alpha = fminf(fmul(co.w, G), 0.99f);
         // skip rules of backward.cu:676-689
-        const bool skip = !inside || pos >= last_contributor || power > 0.0f || alpha < 1.0f / 255.0f;
+        skip = !inside || pos >= last_contributor || power > 0.0f || alpha < 1.0f / 255.0f;
+        // w = colour . dL/dpixel (+ depth): dL/dalpha = T sum_ch (c_ch - accum_rec_ch) dL/dpixel_ch
+        // (backward.cu:707-731); the per-channel recurrence accum_rec = last_alpha last_c + (1 - last_alpha) accum_rec
+        // is linear, so it is carried for this ONE scalar instead of the four channels.
+        wk = fmaf(c.x, dpr, fmaf(c.y, dpg, fmaf(c.z, dpb, a.z * dpd)));
+      };
+      auto p1_back = [&](int k, float G, float alpha, float wk, bool skip) {
         float S = 0.0f, A = 0.0f;
         if (!skip) {
           // 1 / (1 - alpha): ONE reciprocal (SFU estimate + a Newton step: <= 1 ulp on [0.01, 1], no special cases),
@@ -219,10 +225,6 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           inv_1ma = fmaf(inv_1ma, fmaf(-one_m_alpha, inv_1ma, 1.0f), inv_1ma);  // one Newton step
           T = T * inv_1ma;
           A = alpha * T;                                   // dchannel_dcolor (backward.cu:702)
-          // dL/dalpha = T sum_ch (c_ch - accum_rec_ch) dL/dpixel_ch (backward.cu:707-731). The per-channel recurrence
-          // accum_rec = last_alpha last_c + (1 - last_alpha) accum_rec is linear, so it is carried for the ONE scalar
-          // w = colour . dL/dpixel instead of the four channels.
-          const float wk = fmaf(c_k.x, dpr, fmaf(c_k.y, dpg, fmaf(c_k.z, dpb, a_k.z * dpd)));
           acc_w = fmaf(last_alpha, last_w - acc_w, acc_w);
           last_w = wk;
           last_alpha = alpha;
@@ -231,6 +233,21 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         }
         my_S[k * RB_PITCH + lane] = S;
         my_A[k * RB_PITCH + lane] = A;
+      };
+      int k = 0;
+      for (; k + RB_P1 <= gn; k += RB_P1) {
+        float G[RB_P1], al[RB_P1], wk[RB_P1];
+        bool sk[RB_P1];
+#pragma unroll
+        for (int u = 0; u < RB_P1; ++u) p1_front(i0 + k + u, G[u], al[u], wk[u], sk[u]);
+#pragma unroll
+        for (int u = 0; u < RB_P1; ++u) p1_back(k + u, G[u], al[u], wk[u], sk[u]);
+      }
+      for (; k < gn; ++k) {
+        float G, al, wk;
+        bool sk;
+        p1_front(i0 + k, G, al, wk, sk);
+        p1_back(k, G, al, wk, sk);
       }
       __syncwarp();
       // ---- phase 2 (lane = Gaussian g2 x pixel half h2): moments of S and A dL/dpixel over 16 pixels in registers
