@@ -67,6 +67,10 @@ tile_order_kernel(int n_tiles, const uint32_t* __restrict__ tile_work, uint32_t*
 #ifndef GSR_RB_BATCH
 #define GSR_RB_BATCH 256
 #endif
+#ifndef GSR_RB_TILE_ACC
+#define GSR_RB_TILE_ACC 1
+#endif
+constexpr int GRAD_ACC = 10;              // values accumulated per Gaussian (the first 10 of the packed record)
 constexpr int RB_BATCH = GSR_RB_BATCH;    // list entries staged per round (<= one per thread; queue indices are u8)
 static_assert(RB_BATCH <= RENDER_THREADS && RB_BATCH <= 256 && RB_BATCH % 32 == 0, "RB_BATCH");
 using RbStage = RenderStageT<RB_BATCH>;
@@ -75,13 +79,25 @@ struct RbShared {
   float4 dp[RENDER_WARPS][32];                 // dL/d(r, g, b, depth) of every warp's pixels
   float S[RENDER_WARPS][RB_GROUP * RB_PITCH];  // [Gaussian of the round][pixel]
   float A[RENDER_WARPS][RB_GROUP * RB_PITCH];
-  uint32_t max_contrib[RENDER_WARPS];
   uint8_t queue[RENDER_WARPS][RB_BATCH];
+#if GSR_RB_TILE_ACC
+  // the tile's partial gradients of the staged batch: the 8 warps add their (warp, Gaussian) sums here (shared-memory
+  // atomics) and ONE global atomic per value and (tile, Gaussian) goes out when the batch is done -- the reference's
+  // count (one per tile after its block reduction, backward.cu:773-786): an eighth of the global atomics and, with
+  // them, of the fp32 accumulation-order noise on cancellation-dominated gradients (run-to-run spread of dL/drot on
+  // the anisotropic layered 2 M scene 3-10e-5 -> the reference's 1-2e-5).  (max_contrib is only used before the
+  // first batch and shares the space.)
+  float acc[RB_BATCH][GRAD_ACC];
+#else
+  uint32_t max_contrib_[RENDER_WARPS];
+#endif
 };
 
 #ifndef GSR_RB_MIN_CTAS
 #define GSR_RB_MIN_CTAS 3
 #endif
+// 3 CTAs per SM: 3 x (dynamic + 1 KB reserved) <= 228 KB
+static_assert(GSR_RB_MIN_CTAS != 3 || sizeof(RbShared) <= 76800, "RbShared no longer fits three times into an SM");
 __global__ void __launch_bounds__(RENDER_THREADS, GSR_RB_MIN_CTAS)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                   int tiles_x, const float* __restrict__ bg, const float4* __restrict__ rec,
@@ -99,7 +115,11 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   extern __shared__ __align__(16) unsigned char rb_smem_raw[];
   RbShared& sh = *reinterpret_cast<RbShared*>(rb_smem_raw);
   RbStage* const stage = sh.stage;
-  uint32_t* const s_max = sh.max_contrib;
+#if GSR_RB_TILE_ACC
+  uint32_t* const s_max = reinterpret_cast<uint32_t*>(&sh.acc[0][0]);
+#else
+  uint32_t* const s_max = sh.max_contrib_;
+#endif
 
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   int tile_y = blockIdx.y, tile_x = blockIdx.x;
@@ -142,6 +162,14 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   uint32_t tile_last = 0;
 #pragma unroll
   for (int i = 0; i < RENDER_WARPS; ++i) tile_last = max(tile_last, s_max[i]);
+#if GSR_RB_TILE_ACC
+  __syncthreads();   // s_max read by everyone before the accumulators (same space) are cleared
+  if (tid < RB_BATCH) {
+#pragma unroll
+    for (int c = 0; c < GRAD_ACC; ++c) sh.acc[tid][c] = 0.0f;
+  }
+  // (ordered before the first accumulation by the barrier that follows the first batch's gather)
+#endif
   const int total = (int)tile_last;  // list positions [0, total) are replayed, from the back
   const int n_batches = (total + RB_BATCH - 1) / RB_BATCH;
 
@@ -282,7 +310,11 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         if (have && h2 == 0) {
           // dL/dG = o dL/dalpha; dG/ddelx = -G (dx cx + dy cy), dG/ddely = -G (dy cz + dx cy)   (backward.cu:746-771)
           const float o = cog.w;
+#if GSR_RB_TILE_ACC
+          float* dst = sh.acc[jg];
+#else
           float* dst = packed + (size_t)sg.id[jg] * GRAD_STRIDE;
+#endif
           atomicAdd(dst + 0, -o * (cog.x * mx + cog.y * my) * ddelx_dx);
           atomicAdd(dst + 1, -o * (cog.z * my + cog.y * mx) * ddely_dy);
           atomicAdd(dst + 2, -0.5f * o * mxx);
@@ -298,6 +330,21 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       __syncwarp();   // the S / A tiles are rewritten by the next round
     }
     __syncthreads();
+#if GSR_RB_TILE_ACC
+    // flush the batch: thread t owns staged entry t (it also re-gathers slot t next, so sg.id[t] is still valid here);
+    // the next batch's accumulation starts behind the barrier at the top of the loop
+    if (tid < count) {
+      float v[GRAD_ACC];
+      bool any = false;
+#pragma unroll
+      for (int c = 0; c < GRAD_ACC; ++c) { v[c] = sh.acc[tid][c]; any |= v[c] != 0.0f; }
+      if (any) {
+        float* dst = packed + (size_t)sg.id[tid] * GRAD_STRIDE;
+#pragma unroll
+        for (int c = 0; c < GRAD_ACC; ++c) { atomicAdd(dst + c, v[c]); sh.acc[tid][c] = 0.0f; }
+      }
+    }
+#endif
   }
   cp_async_wait<0>();
 #ifdef GSR_CTA_TRACE

@@ -71,10 +71,11 @@ def _run_ours(cam, sc, bg, dcol, ddep, **kw):
     keys = ours.debug_sorted_keys(geom, binning, plist, P, R, cam.W, cam.H) if R > 0 else torch.empty(0)
     ba = _bargs(fa, radii, R, geom, plist, img, dcol, ddep)
     grads = ours.rasterize_gaussians_backward(*ba)
+    grads2 = ours.rasterize_gaussians_backward(*ba)     # second run: our own run-to-run spread (fp32 atomics)
     _, tau = ours.rasterize_gaussians_backward_fused(*ba)
     torch.cuda.synchronize()
     return dict(R=R, color=col, radii=radii, geom=geom, plist=plist, img=img, depth=dep, opacity=opa, n_touched=nt,
-                keys=keys, grads=grads, tau=tau, fa=fa)
+                keys=keys, grads=grads, grads2=grads2, tau=tau, fa=fa)
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -206,12 +207,19 @@ def _compare_with_reference(cam, sc, bg, dcol, ddep, grad_tol=1e-4, well_conditi
     n = lambda t: t.detach().cpu().numpy()
     for a, r, k in ((o["color"], col_r, "color"), (o["depth"], dep_r, "depth"), (o["opacity"], opa_r, "opacity")):
         assert rel_inf(n(a), n(r)) <= 1e-5, k
-    for name, a, r, r2 in zip(GRAD_NAMES, o["grads"], gr, gr2):
+    # Bar: the north star's 1e-4 relative per tensor. Both implementations accumulate fp32 partial gradients with
+    # atomics in arbitrary order; on the cancellation-dominated rotation / scale gradients of the anisotropic layered
+    # 2 M scene the reference disagrees with its own second run by 1-3e-5 and this library by 1-2e-5 (one global
+    # atomic per (tile, Gaussian) like the reference), the two with each other by 3-6e-5. Should a box ever show a
+    # larger run-to-run spread, the bar follows 3 x the measured spread of the two -- never beyond 5e-4.
+    for name, a, a2, r, r2 in zip(GRAD_NAMES, o["grads"], o["grads2"], gr, gr2):
         if a.numel():
             if well_conditioned is not None and name in ("dmeans3D", "dcov3D", "dscales", "drots", "dtau"):
-                a, r, r2 = a[well_conditioned], r[well_conditioned], r2[well_conditioned]
-            spread = rel_inf(n(r2), n(r))  # the reference's own run-to-run spread (fp32 atomics)
-            assert rel_inf(n(a), n(r)) <= max(grad_tol, 3 * spread), (name, rel_inf(n(a), n(r)), spread)
+                a, a2, r, r2 = a[well_conditioned], a2[well_conditioned], r[well_conditioned], r2[well_conditioned]
+            spread = rel_inf(n(r2), n(r)) + rel_inf(n(a2), n(a))
+            err = rel_inf(n(a), n(r))
+            assert err <= max(grad_tol, 3 * spread), (name, err, spread)
+            assert err <= 5 * grad_tol, (name, err)   # and never more than 5e-4, whatever the spread
     if well_conditioned is None:
         assert rel_inf(n(o["tau"]), n(gr[8]).astype(np.float64).sum(0)) <= max(grad_tol, 1e-4)
     return o
