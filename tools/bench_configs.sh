@@ -2,7 +2,7 @@
 # tools/bench_configs.sh -- the non-headline BASELINE.json configs, ours and the reference arm, one JSON line each
 mkdir -p gpurun_out
 : > gpurun_out/bench_configs.jsonl
-for wl in c2 c3 c5; do
+for wl in c2 c3 c4 c5; do
   for impl in ours reference; do
     python bench.py --workload $wl --impl $impl --steps 20 --warmup 5 --no-cpu-baseline 2>> gpurun_out/bench_configs.err >> gpurun_out/bench_configs.jsonl
   done
