@@ -156,3 +156,42 @@ def test_sort_pairs_u64_stable(built):
         mask = (1 << end_bit) - 1
         order = torch.sort(keys & mask, stable=True)[1]
         assert torch.equal(vo.long(), order) and torch.equal(ko, keys[order]), (n, end_bit)
+
+
+def test_profile_hook_times_selected_stages_only(built):
+    """gsr_profile_enable(1): every stage of a forward + backward is bracketed; gsr_profile_enable(1 | mask << 8): only
+    the stages of the mask (bench.py brackets just the dominant stage inside its timed region)."""
+    lib = _abi.load()
+    cam = synth.make_camera("tum_half")
+    sc = synth.make_scene(20_000, cam, seed=3, device=DEV)
+    bg = torch.zeros(3, device=DEV)
+
+    def step():
+        leaves = [sc[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "colors", "scales", "rotations")]
+        m3, op, col, s, r = leaves
+        m2 = torch.zeros_like(m3, requires_grad=True)
+        out = GaussianRasterizer(_settings(cam, bg))(means3D=m3, means2D=m2, opacities=op, colors_precomp=col, scales=s,
+                                                     rotations=r)
+        (out[0].sum() + out[2].sum()).backward()
+        torch.cuda.synchronize()
+
+    step()
+    ms, n = (C.c_double * 9)(), (C.c_int * 9)()
+    lib.gsr_profile_collect(ms, n)
+    try:
+        lib.gsr_profile_enable(1)
+        step()
+        lib.gsr_profile_enable(0)
+        assert lib.gsr_profile_collect(ms, n) == 0
+        timed = {i for i in range(9) if n[i] > 0}
+        assert {0, 1, 2, 3, 4, 6, 7, 8} <= timed and all(ms[i] > 0 for i in timed)
+        RENDER_BWD = _abi.STAGES.index("render_bwd")
+        lib.gsr_profile_enable(1 | (1 << (8 + RENDER_BWD)))
+        step()
+        lib.gsr_profile_enable(0)
+        assert lib.gsr_profile_collect(ms, n) == 0
+        assert [i for i in range(9) if n[i] > 0] == [RENDER_BWD] and ms[RENDER_BWD] > 0
+        step()                                            # disabled: nothing recorded
+        assert lib.gsr_profile_collect(ms, n) == 0 and sum(n) == 0
+    finally:
+        lib.gsr_profile_enable(0)
