@@ -440,7 +440,7 @@ static int backward_impl(void* stream, int P, int sh_degree, int sh_coeffs, int 
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
-                                    dL_dout_depth, loss, bw.packed, zero_bytes)));
+                                    dL_dout_depth, loss, bw.packed, bw.touched_flag, zero_bytes)));
     GSR_TRY(debug_sync(st, debug));
   } else {
     GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, zero_bytes, st)));
@@ -570,7 +570,7 @@ static int backward_render_impl(void* stream, int P, int width, int height, cons
   if (num_rendered > 0) {
     StageTimer tm(st, GSR_STAGE_RENDER_BWD);
     GSR_TRY(check(launch_render_bwd(st, width, height, im, point_list, g, background, dL_dout_color,
-                                    dL_dout_depth, loss, bw.packed, zero_bytes)));
+                                    dL_dout_depth, loss, bw.packed, bw.touched_flag, zero_bytes)));
   } else {
     GSR_TRY(check(cudaMemsetAsync(bw.packed, 0, zero_bytes, st)));
   }

@@ -268,18 +268,21 @@ struct BackwardViews {
   double* tau_partial;  // [nblocks * 6]
   uint16_t* touched_list;   // [nblocks * 256] chunk-local indices of the Gaussians with a non-zero record, ascending
   uint32_t* touched_count;  // [nblocks]
-  size_t zero_bytes;        // leading bytes (packed + tau_partial) that must be zero before the backward renderer runs
+  uint8_t* touched_flag;    // [P] 1 = the backward renderer added something to the Gaussian's record
+  size_t zero_bytes;        // leading bytes (packed + tau_partial + touched_flag) that must be zero before the backward renderer runs
 };
 __host__ __device__ inline size_t carve_backward(char* base, int P, BackwardViews* v) {
   size_t off = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align_up(bytes); return p; };
   char* a = take(sizeof(float) * GRAD_STRIDE * (size_t)P);
   char* b = take(sizeof(double) * 6 * (size_t)num_pre_blocks(P));
+  char* tf = take((size_t)P);
   const size_t zb = off;
   char* c = take(sizeof(uint16_t) * 256 * (size_t)num_pre_blocks(P));
   char* d = take(sizeof(uint32_t) * (size_t)num_pre_blocks(P));
   if (v) {
     v->packed = (float*)a; v->tau_partial = (double*)b; v->touched_list = (uint16_t*)c; v->touched_count = (uint32_t*)d;
+    v->touched_flag = (uint8_t*)tf;
     v->zero_bytes = zb;
   }
   return off;

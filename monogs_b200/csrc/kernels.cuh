@@ -69,7 +69,8 @@ cudaError_t launch_tile_order(cudaStream_t st, int n_tiles, const uint32_t* tile
 cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, const float* dL_dpix,
                               const float* dL_dpix_depth, const LossView& loss, float* packed,
-                              size_t zero_bytes /* of `packed`, zeroed before the renderer runs (multiple of 16) */);
+                              uint8_t* touched_flag /* [P], inside the zeroed bytes: set for every Gaussian added to */,
+                              size_t zero_bytes /* from `packed` on, zeroed before the renderer runs (multiple of 16) */);
 
 // loss.cu
 cudaError_t launch_l1_loss(cudaStream_t st, int kind, int W, int H, const float* color, const float* depth,

@@ -127,7 +127,7 @@ GSR_DEVINL PbLoads pb_issue_loads(int idx, const float* __restrict__ means3D, co
 // 256-Gaussian chunk are listed (chunk-local index, ascending) for kernel 2.
 __global__ void __launch_bounds__(PB_THREADS)
 preprocess_bwd_classify_kernel(int P, int M, const int* __restrict__ radii, const float* __restrict__ shs,
-                               const float* __restrict__ packed, float* __restrict__ dL_dmeans2D,
+                               const uint8_t* __restrict__ touched_flag, float* __restrict__ dL_dmeans2D,
                                float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
                                float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
                                float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
@@ -149,16 +149,14 @@ preprocess_bwd_classify_kernel(int P, int M, const int* __restrict__ radii, cons
     const int idx = chunk_base + tid;
     const bool in_range = idx < P;
     int my_radius = 0;
-    float4 pk0 = make_float4(0.f, 0.f, 0.f, 0.f), pk1 = pk0, pk2 = pk0;
+    uint8_t flag = 0;
     if (in_range) {
       my_radius = __ldg(radii + idx);
-      pk0 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE));
-      pk1 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 4));
-      pk2 = __ldg(reinterpret_cast<const float4*>(packed + (size_t)idx * GRAD_STRIDE + 8));
+      flag = __ldg(touched_flag + idx);   // set by the backward renderer for every record it added to (5 B per Gaussian
+                                          // here instead of the 48-byte record)
     }
     const bool visible = in_range && my_radius > 0;
-    const bool nonzero = visible && (pk0.x != 0.f || pk0.y != 0.f || pk0.z != 0.f || pk0.w != 0.f || pk1.x != 0.f ||
-                                     pk1.y != 0.f || pk1.z != 0.f || pk1.w != 0.f || pk2.x != 0.f || pk2.y != 0.f);
+    const bool nonzero = visible && flag != 0;
     // with SH colours the zero-gradient Gaussians still get their dL_dsh written by the full path
     const bool touched = nonzero || (visible && shs && dL_dsh);
     const unsigned bal = __ballot_sync(0xffffffffu, touched);
@@ -559,7 +557,7 @@ cudaError_t launch_preprocess_bwd(cudaStream_t st, int P, int D, int M, const fl
   if (n_chunks > 0) {
     const int nb1 = n_chunks < 148 * 8 ? n_chunks : 148 * 8;
     count_launch();
-    launch_k(preprocess_bwd_classify_kernel, nb1, PB_THREADS, 0, st, p_end, M, radii, shs, bw.packed, dL_dmeans2D,
+    launch_k(preprocess_bwd_classify_kernel, nb1, PB_THREADS, 0, st, p_end, M, radii, shs, bw.touched_flag, dL_dmeans2D,
              dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drots, dL_dtau_pg, p_begin, rows,
              accumulate, touched_words, vis_u8, bw.touched_list, bw.touched_count);
     count_launch();

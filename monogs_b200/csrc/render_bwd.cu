@@ -103,7 +103,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   int tiles_x, const float* __restrict__ bg, const float4* __restrict__ rec,
                   const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
                   const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth, LossView loss,
-                  float* __restrict__ packed /*[P][GRAD_STRIDE]*/, const uint32_t* __restrict__ tile_order) {
+                  float* __restrict__ packed /*[P][GRAD_STRIDE]*/, uint8_t* __restrict__ touched_flag /*[P]*/,
+                  const uint32_t* __restrict__ tile_order) {
   pdl_launch_dependents();
 #ifdef GSR_CTA_TRACE
   const unsigned long long t_enter = trace_now();
@@ -314,6 +315,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           float* dst = sh.acc[jg];
 #else
           float* dst = packed + (size_t)sg.id[jg] * GRAD_STRIDE;
+          touched_flag[sg.id[jg]] = 1;
 #endif
           atomicAdd(dst + 0, -o * (cog.x * mx + cog.y * my) * ddelx_dx);
           atomicAdd(dst + 1, -o * (cog.z * my + cog.y * mx) * ddely_dy);
@@ -339,9 +341,11 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 #pragma unroll
       for (int c = 0; c < GRAD_ACC; ++c) { v[c] = sh.acc[tid][c]; any |= v[c] != 0.0f; }
       if (any) {
-        float* dst = packed + (size_t)sg.id[tid] * GRAD_STRIDE;
+        const uint32_t id = sg.id[tid];
+        float* dst = packed + (size_t)id * GRAD_STRIDE;
 #pragma unroll
         for (int c = 0; c < GRAD_ACC; ++c) { atomicAdd(dst + c, v[c]); sh.acc[tid][c] = 0.0f; }
+        touched_flag[id] = 1;   // the per-Gaussian backward reads this byte instead of the 48-byte record to classify
       }
     }
 #endif
@@ -372,7 +376,8 @@ static bool tile_order_enabled() {  // GSR_TILE_ORDER=0: linear CTA -> tile map 
 
 cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& im, const uint32_t* point_list,
                               const GeomViews& g, const float* bg, const float* dL_dpix,
-                              const float* dL_dpix_depth, const LossView& loss, float* packed, size_t zero_bytes) {
+                              const float* dL_dpix_depth, const LossView& loss, float* packed, uint8_t* touched_flag,
+                              size_t zero_bytes) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   dim3 grid(tiles_x, tiles_y);
   const uint32_t* order = nullptr;
@@ -392,7 +397,7 @@ cudaError_t launch_render_bwd(cudaStream_t st, int W, int H, const ImageViews& i
                                                             (int)sizeof(RbShared));
   if (smem_attr != cudaSuccess) return smem_attr;
   count_launch(); launch_k(render_bwd_kernel, grid, RENDER_THREADS, sizeof(RbShared), st, im.ranges, point_list, W, H, tiles_x, bg, g.rec,
-                                                 im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, loss, packed, order);
+                                                 im.final_T, im.n_contrib, dL_dpix, dL_dpix_depth, loss, packed, touched_flag, order);
   return cudaGetLastError();
 }
 
